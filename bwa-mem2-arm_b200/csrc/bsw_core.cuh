@@ -1,0 +1,389 @@
+/*
+ * bsw_core.cuh -- per-thread dynamic programming of the banded extension
+ * (BandedPairWiseSW::getScores8/16, bwa-mem2 src/bandedSWA.cpp; semantics =
+ * bwa ksw_extend2).
+ *
+ * Mapping (DESIGN.md "BSW kernel"): inter-pair SIMD-in-word.  One thread owns
+ * TWO sequence pairs, lane A in the low and lane B in the high 16 bits of every
+ * 32-bit register, and sweeps them row-synchronously, exactly like one
+ * 2-lane slice of the reference's inter-sequence vector kernels.  A warp is a
+ * 64-pair vector.  All cell arithmetic is packed signed 16-bit DPX:
+ *     M  = min(Hd + s, 2*Hd)                 VIADDMNMX.S16x2   (zero gate of A.1)
+ *     h  = max3(M, e, f)                     VIMNMX3.S16x2
+ *     e' = max(M - oe_del, e - e_del, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
+ *     f' = max(M - oe_ins, f - e_ins, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
+ *     (m, mj) = max over (h << 8 | j)        IMAD + VIMNMX.U16x2  (ties -> last j)
+ * The substitution score of both lanes comes from one LOP3 + one PRMT used as
+ * an 8-entry byte LUT with sign replication.
+ * The DP row (H shifted by one column, E) lives in shared memory as
+ * [column][thread] uint2, so every access is bank-conflict free no matter
+ * which column a thread is at; rows are never re-read from HBM.
+ *
+ * The functions are __host__ __device__: tests/emu builds them with g++ (DPX
+ * emulated in plain C) to check the kernel logic against the oracle without a
+ * GPU.  The product library only ever runs the __device__ instantiation.
+ */
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define BSW_HD __host__ __device__ __forceinline__
+#else
+#define BSW_HD static inline
+struct uint2 { uint32_t x, y; };
+static inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 r; r.x = x; r.y = y; return r; }
+struct int2 { int32_t x, y; };
+static inline int2 make_int2(int32_t x, int32_t y) { int2 r; r.x = x; r.y = y; return r; }
+#endif
+
+namespace bswk {
+
+struct Const {
+    int o_del, e_del, o_ins, e_ins, oe_del, oe_ins;
+    int zdrop, end_bonus;
+    int a;        /* match score  (> 0)              */
+    int b;        /* mismatch penalty (> 0)          */
+    int ambig;    /* score against N (<= 0, ref: -1) */
+    int maxsc;    /* max entry of the scoring matrix */
+};
+
+struct PairIn  { int idr, idq, len1, len2, h0, valid; };
+struct PairOut { int score, tle, gtle, qle, gscore, max_off; long long cells; };
+
+/* ---------------------------------------------------------------- packed ops */
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ uint32_t p_addmin(uint32_t a, uint32_t b, uint32_t c) { return __viaddmin_s16x2(a, b, c); }
+__device__ __forceinline__ uint32_t p_max3(uint32_t a, uint32_t b, uint32_t c)   { return __vimax3_s16x2(a, b, c); }
+__device__ __forceinline__ uint32_t p_addmax_relu(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2_relu(a, b, c); }
+__device__ __forceinline__ uint32_t p_add(uint32_t a, uint32_t b)                { return __vadd2(a, b); }
+__device__ __forceinline__ uint32_t p_maxu(uint32_t a, uint32_t b)               { return __vmaxu2(a, b); }
+__device__ __forceinline__ uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)   { return __byte_perm(a, b, s); }
+#else
+static inline int16_t lo16(uint32_t v) { return (int16_t)(v & 0xffff); }
+static inline int16_t hi16(uint32_t v) { return (int16_t)(v >> 16); }
+static inline uint32_t pk(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+static inline int imin(int a, int b) { return a < b ? a : b; }
+static inline int imax(int a, int b) { return a > b ? a : b; }
+static inline uint32_t p_addmin(uint32_t a, uint32_t b, uint32_t c)
+{ return pk(imin((int16_t)(lo16(a) + lo16(b)), lo16(c)), imin((int16_t)(hi16(a) + hi16(b)), hi16(c))); }
+static inline uint32_t p_max3(uint32_t a, uint32_t b, uint32_t c)
+{ return pk(imax(imax(lo16(a), lo16(b)), lo16(c)), imax(imax(hi16(a), hi16(b)), hi16(c))); }
+static inline uint32_t p_addmax_relu(uint32_t a, uint32_t b, uint32_t c)
+{ return pk(imax(imax((int16_t)(lo16(a) + lo16(b)), lo16(c)), 0), imax(imax((int16_t)(hi16(a) + hi16(b)), hi16(c)), 0)); }
+static inline uint32_t p_add(uint32_t a, uint32_t b) { return pk(lo16(a) + lo16(b), hi16(a) + hi16(b)); }
+static inline uint32_t p_maxu(uint32_t a, uint32_t b)
+{ uint32_t l = (a & 0xffff) > (b & 0xffff) ? (a & 0xffff) : (b & 0xffff), h = (a >> 16) > (b >> 16) ? (a >> 16) : (b >> 16); return l | (h << 16); }
+static inline uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)
+{
+    uint64_t v = ((uint64_t)b << 32) | a; uint32_t r = 0;
+    for (int k = 0; k < 4; ++k) {
+        uint32_t n = (s >> (4 * k)) & 0xf;
+        uint32_t byte = (uint32_t)(v >> (8 * (n & 7))) & 0xff;
+        if (n & 8) byte = (byte & 0x80) ? 0xff : 0x00;
+        r |= byte << (8 * k);
+    }
+    return r;
+}
+#endif
+
+BSW_HD uint32_t pack2(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+BSW_HD int half_s(uint32_t v, int p) { return p ? (int)(int16_t)(v >> 16) : (int)(int16_t)(v & 0xffff); }
+BSW_HD int half_u(uint32_t v, int p) { return p ? (int)(v >> 16) : (int)(v & 0xffff); }
+BSW_HD int mn(int a, int b) { return a < b ? a : b; }
+BSW_HD int mx(int a, int b) { return a > b ? a : b; }
+
+/* limits of the packed kernel: every cell value h <= h0 + min(len1,len2)*a must
+ * fit 8 bits and every column index must fit 8 bits, so that (h << 8 | j) fits
+ * one unsigned 16-bit lane. */
+#define BSW_PACKED_MAX_SCORE 255
+#define BSW_PACKED_MAX_QLEN  255
+
+BSW_HD bool packed_eligible(const Const &c, int len1, int len2, int h0)
+{
+    if (len1 < 0 || len2 < 0 || h0 <= 0) return false;
+    if (len2 > BSW_PACKED_MAX_QLEN) return false;
+    long long bound = (long long)h0 + (long long)mn(len1, len2) * c.a;
+    return bound <= BSW_PACKED_MAX_SCORE;
+}
+
+/* effective band of one pair (A.1: w = min(w, max_ins, max_del)) */
+BSW_HD int eff_band(const Const &c, int qlen, int w)
+{
+    int max_ins = (int)((double)(qlen * c.maxsc + c.end_bonus - c.o_ins) / c.e_ins + 1.);
+    max_ins = max_ins > 1 ? max_ins : 1;
+    w = w < max_ins ? w : max_ins;
+    int max_del = (int)((double)(qlen * c.maxsc + c.end_bonus - c.o_del) / c.e_del + 1.);
+    max_del = max_del > 1 ? max_del : 1;
+    w = w < max_del ? w : max_del;
+    return w;
+}
+
+/* score LUT for PRMT: index = (q ^ t) | ((q | t) & 4):  0 match, 1..3 mismatch, 4..7 ambiguous */
+BSW_HD uint32_t lut_lo(const Const &c)
+{ uint32_t m = (uint32_t)c.a & 0xff, x = (uint32_t)(-c.b) & 0xff; return m | (x << 8) | (x << 16) | (x << 24); }
+BSW_HD uint32_t lut_hi(const Const &c)
+{ uint32_t n = (uint32_t)c.ambig & 0xff; return n * 0x01010101u; }
+
+/* per-pair scalar state of the row loop */
+struct PState {
+    int qlen, tlen, h0, w, idr;
+    int beg, end, max, max_i, max_j, max_ie, gscore, max_off;
+    int act;
+    long long cells;
+};
+
+/*
+ * One thread, two pairs.  he[j*S] = { H(i-1, j-1) packed, E(i, j) packed },
+ * qs[j*S] = PRMT selector of query column j for both lanes.  S = element stride
+ * (32 in the kernel: [column][lane]).
+ */
+template <int S>
+BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const PairIn &B,
+                              const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                              uint2 *he, uint16_t *qs, PairOut &oa, PairOut &ob)
+{
+    PState ps[2];
+    const PairIn *in[2] = { &A, &B };
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const PairIn &x = *in[p];
+        ps[p].qlen = x.valid ? x.len2 : 0;
+        ps[p].tlen = x.valid ? x.len1 : 0;
+        ps[p].h0 = x.valid ? x.h0 : 0;
+        ps[p].idr = x.idr;
+        ps[p].w = eff_band(c, ps[p].qlen, w_in);
+        ps[p].beg = 0; ps[p].end = ps[p].qlen;
+        ps[p].max = ps[p].h0; ps[p].max_i = -1; ps[p].max_j = -1; ps[p].max_ie = -1;
+        ps[p].gscore = -1; ps[p].max_off = 0; ps[p].cells = 0;
+        ps[p].act = (x.valid && x.len1 > 0) ? 1 : 0;
+    }
+
+    /* ---- first row of H (A.1), E = 0, query selectors ---- */
+    {
+        const int qmax = mx(ps[0].qlen, ps[1].qlen);
+        int hp0 = 0, hp1 = 0;
+        for (int j = 0; j <= qmax; ++j) {
+            int hv[2];
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                int prev = p ? hp1 : hp0, v;
+                if (j > ps[p].qlen) v = 0;
+                else if (j == 0) v = ps[p].h0;
+                else if (j == 1) v = ps[p].h0 > c.oe_ins ? ps[p].h0 - c.oe_ins : 0;
+                else v = prev > c.e_ins ? prev - c.e_ins : 0;
+                hv[p] = v;
+            }
+            hp0 = hv[0]; hp1 = hv[1];
+            he[j * S] = make_uint2(pack2(hv[0], hv[1]), 0u);
+            uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
+            uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
+            qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
+            qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+        }
+    }
+
+    const uint32_t LUTLO = lut_lo(c), LUTHI = lut_hi(c);
+    const uint32_t NEG_OE_DEL = pack2(-c.oe_del, -c.oe_del), NEG_OE_INS = pack2(-c.oe_ins, -c.oe_ins);
+    const uint32_t NEG_E_DEL = pack2(-c.e_del, -c.e_del), NEG_E_INS = pack2(-c.e_ins, -c.e_ins);
+    const int BIG = 0x3fffffff;
+
+    int i = 0;
+    while (ps[0].act | ps[1].act) {
+        int rb[2], re[2], h1i[2];
+        uint32_t tb[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            PState &s = ps[p];
+            if (s.act) {
+                if (s.beg < i - s.w) s.beg = i - s.w;
+                if (s.end > i + s.w + 1) s.end = i + s.w + 1;
+                if (s.end > s.qlen) s.end = s.qlen;
+                int h1 = 0;
+                if (s.beg == 0) { h1 = s.h0 - (c.o_del + c.e_del * (i + 1)); if (h1 < 0) h1 = 0; }
+                h1i[p] = h1;
+                const bool some = s.beg < s.end;
+                rb[p] = some ? s.beg : BIG; re[p] = some ? s.end : 0;
+                uint32_t t = ref[s.idr + i];
+                tb[p] = t > 4u ? 4u : t;
+                if (some) s.cells += s.end - s.beg;
+            } else { rb[p] = BIG; re[p] = 0; h1i[p] = 0; tb[p] = 0; }
+        }
+        const int jlo = mn(rb[0], rb[1]), jhi = mx(re[0], re[1]);
+        const int c0 = mx(rb[0], rb[1]), c1 = mn(re[0], re[1]);
+        const uint32_t T = tb[0] * 0x0011u | tb[1] * 0x1100u;
+        uint32_t f = 0, key = 0, h1 = pack2(h1i[0], h1i[1]);
+
+        /* generic masked cell: lanes outside their [beg,end) are left untouched */
+#define BSW_CELL_MASKED(J)                                                              \
+        {                                                                               \
+            const int j_ = (J);                                                         \
+            const uint32_t MK = ((j_ >= rb[0] && j_ < re[0]) ? 0x0000ffffu : 0u) |      \
+                                ((j_ >= rb[1] && j_ < re[1]) ? 0xffff0000u : 0u);       \
+            uint2 v = he[j_ * S];                                                       \
+            uint32_t q_ = qs[j_ * S];                                                   \
+            uint32_t x_ = (q_ ^ T) | ((q_ | T) & 0x4444u);                              \
+            uint32_t s_ = p_perm(LUTLO, LUTHI, x_);                                     \
+            uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);                                 \
+            uint32_t h_ = p_max3(M_, v.y, f);                                           \
+            uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));         \
+            uint32_t fn = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));           \
+            uint32_t kk = ((h_ & MK) << 8) + ((uint32_t)j_ * 0x00010001u);              \
+            he[j_ * S] = make_uint2((h1 & MK) | (v.x & ~MK), (en & MK) | (v.y & ~MK));  \
+            f = fn & MK;                                                                \
+            h1 = (h_ & MK) | (h1 & ~MK);                                                \
+            key = p_maxu(key, kk & MK);                                                 \
+        }
+
+        int j = jlo;
+        const int head_end = mn(c0, jhi);
+        for (; j < head_end; ++j) BSW_CELL_MASKED(j)
+        /* both lanes in range: no masks */
+        if (c1 > c0) {
+            uint2 *hp = he + c0 * S;
+            const uint16_t *qp = qs + c0 * S;
+            uint32_t jv = (uint32_t)c0 * 0x00010001u;
+            const int nb = c1 - c0;
+#pragma unroll 4
+            for (int k = 0; k < nb; ++k) {
+                uint2 v = hp[k * S];
+                uint32_t q_ = qp[k * S];
+                uint32_t x_ = (q_ ^ T) | ((q_ | T) & 0x4444u);
+                uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
+                uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);
+                uint32_t h_ = p_max3(M_, v.y, f);
+                uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));
+                f = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));
+                hp[k * S] = make_uint2(h1, en);
+                h1 = h_;
+                key = p_maxu(key, (h_ << 8) + jv);
+                jv += 0x00010001u;
+            }
+            j = c1;
+        }
+        if (j < c0) j = c0;            /* nothing lives in [c1, c0) when the ranges are disjoint */
+        for (; j < jhi; ++j) BSW_CELL_MASKED(j)
+#undef BSW_CELL_MASKED
+
+        /* ---- per-pair row epilogue (A.1) ---- */
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            PState &s = ps[p];
+            if (!s.act) continue;
+            const uint32_t hm = p ? 0xffff0000u : 0x0000ffffu;
+            const int h1p = half_s(h1, p);
+            const int kp = half_u(key, p);
+            const int m = kp >> 8, mj = kp & 0xff;
+            {   /* eh[end].h = h1; eh[end].e = 0 */
+                uint2 v = he[s.end * S];
+                v.x = (v.x & ~hm) | (h1 & hm);
+                v.y = v.y & ~hm;
+                he[s.end * S] = v;
+            }
+            const int jafter = s.beg < s.end ? s.end : s.beg;
+            if (jafter == s.qlen) {
+                s.max_ie = s.gscore > h1p ? s.max_ie : i;
+                s.gscore = s.gscore > h1p ? s.gscore : h1p;
+            }
+            if (m == 0) { s.act = 0; continue; }
+            if (m > s.max) {
+                int off = mj - i; off = off < 0 ? -off : off;
+                s.max = m; s.max_i = i; s.max_j = mj;
+                s.max_off = s.max_off > off ? s.max_off : off;
+            } else if (c.zdrop > 0) {
+                const int di = i - s.max_i, dj = mj - s.max_j;
+                if (di > dj) { if (s.max - m - (di - dj) * c.e_del > c.zdrop) { s.act = 0; continue; } }
+                else         { if (s.max - m - (dj - di) * c.e_ins > c.zdrop) { s.act = 0; continue; } }
+            }
+            int jj = s.beg;
+            while (jj < s.end) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; ++jj; }
+            s.beg = jj;
+            jj = s.end;
+            while (jj >= s.beg) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; --jj; }
+            s.end = jj + 2 < s.qlen ? jj + 2 : s.qlen;
+            if (i + 1 >= s.tlen) s.act = 0;
+        }
+        ++i;
+    }
+
+    PairOut *out[2] = { &oa, &ob };
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        out[p]->score = ps[p].max; out[p]->qle = ps[p].max_j + 1; out[p]->tle = ps[p].max_i + 1;
+        out[p]->gtle = ps[p].max_ie + 1; out[p]->gscore = ps[p].gscore; out[p]->max_off = ps[p].max_off;
+        out[p]->cells = ps[p].cells;
+    }
+}
+
+/*
+ * General 32-bit path: one thread, one pair, any length / score (pairs the
+ * packed kernel does not admit, incl. the reference's scalar tier >= 32768).
+ * eh[j*S] = { H(i-1,j-1), E(i,j) } in global memory.  Literal A.1.
+ */
+template <typename IDX>
+BSW_HD void bsw_general_thread(const Const &c, int w, const PairIn &P,
+                               const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                               int2 *eh, IDX S, PairOut &o)
+{
+    const int qlen = P.len2, tlen = P.len1, h0 = P.h0;
+    const uint8_t *query = qer + P.idq, *target = ref + P.idr;
+    int i, j, beg, end, max, max_i, max_j, max_ie, gscore, max_off;
+    long long cells = 0;
+    {
+        int prev = 0;
+        for (j = 0; j <= qlen; ++j) {
+            int v;
+            if (j == 0) v = h0;
+            else if (j == 1) v = h0 > c.oe_ins ? h0 - c.oe_ins : 0;
+            else v = prev > c.e_ins ? prev - c.e_ins : 0;
+            prev = v;
+            eh[(IDX)j * S] = make_int2(v, 0);
+        }
+    }
+    w = eff_band(c, qlen, w);
+    max = h0; max_i = max_j = -1; max_ie = -1; gscore = -1; max_off = 0;
+    beg = 0; end = qlen;
+    for (i = 0; i < tlen; ++i) {
+        int f = 0, h1, m = 0, mj = -1;
+        int t = target[i]; t = t > 4 ? 4 : t;
+        if (beg < i - w) beg = i - w;
+        if (end > i + w + 1) end = i + w + 1;
+        if (end > qlen) end = qlen;
+        if (beg == 0) { h1 = h0 - (c.o_del + c.e_del * (i + 1)); if (h1 < 0) h1 = 0; }
+        else h1 = 0;
+        if (end > beg) cells += end - beg;
+        for (j = beg; j < end; ++j) {
+            int2 v = eh[(IDX)j * S];
+            int q = query[j]; q = q > 4 ? 4 : q;
+            int sc = (q == 4 || t == 4) ? c.ambig : (q == t ? c.a : -c.b);
+            int M = v.x ? v.x + sc : 0, e = v.y, h, tt;
+            h = M > e ? M : e; h = h > f ? h : f;
+            eh[(IDX)j * S].x = h1;
+            h1 = h;
+            mj = m > h ? mj : j; m = m > h ? m : h;
+            tt = M - c.oe_del; tt = tt > 0 ? tt : 0; e -= c.e_del; e = e > tt ? e : tt;
+            eh[(IDX)j * S].y = e;
+            tt = M - c.oe_ins; tt = tt > 0 ? tt : 0; f -= c.e_ins; f = f > tt ? f : tt;
+        }
+        eh[(IDX)end * S] = make_int2(h1, 0);
+        if ((beg < end ? end : beg) == qlen) {
+            max_ie = gscore > h1 ? max_ie : i;
+            gscore = gscore > h1 ? gscore : h1;
+        }
+        if (m == 0) break;
+        if (m > max) {
+            int off = mj - i; off = off < 0 ? -off : off;
+            max = m; max_i = i; max_j = mj; max_off = max_off > off ? max_off : off;
+        } else if (c.zdrop > 0) {
+            if (i - max_i > mj - max_j) { if (max - m - ((i - max_i) - (mj - max_j)) * c.e_del > c.zdrop) break; }
+            else                        { if (max - m - ((mj - max_j) - (i - max_i)) * c.e_ins > c.zdrop) break; }
+        }
+        for (j = beg; j < end; ++j) { int2 v = eh[(IDX)j * S]; if (v.x | v.y) break; }
+        beg = j;
+        for (j = end; j >= beg; --j) { int2 v = eh[(IDX)j * S]; if (v.x | v.y) break; }
+        end = j + 2 < qlen ? j + 2 : qlen;
+    }
+    o.score = max; o.qle = max_j + 1; o.tle = max_i + 1; o.gtle = max_ie + 1;
+    o.gscore = gscore; o.max_off = max_off; o.cells = cells;
+}
+
+} /* namespace bswk */

@@ -1,0 +1,168 @@
+/*
+ * include/bsw_cuda.h -- C ABI of the B200 (sm_100a) batched banded Smith-Waterman
+ * seed-extension path and the kswv batched mate-rescue path.
+ *
+ * This is the drop-in boundary: every entry point keeps
+ * the argument list of the bwa-mem2 method it replaces, with the object turned
+ * into an opaque handle.  Plain pointers and sizes only.  INTEGRATION.md shows
+ * the C++ shim classes (`BandedPairWiseSW`, `kswv`) a maintainer drops into
+ * bwa-mem2 so that bwamem.cpp / bwamem_pair.cpp compile unchanged; the same
+ * classes ship in bwa-mem2-arm_b200/bandedSWA_b200.h.
+ *
+ * Reference interfaces replaced ("R:" = /root/reference, which quotes the
+ * signatures; the code itself is bwa-mem2 v2.2.1 src/bandedSWA.{h,cpp},
+ * src/kswv.{h,cpp}):
+ *   BandedPairWiseSW ctor   R:docs-archive/INTEGRATION_COMPLETE.md:61-63
+ *   getScores8 / getScores16 R:docs-archive/WEEK1_WRAPPER_COMPLETE.md:263-268
+ *                            R:docs-archive/WEEK2_STATUS.md:143-156,209-211
+ *   kswv ctor / getScores8/16(…, kswr_t* aln, …, phase)
+ *                            R:docs-archive/INTEGRATION_COMPLETE.md:57-58,69-71,95-97
+ *                            R:docs-archive/WEEK2_STATUS.md:94
+ *   SeqPair field use        R:PHASE2_COMPLETE.md:138-140, R:docs-archive/WEEK2_STATUS.md:49-53,159
+ *   h0 carries `xtra` for kswv  R:docs-archive/WEEK1_BENCHMARK_RESULTS.md:97-103
+ *
+ * Error convention = the reference's (R:docs-archive/WEEK1_WRAPPER_COMPLETE.md:239-242):
+ * void returns; on a CUDA failure or a contract violation the library prints a
+ * message to stderr and calls exit(EXIT_FAILURE).  There is NO CPU fallback:
+ * without a usable CUDA device every compute entry point fails loudly.
+ */
+#ifndef BSW_CUDA_H
+#define BSW_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* bwa-mem2 src/bandedSWA.h `typedef struct dnaSeqPair {...} SeqPair;`  14 x int32 = 56 B.
+ * Inputs : idr, idq (byte offsets into seqBufRef / seqBufQer), len1 (target), len2 (query),
+ *          h0 (BSW: initial score > 0;  kswv: the `xtra` flag word).
+ * Outputs: score, tle, gtle, qle, gscore, max_off (BSW only).
+ * id, seqid, regid are caller bookkeeping and are preserved; kswv phase 1 reads
+ * regid as the index of the kswr_t entry the pair refines. */
+typedef struct bsw_seqpair {
+    int32_t idr, idq, id;
+    int32_t len1, len2;
+    int32_t h0;
+    int32_t seqid, regid;
+    int32_t score, tle, gtle, qle;
+    int32_t gscore, max_off;
+} bsw_seqpair_t;
+
+/* bwa ksw.h `kswr_t`: 7 x int32 = 28 B */
+typedef struct bsw_kswr {
+    int32_t score;
+    int32_t te, qe;
+    int32_t score2, te2;
+    int32_t tb, qb;
+} bsw_kswr_t;
+
+#define BSW_KSW_XBYTE  0x10000
+#define BSW_KSW_XSTOP  0x20000
+#define BSW_KSW_XSUBO  0x40000
+#define BSW_KSW_XSTART 0x80000
+
+/* tier limits of the reference (bandedSWA.h MAX_SEQ_LEN8 / MAX_SEQ_LEN16) */
+#define BSW_MAX_SEQ_LEN8   128
+#define BSW_MAX_SEQ_LEN16  32768
+
+typedef struct bsw_handle  bsw_t;
+typedef struct kswv_handle kswv_t;
+
+/* ---- BandedPairWiseSW ------------------------------------------------------
+ * replaces BandedPairWiseSW::BandedPairWiseSW(o_del,e_del,o_ins,e_ins,zdrop,
+ *          end_bonus,mat,w_match,w_mismatch,numThreads) and its destructor.
+ * w_mismatch may be given as the penalty (upstream passes opt->b) or already
+ * negated (the fork's ARM call sites pass -opt->b); the ambiguous-base score is
+ * the reference's DEFAULT_AMBIG = -1.  `mat` (5x5) is accepted for signature
+ * compatibility; like the reference's vector kernels, scoring uses
+ * w_match / w_mismatch / ambig.
+ * The handle binds to the CUDA device(s) named by BSW_CUDA_DEVICES (comma list,
+ * default: LOCAL_RANK if set, else device 0).  With several devices every call
+ * shards its pair array into contiguous slices, one per device. */
+bsw_t *bsw_create(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
+                  const int8_t *mat, int8_t w_match, int8_t w_mismatch, int numThreads);
+void   bsw_destroy(bsw_t *h);
+
+/* replaces BandedPairWiseSW::getScores8 / getScores16 (same argument order).
+ * Host pointers.  Writes score,tle,gtle,qle,gscore,max_off of pairArray[0..numPairs)
+ * in place; synchronous.  getScores8 enforces the reference's 8-bit contract
+ * (len1,len2 < 128); both tiers compute in packed signed 16-bit lanes, which is
+ * value-identical on admitted pairs (SURVEY.md A.1 note 2). */
+void bsw_getScores8 (bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
+                     const uint8_t *seqBufQer, int32_t numPairs, uint16_t numThreads, int32_t w);
+void bsw_getScores16(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
+                     const uint8_t *seqBufQer, int32_t numPairs, uint16_t numThreads, int32_t w);
+/* replaces BandedPairWiseSW::scalarBandedSWAWrapper (pairs >= 32768 bases): same
+ * device path, no length limit other than memory. */
+void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
+                                const uint8_t *seqBufQer, int32_t numPairs, int nthreads, int32_t w);
+
+/* ---- kswv ------------------------------------------------------------------
+ * replaces kswv::kswv(o_del,e_del,o_ins,e_ins,w_match,w_mismatch,numThreads,
+ *          maxRefLen,maxQerLen), ~kswv and kswv::getScores8/16(pairs,ref,qer,aln,
+ *          numPairs,numThreads,phase).
+ * phase 0: aln[i] <- {score, te, qe, score2, te2, tb=-1, qb=-1} of pairArray[i],
+ *          xtra = pairArray[i].h0.
+ * phase 1: pairArray[i] holds the reversed prefixes with h0 = KSW_XSTOP|score;
+ *          updates aln[pairArray[i].regid].{tb,qb} when the reverse score matches. */
+kswv_t *kswv_create(int o_del, int e_del, int o_ins, int e_ins, int8_t w_match, int8_t w_mismatch,
+                    int numThreads, int32_t maxRefLen, int32_t maxQerLen);
+void    kswv_destroy(kswv_t *h);
+void kswv_getScores8 (kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
+                      const uint8_t *seqBufQer, bsw_kswr_t *aln, int32_t numPairs,
+                      uint16_t numThreads, int phase);
+void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
+                      const uint8_t *seqBufQer, bsw_kswr_t *aln, int32_t numPairs,
+                      uint16_t numThreads, int phase);
+
+/* ---- device-resident entry points (no reference counterpart) ----------------
+ * Same computation on buffers that already live in the HBM of the handle's
+ * first device; asynchronous on `stream` (a cudaStream_t, 0 = default stream).
+ * Used by bench.py for the inputs-resident number and by pipelines that keep
+ * read batches on the GPU.  refBytes/qerBytes are the buffer extents. */
+void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
+                       const uint8_t *d_seqBufQer, int32_t numPairs, int32_t w, void *stream);
+void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
+                        const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs,
+                        int is8, int phase, void *stream);
+
+/* pinned host arenas for the caller's SeqPair / sequence buffers (optional:
+ * pageable memory works, pinned memory lets the copies run at link speed). */
+void *bsw_host_alloc(size_t bytes);
+void  bsw_host_free(void *p);
+
+/* ---- counters / introspection ------------------------------------------------ */
+typedef struct bsw_stats {
+    int64_t calls;            /* boundary calls served                       */
+    int64_t pairs;            /* pairs processed                             */
+    int64_t pairs_packed;     /* pairs served by the packed s16x2 kernel     */
+    int64_t pairs_general;    /* pairs served by the general 32-bit kernel   */
+    int64_t cells;            /* DP cells evaluated, oracle definition (8d)  */
+    int64_t kernel_launches;  /* CUDA kernels launched by this library       */
+    int64_t h2d_bytes, d2h_bytes;
+    double  kernel_ms;        /* device time of the DP kernels (CUDA events), only
+                                 when BSW_CUDA_TIMING=1 or bsw_set_timing(h,1)   */
+} bsw_stats_t;
+void bsw_get_stats(bsw_t *h, bsw_stats_t *out);
+void bsw_reset_stats(bsw_t *h);
+void bsw_set_timing(bsw_t *h, int on);
+void kswv_get_stats(kswv_t *h, bsw_stats_t *out);
+void kswv_reset_stats(kswv_t *h);
+void kswv_set_timing(kswv_t *h, int on);
+
+/* Measures the sustained issue rate of independent packed-16-bit DPX
+ * instructions (VIMNMX3.S16x2 / VIADDMNMX.S16x2) on `device`: the roofline
+ * denominator of SURVEY.md section 8d.  Returns instructions per second over
+ * all SMs (thread-level: one count per lane per instruction), 0 on failure. */
+double bsw_measure_dpx_peak(int device, int which /*0 = vimax3, 1 = viaddmax, 2 = mix*/);
+
+/* number of visible CUDA devices (0 when none: compute calls will exit) */
+int bsw_device_count(void);
+const char *bsw_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSW_CUDA_H */

@@ -1,0 +1,57 @@
+// tests/emu/emu.cpp -- TEST-ONLY host build of the kernel's per-thread DP
+// (bwa-mem2-arm_b200/csrc/bsw_core.cuh, kswv_core.cuh) with the DPX intrinsics
+// emulated in plain C.  Lets `pytest -m "not gpu"` check the kernel LOGIC against
+// the oracle in a container without a GPU.  Never linked into libbswcuda.so.
+#include <vector>
+#include <cstring>
+#include <cstdint>
+#include "../../bwa-mem2-arm_b200/csrc/bsw_core.cuh"
+#include "../../include/bsw_cuda.h"
+
+using namespace bswk;
+
+static Const mk(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus, int a, int b, int ambig)
+{
+    Const c; c.o_del = o_del; c.e_del = e_del; c.o_ins = o_ins; c.e_ins = e_ins;
+    c.oe_del = o_del + e_del; c.oe_ins = o_ins + e_ins; c.zdrop = zdrop; c.end_bonus = end_bonus;
+    c.a = a; c.b = b; c.ambig = ambig; c.maxsc = a > 0 ? a : 0;
+    return c;
+}
+
+static void put(bsw_seqpair_t &sp, const PairOut &o)
+{ sp.score = o.score; sp.tle = o.tle; sp.gtle = o.gtle; sp.qle = o.qle; sp.gscore = o.gscore; sp.max_off = o.max_off; }
+
+extern "C" {
+
+// returns number of pairs that went through the packed path; cells_out nullable
+int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
+            int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
+            int a, int b, int ambig, int w, int force_general, long long *cells_out)
+{
+    Const c = mk(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig);
+    std::vector<int> el, ge;
+    for (int i = 0; i < n; ++i)
+        (!force_general && packed_eligible(c, pairs[i].len1, pairs[i].len2, pairs[i].h0) ? el : ge).push_back(i);
+    for (size_t k = 0; k < el.size(); k += 2) {
+        PairIn A, B; PairOut oa, ob;
+        int ia = el[k], ib = k + 1 < el.size() ? el[k + 1] : -1;
+        A = { pairs[ia].idr, pairs[ia].idq, pairs[ia].len1, pairs[ia].len2, pairs[ia].h0, 1 };
+        if (ib >= 0) B = { pairs[ib].idr, pairs[ib].idq, pairs[ib].len1, pairs[ib].len2, pairs[ib].h0, 1 };
+        else B = { 0, 0, 0, 0, 0, 0 };
+        int qm = A.len2 > B.len2 ? A.len2 : B.len2;
+        std::vector<uint2> he(qm + 2); std::vector<uint16_t> qs(qm + 2);
+        bsw_packed_thread<1>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+        put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
+        if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
+    }
+    for (int i : ge) {
+        PairIn P = { pairs[i].idr, pairs[i].idq, pairs[i].len1, pairs[i].len2, pairs[i].h0, 1 };
+        PairOut o;
+        std::vector<int2> eh(P.len2 + 2);
+        bsw_general_thread<int>(c, w, P, ref, qer, eh.data(), 1, o);
+        put(pairs[i], o); if (cells_out) cells_out[i] = o.cells;
+    }
+    return (int)el.size();
+}
+
+}
