@@ -1,0 +1,215 @@
+"""Python host mirror of the reference's BSW / kswv operator interface.
+
+Thin ctypes binding over libbswcuda.so (the C ABI in include/bsw_cuda.h).  The
+class and method names, argument order and error behaviour follow bwa-mem2's
+`BandedPairWiseSW` (src/bandedSWA.h) and `kswv` (src/kswv.h) as the reference
+docs quote them (R:docs-archive/INTEGRATION_COMPLETE.md:57-71,95-97,
+R:docs-archive/WEEK1_WRAPPER_COMPLETE.md:263-268).  There is no CPU path: if
+the CUDA library is missing, import of the symbols fails; if no GPU is present,
+constructing an object terminates the process with the library's error, as the
+reference does on fatal errors.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbswcuda.so")
+
+SEQPAIR = np.dtype([(n, "<i4") for n in (
+    "idr", "idq", "id", "len1", "len2", "h0", "seqid", "regid",
+    "score", "tle", "gtle", "qle", "gscore", "max_off")])
+KSWR = np.dtype([(n, "<i4") for n in ("score", "te", "qe", "score2", "te2", "tb", "qb")])
+KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
+
+# every symbol include/bsw_cuda.h declares (tests check the .so exports all of them)
+EXPORTS = (
+    "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
+    "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
+    "bsw_dev_getScores", "kswv_dev_getScores", "bsw_host_alloc", "bsw_host_free",
+    "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing",
+    "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
+    "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
+)
+
+
+class Stats(C.Structure):
+    _fields_ = [("calls", C.c_int64), ("pairs", C.c_int64), ("pairs_packed", C.c_int64),
+                ("pairs_general", C.c_int64), ("cells", C.c_int64), ("kernel_launches", C.c_int64),
+                ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("kernel_ms", C.c_double)]
+
+    def asdict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_}
+
+
+_lib = None
+
+
+def lib():
+    """Loads libbswcuda.so; raises (never falls back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback for this path)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i8 = C.c_void_p, C.c_int32, C.c_int8
+    L.bsw_create.restype = vp
+    L.bsw_create.argtypes = [C.c_int] * 6 + [vp, i8, i8, C.c_int]
+    L.bsw_destroy.argtypes = [vp]
+    for f in (L.bsw_getScores8, L.bsw_getScores16):
+        f.restype = None
+        f.argtypes = [vp, vp, vp, vp, i32, C.c_uint16, i32]
+    L.bsw_scalarBandedSWAWrapper.restype = None
+    L.bsw_scalarBandedSWAWrapper.argtypes = [vp, vp, vp, vp, i32, C.c_int, i32]
+    L.kswv_create.restype = vp
+    L.kswv_create.argtypes = [C.c_int] * 4 + [i8, i8, C.c_int, i32, i32]
+    L.kswv_destroy.argtypes = [vp]
+    for f in (L.kswv_getScores8, L.kswv_getScores16):
+        f.restype = None
+        f.argtypes = [vp, vp, vp, vp, vp, i32, C.c_uint16, C.c_int]
+    L.bsw_dev_getScores.restype = None
+    L.bsw_dev_getScores.argtypes = [vp, vp, vp, vp, i32, i32, vp]
+    L.kswv_dev_getScores.restype = None
+    L.kswv_dev_getScores.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, C.c_int, vp]
+    L.bsw_host_alloc.restype = vp
+    L.bsw_host_alloc.argtypes = [C.c_size_t]
+    L.bsw_host_free.argtypes = [vp]
+    for f in (L.bsw_get_stats, L.kswv_get_stats):
+        f.argtypes = [vp, C.POINTER(Stats)]
+    for f in (L.bsw_reset_stats, L.kswv_reset_stats):
+        f.argtypes = [vp]
+    for f in (L.bsw_set_timing, L.kswv_set_timing):
+        f.argtypes = [vp, C.c_int]
+    L.bsw_measure_dpx_peak.restype = C.c_double
+    L.bsw_measure_dpx_peak.argtypes = [C.c_int, C.c_int]
+    L.bsw_device_count.restype = C.c_int
+    L.bsw_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags.c_contiguous
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):          # torch tensor (host pinned or device)
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(int(a))
+
+
+def fill_scmat(a, b, ambig=-1):
+    """bwa `bwa_fill_scmat` (the 5x5 `mat` the reference constructor receives)."""
+    m = np.full((5, 5), ambig, dtype=np.int8)
+    for i in range(4):
+        for j in range(4):
+            m[i, j] = a if i == j else -b
+    return np.ascontiguousarray(m.reshape(-1))
+
+
+class BandedPairWiseSW:
+    """Mirror of bwa-mem2 `class BandedPairWiseSW` (src/bandedSWA.h).
+
+    Constructor arguments in the reference's order:
+    (o_del, e_del, o_ins, e_ins, zdrop, end_bonus, mat, w_match, w_mismatch, numThreads).
+    """
+
+    def __init__(self, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=100, end_bonus=5, mat=None,
+                 w_match=1, w_mismatch=4, numThreads=1):
+        self._L = lib()
+        self._mat = fill_scmat(w_match, abs(w_mismatch)) if mat is None else np.ascontiguousarray(mat, dtype=np.int8)
+        self._h = self._L.bsw_create(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, _ptr(self._mat),
+                                     w_match, w_mismatch, numThreads)
+        if not self._h:
+            raise RuntimeError("bsw_create failed")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.bsw_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def getScores8(self, pairArray, seqBufRef, seqBufQer, numPairs=None, numThreads=1, w=100):
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.bsw_getScores8(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), n, numThreads, w)
+
+    def getScores16(self, pairArray, seqBufRef, seqBufQer, numPairs=None, numThreads=1, w=100):
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.bsw_getScores16(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), n, numThreads, w)
+
+    def scalarBandedSWAWrapper(self, pairArray, seqBufRef, seqBufQer, numPairs=None, nthreads=1, w=100):
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.bsw_scalarBandedSWAWrapper(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), n, nthreads, w)
+
+    def dev_getScores(self, d_pairs, d_ref, d_qer, numPairs, w=100, stream=0):
+        """Device-resident variant: arguments are device pointers / CUDA tensors."""
+        self._L.bsw_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), numPairs, w, C.c_void_p(stream))
+
+    def stats(self):
+        s = Stats()
+        self._L.bsw_get_stats(self._h, C.byref(s))
+        return s.asdict()
+
+    def reset_stats(self):
+        self._L.bsw_reset_stats(self._h)
+
+    def set_timing(self, on=True):
+        self._L.bsw_set_timing(self._h, int(on))
+
+
+class kswv:
+    """Mirror of bwa-mem2 `class kswv` (src/kswv.h).
+
+    Constructor: (o_del, e_del, o_ins, e_ins, w_match, w_mismatch, numThreads, maxRefLen, maxQerLen);
+    getScores8/16(pairArray, seqBufRef, seqBufQer, aln, numPairs, numThreads, phase).
+    """
+
+    def __init__(self, o_del=6, e_del=1, o_ins=6, e_ins=1, w_match=1, w_mismatch=4, numThreads=1,
+                 maxRefLen=2048, maxQerLen=256):
+        self._L = lib()
+        self._h = self._L.kswv_create(o_del, e_del, o_ins, e_ins, w_match, w_mismatch, numThreads, maxRefLen, maxQerLen)
+        if not self._h:
+            raise RuntimeError("kswv_create failed")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.kswv_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def getScores8(self, pairArray, seqBufRef, seqBufQer, aln, numPairs=None, numThreads=1, phase=0):
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.kswv_getScores8(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), _ptr(aln), n, numThreads, phase)
+
+    def getScores16(self, pairArray, seqBufRef, seqBufQer, aln, numPairs=None, numThreads=1, phase=0):
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.kswv_getScores16(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), _ptr(aln), n, numThreads, phase)
+
+    def dev_getScores(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, phase=0, stream=0):
+        self._L.kswv_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), _ptr(d_aln), numPairs,
+                                   int(is8), int(phase), C.c_void_p(stream))
+
+    def stats(self):
+        s = Stats()
+        self._L.kswv_get_stats(self._h, C.byref(s))
+        return s.asdict()
+
+    def reset_stats(self):
+        self._L.kswv_reset_stats(self._h)
+
+    def set_timing(self, on=True):
+        self._L.kswv_set_timing(self._h, int(on))
+
+
+def measure_dpx_peak(device=0, which=2):
+    return lib().bsw_measure_dpx_peak(device, which)
+
+
+def device_count():
+    return lib().bsw_device_count()

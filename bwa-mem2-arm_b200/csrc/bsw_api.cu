@@ -1,0 +1,529 @@
+/*
+ * bsw_api.cu -- extern "C" boundary of the B200 BSW / kswv path (include/bsw_cuda.h).
+ *
+ * Host side of the drop-in replacement for BandedPairWiseSW::getScores8/16 and
+ * kswv::getScores8/16 (bwa-mem2 src/bandedSWA.cpp, src/kswv.cpp; call sites in
+ * mem_chain2aln_across_reads_V2 / mem_sam_pe_batch, SURVEY.md sections 3, 8b).
+ * One handle per calling host thread (as the reference constructs one object
+ * per worker); a handle owns, per device, a stream, grow-only device scratch
+ * and a pinned mailbox.  No CPU fallback: any CUDA failure is fatal, as in the
+ * reference (fprintf + exit).
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <string>
+#include <algorithm>
+#include <cub/device/device_radix_sort.cuh>
+#include "bsw_kernels.cuh"
+
+using namespace bswk;
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            fprintf(stderr, "[bsw-b200] CUDA error %s at %s:%d: %s\n", cudaGetErrorName(e_),  \
+                    __FILE__, __LINE__, cudaGetErrorString(e_));                              \
+            exit(EXIT_FAILURE);                                                               \
+        }                                                                                     \
+    } while (0)
+
+static void die(const char *msg)
+{
+    fprintf(stderr, "[bsw-b200] fatal: %s\n", msg);
+    exit(EXIT_FAILURE);
+}
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr; size_t cap = 0;
+    void reserve(size_t bytes)
+    {
+        if (bytes <= cap) return;
+        if (p) CK(cudaFree(p));
+        size_t want = bytes + bytes / 4 + 256;
+        CK(cudaMalloc(&p, want)); cap = want;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct DevCtx {
+    int dev = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0, smem_optin = 0;
+    DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax, cells;
+    Plan *h_plan = nullptr;          /* pinned mailbox */
+};
+
+struct Core {
+    Const c;
+    std::vector<DevCtx> ctx;
+    bsw_stats_t st;
+    int timing = 0;
+    int smem_bytes = 0, block_warps = 16, blocks_per_sm = 1;
+    int mode = MODE_BSW;
+};
+
+int env_int(const char *name, int dflt)
+{
+    const char *s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+std::vector<int> pick_devices()
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) die("no CUDA device available (this library has no CPU fallback)");
+    std::vector<int> out;
+    const char *s = getenv("BSW_CUDA_DEVICES");
+    if (s && *s) {
+        std::string t(s); size_t p = 0;
+        while (p < t.size()) {
+            size_t q = t.find(',', p); if (q == std::string::npos) q = t.size();
+            int d = atoi(t.substr(p, q - p).c_str());
+            if (d < 0 || d >= n) die("BSW_CUDA_DEVICES names a device that does not exist");
+            out.push_back(d); p = q + 1;
+        }
+    }
+    if (out.empty()) {
+        const char *lr = getenv("LOCAL_RANK");
+        int d = (lr && *lr) ? atoi(lr) % n : 0;
+        out.push_back(d);
+    }
+    return out;
+}
+
+void core_init(Core &k, int mode)
+{
+    k.mode = mode;
+    memset(&k.st, 0, sizeof k.st);
+    k.timing = env_int("BSW_CUDA_TIMING", 0);
+    std::vector<int> devs = pick_devices();
+    k.ctx.resize(devs.size());
+    for (size_t i = 0; i < devs.size(); ++i) {
+        DevCtx &x = k.ctx[i];
+        x.dev = devs[i];
+        CK(cudaSetDevice(x.dev));
+        CK(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&x.ev0)); CK(cudaEventCreate(&x.ev1));
+        CK(cudaDeviceGetAttribute(&x.sm_count, cudaDevAttrMultiProcessorCount, x.dev));
+        CK(cudaDeviceGetAttribute(&x.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, x.dev));
+        CK(cudaHostAlloc((void **)&x.h_plan, sizeof(Plan), cudaHostAllocDefault));
+        x.plan.reserve(sizeof(Plan));
+        x.cells.reserve(sizeof(unsigned long long));
+        CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
+    }
+    /* launch shape of the packed kernels (DESIGN.md "occupancy"): blocks_per_sm persistent
+     * blocks share the SM's shared memory; block_warps bounds the warps of one tile. */
+    k.blocks_per_sm = std::max(1, env_int("BSW_CUDA_BLOCKS_PER_SM", 1));
+    k.block_warps = std::min(16, std::max(1, env_int("BSW_CUDA_BLOCK_WARPS", 16)));
+    int optin = k.ctx[0].smem_optin;                    /* 227 KB on sm_100 */
+    int per_block = (optin + 1024) / k.blocks_per_sm - 1024;
+    per_block = std::min(per_block, optin);
+    int kb = env_int("BSW_CUDA_SMEM_KB", 0);
+    if (kb > 0) per_block = std::min(per_block, kb * 1024);
+    k.smem_bytes = per_block & ~15;
+    for (DevCtx &x : k.ctx) {
+        CK(cudaSetDevice(x.dev));
+        CK(cudaFuncSetAttribute(bsw_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem_bytes));
+        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem_bytes));
+    }
+}
+
+void core_destroy(Core &k)
+{
+    for (DevCtx &x : k.ctx) {
+        cudaSetDevice(x.dev);
+        cudaStreamSynchronize(x.stream);
+        x.pairs.release(); x.ref.release(); x.qer.release(); x.aln.release();
+        x.keys_a.release(); x.keys_b.release(); x.idx_a.release(); x.idx_b.release();
+        x.cubtmp.release(); x.plan.release(); x.scratch.release(); x.rowmax.release(); x.cells.release();
+        if (x.h_plan) cudaFreeHost(x.h_plan);
+        cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
+        cudaStreamDestroy(x.stream);
+    }
+    k.ctx.clear();
+}
+
+Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus, int w_match, int w_mismatch)
+{
+    Const c;
+    if (e_del <= 0 || e_ins <= 0) die("gap extension penalties must be positive");
+    if (w_match <= 0) die("w_match must be positive");
+    c.o_del = o_del; c.e_del = e_del; c.o_ins = o_ins; c.e_ins = e_ins;
+    c.oe_del = o_del + e_del; c.oe_ins = o_ins + e_ins;
+    c.zdrop = zdrop; c.end_bonus = end_bonus;
+    c.a = w_match; c.b = w_mismatch < 0 ? -w_mismatch : w_mismatch;   /* upstream passes +b, the fork -b */
+    c.ambig = -1;                                                      /* bandedSWA.h DEFAULT_AMBIG */
+    c.maxsc = w_match;
+    return c;
+}
+
+/* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
+const Plan *run_plan(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+{
+    x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
+    x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp_bytes, (uint32_t *)nullptr, (uint32_t *)nullptr,
+                                                 (uint32_t *)nullptr, (uint32_t *)nullptr, n, 0, 25, s));
+    x.cubtmp.reserve(tmp_bytes);
+    Plan *d_plan = (Plan *)x.plan.p;
+    CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));
+    const int max_elems = std::min(BSW_NBINS * 16, k.smem_bytes / BSW_WARP_ELEM_BYTES / 16 * 16);
+    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, n, k.c, k.mode, max_elems, tier8_check,
+                                                 (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
+    CK(cudaGetLastError());
+    CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
+                                                 (uint32_t *)x.idx_a.p, (uint32_t *)x.idx_b.p, n, 0, 25, s));
+    plan_kernel<<<1, 32, 0, s>>>(d_plan, k.smem_bytes, k.block_warps);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(x.h_plan, d_plan, sizeof(Plan), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    k.st.kernel_launches += 2 + 8;    /* prep + plan + the sort's internal launches (upper bound of cub's onesweep path) */
+    if (x.h_plan->bad_pairs) {
+        fprintf(stderr, "[bsw-b200] fatal: %d pair(s) violate the call contract (negative length, h0 <= 0, or "
+                        ">= %d bases in getScores8)\n", x.h_plan->bad_pairs, BSW_MAX_SEQ_LEN8);
+        exit(EXIT_FAILURE);
+    }
+    return x.h_plan;
+}
+
+void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                int n, int w, cudaStream_t s, int tier8_check)
+{
+    if (n <= 0) return;
+    const Plan *pl = run_plan(k, x, d_pairs, n, s, tier8_check);
+    Plan *d_plan = (Plan *)x.plan.p;
+    const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
+    if (k.timing) CK(cudaEventRecord(x.ev0, s));
+    if (pl->ntiles > 0) {
+        int grid = std::min(pl->ntiles, x.sm_count * k.blocks_per_sm);
+        bsw_packed_kernel<<<grid, k.block_warps * 32, k.smem_bytes, s>>>(d_pairs, d_ref, d_qer, sorted, d_plan, k.c, w,
+                                                                          (unsigned long long *)x.cells.p);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+    }
+    if (pl->n_general > 0) {
+        /* bounded scratch: at most ~1 GiB of eh rows per launch */
+        const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2);
+        int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));
+        x.scratch.reserve((size_t)chunk * per_pair);
+        for (int first = 0; first < pl->n_general; first += chunk) {
+            int cnt = std::min(chunk, pl->n_general - first);
+            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, sorted, pl->n_packed + first, cnt,
+                                                              k.c, w, (int2 *)x.scratch.p, (unsigned long long *)x.cells.p);
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+        }
+    }
+    if (k.timing) {
+        CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
+    }
+    k.st.pairs += n; k.st.pairs_packed += pl->n_packed; k.st.pairs_general += pl->n_general;
+}
+
+void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                 bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
+{
+    if (n <= 0) return;
+    const Plan *pl = run_plan(k, x, d_pairs, n, s, 0);
+    Plan *d_plan = (Plan *)x.plan.p;
+    const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
+    if (k.timing) CK(cudaEventRecord(x.ev0, s));
+    if (pl->ntiles > 0) {
+        const long long stride = pl->n_packed;
+        x.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
+        int grid = std::min(pl->ntiles, x.sm_count * k.blocks_per_sm);
+        kswv_packed_kernel<<<grid, k.block_warps * 32, k.smem_bytes, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, d_plan,
+                                                                         k.c, is8, phase, (uint16_t *)x.rowmax.p, stride,
+                                                                         (unsigned long long *)x.cells.p);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+    }
+    if (pl->n_general > 0) {
+        const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
+        int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));
+        x.scratch.reserve((size_t)chunk * per_pair);
+        int2 *he = (int2 *)x.scratch.p;
+        int *rm = (int *)((char *)x.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
+        for (int first = 0; first < pl->n_general; first += chunk) {
+            int cnt = std::min(chunk, pl->n_general - first);
+            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, pl->n_packed + first, cnt,
+                                                               k.c, is8, phase, he, rm, (unsigned long long *)x.cells.p);
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+        }
+    }
+    if (k.timing) {
+        CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
+    }
+    k.st.pairs += n; k.st.pairs_packed += pl->n_packed; k.st.pairs_general += pl->n_general;
+}
+
+/* byte extents [lo, hi) of the sequence buffers touched by pairs[first, first+cnt) */
+void extents(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long long &rhi, long long &qlo, long long &qhi)
+{
+    rlo = qlo = (long long)1 << 62; rhi = qhi = 0;
+    for (int i = first; i < first + cnt; ++i) {
+        long long a = p[i].idr, b = a + std::max(p[i].len1, 0), c = p[i].idq, d = c + std::max(p[i].len2, 0);
+        rlo = std::min(rlo, a); rhi = std::max(rhi, b); qlo = std::min(qlo, c); qhi = std::max(qhi, d);
+    }
+    if (rhi <= rlo) { rlo = 0; rhi = 0; }
+    if (qhi <= qlo) { qlo = 0; qhi = 0; }
+}
+
+/* host-pointer call: shard, copy in, compute, copy out.  Synchronous. */
+void host_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
+               int n, int w, int is8, int phase, int tier8_check)
+{
+    k.st.calls++;
+    if (n <= 0) return;
+    if (!pairs || !ref || !qer) die("null buffer passed to getScores");
+    const int nd = (int)k.ctx.size();
+    struct Slice { int first, cnt; long long rlo, rhi, qlo, qhi; };
+    std::vector<Slice> sl(nd);
+    for (int d = 0; d < nd; ++d) {
+        sl[d].first = (int)((long long)n * d / nd);
+        sl[d].cnt = (int)((long long)n * (d + 1) / nd) - sl[d].first;
+        if (sl[d].cnt > 0) extents(pairs, sl[d].first, sl[d].cnt, sl[d].rlo, sl[d].rhi, sl[d].qlo, sl[d].qhi);
+    }
+    /* kswv phase 1 refines aln[regid]: regid may point anywhere in aln, so every device gets the
+     * entries its slice names (we send the span [min regid, max regid]). */
+    std::vector<std::pair<int, int>> aspan(nd, {0, 0});
+    for (int d = 0; d < nd; ++d) {
+        DevCtx &x = k.ctx[d];
+        const Slice &s = sl[d];
+        if (s.cnt <= 0) continue;
+        CK(cudaSetDevice(x.dev));
+        x.pairs.reserve((size_t)s.cnt * sizeof(bsw_seqpair_t));
+        x.ref.reserve((size_t)(s.rhi - s.rlo) + 16);
+        x.qer.reserve((size_t)(s.qhi - s.qlo) + 16);
+        CK(cudaMemcpyAsync(x.pairs.p, pairs + s.first, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, x.stream));
+        if (s.rhi > s.rlo) CK(cudaMemcpyAsync(x.ref.p, ref + s.rlo, (size_t)(s.rhi - s.rlo), cudaMemcpyHostToDevice, x.stream));
+        if (s.qhi > s.qlo) CK(cudaMemcpyAsync(x.qer.p, qer + s.qlo, (size_t)(s.qhi - s.qlo), cudaMemcpyHostToDevice, x.stream));
+        k.st.h2d_bytes += (int64_t)s.cnt * sizeof(bsw_seqpair_t) + (s.rhi - s.rlo) + (s.qhi - s.qlo);
+        if (k.mode == MODE_KSWV) {
+            if (!aln) die("null aln passed to kswv getScores");
+            if (phase == 0) { aspan[d] = { s.first, s.first + s.cnt }; x.aln.reserve((size_t)s.cnt * sizeof(bsw_kswr_t)); }
+            else {
+                int lo = 0x7fffffff, hi = -1;
+                for (int i = s.first; i < s.first + s.cnt; ++i) { lo = std::min(lo, pairs[i].regid); hi = std::max(hi, pairs[i].regid); }
+                if (lo < 0) die("kswv phase 1: negative regid");
+                aspan[d] = { lo, hi + 1 };
+                x.aln.reserve((size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t));
+                CK(cudaMemcpyAsync(x.aln.p, aln + lo, (size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t), cudaMemcpyHostToDevice, x.stream));
+                k.st.h2d_bytes += (int64_t)(hi + 1 - lo) * sizeof(bsw_kswr_t);
+            }
+        }
+    }
+    for (int d = 0; d < nd; ++d) {
+        DevCtx &x = k.ctx[d];
+        const Slice &s = sl[d];
+        if (s.cnt <= 0) continue;
+        CK(cudaSetDevice(x.dev));
+        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
+        const uint8_t *d_ref = (const uint8_t *)x.ref.p - s.rlo;
+        const uint8_t *d_qer = (const uint8_t *)x.qer.p - s.qlo;
+        if (k.mode == MODE_BSW) {
+            launch_bsw(k, x, (bsw_seqpair_t *)x.pairs.p, d_ref, d_qer, s.cnt, w, x.stream, tier8_check);
+            CK(cudaMemcpyAsync(pairs + s.first, x.pairs.p, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, x.stream));
+            k.st.d2h_bytes += (int64_t)s.cnt * sizeof(bsw_seqpair_t);
+        } else {
+            /* phase 0 indexes aln by slice-local pair index; phase 1 by regid, rebased to the span */
+            bsw_kswr_t *d_aln = (bsw_kswr_t *)x.aln.p - (phase == 0 ? 0 : aspan[d].first);
+            launch_kswv(k, x, (const bsw_seqpair_t *)x.pairs.p, d_ref, d_qer, d_aln, s.cnt, is8, phase, x.stream);
+            size_t cnt = (size_t)(aspan[d].second - aspan[d].first);
+            if (phase == 0) {
+                CK(cudaMemcpyAsync(aln + aspan[d].first, x.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, x.stream));
+            } else {
+                /* only tb/qb of the named entries change; copy back through a bounce so other devices'
+                 * entries inside the span are not clobbered */
+                std::vector<bsw_kswr_t> tmp(cnt);
+                CK(cudaMemcpyAsync(tmp.data(), x.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, x.stream));
+                CK(cudaStreamSynchronize(x.stream));
+                for (int i = s.first; i < s.first + s.cnt; ++i) {
+                    int r = pairs[i].regid;
+                    aln[r].tb = tmp[r - aspan[d].first].tb; aln[r].qb = tmp[r - aspan[d].first].qb;
+                }
+            }
+            k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_kswr_t);
+        }
+    }
+    for (int d = 0; d < nd; ++d) {
+        if (sl[d].cnt <= 0) continue;
+        CK(cudaSetDevice(k.ctx[d].dev));
+        CK(cudaStreamSynchronize(k.ctx[d].stream));
+    }
+}
+
+} /* namespace */
+
+struct bsw_handle  { Core k; };
+struct kswv_handle { Core k; int32_t maxRefLen, maxQerLen; };
+
+extern "C" {
+
+const char *bsw_version(void) { return "bsw-b200 0.1 (sm_100a, packed s16x2 DPX)"; }
+
+int bsw_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+bsw_t *bsw_create(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
+                  const int8_t *mat, int8_t w_match, int8_t w_mismatch, int numThreads)
+{
+    (void)mat; (void)numThreads;
+    bsw_t *h = new bsw_handle();
+    h->k.c = make_const(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, w_match, w_mismatch);
+    core_init(h->k, MODE_BSW);
+    return h;
+}
+
+void bsw_destroy(bsw_t *h) { if (!h) return; core_destroy(h->k); delete h; }
+
+void bsw_getScores8(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                    int32_t numPairs, uint16_t numThreads, int32_t w)
+{
+    (void)numThreads;
+    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 1);
+}
+
+void bsw_getScores16(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                     int32_t numPairs, uint16_t numThreads, int32_t w)
+{
+    (void)numThreads;
+    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 0);
+}
+
+void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                                int32_t numPairs, int nthreads, int32_t w)
+{
+    (void)nthreads;
+    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 0);
+}
+
+void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                       int32_t numPairs, int32_t w, void *stream)
+{
+    DevCtx &x = h->k.ctx[0];
+    CK(cudaSetDevice(x.dev));
+    h->k.st.calls++;
+    launch_bsw(h->k, x, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
+}
+
+kswv_t *kswv_create(int o_del, int e_del, int o_ins, int e_ins, int8_t w_match, int8_t w_mismatch,
+                    int numThreads, int32_t maxRefLen, int32_t maxQerLen)
+{
+    (void)numThreads;
+    kswv_t *h = new kswv_handle();
+    h->k.c = make_const(o_del, e_del, o_ins, e_ins, 0, 0, w_match, w_mismatch);
+    h->maxRefLen = maxRefLen; h->maxQerLen = maxQerLen;
+    core_init(h->k, MODE_KSWV);
+    return h;
+}
+
+void kswv_destroy(kswv_t *h) { if (!h) return; core_destroy(h->k); delete h; }
+
+void kswv_getScores8(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                     bsw_kswr_t *aln, int32_t numPairs, uint16_t numThreads, int phase)
+{
+    (void)numThreads;
+    host_call(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 0, 1, phase, 0);
+}
+
+void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                      bsw_kswr_t *aln, int32_t numPairs, uint16_t numThreads, int phase)
+{
+    (void)numThreads;
+    host_call(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 0, 0, phase, 0);
+}
+
+void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                        bsw_kswr_t *d_aln, int32_t numPairs, int is8, int phase, void *stream)
+{
+    DevCtx &x = h->k.ctx[0];
+    CK(cudaSetDevice(x.dev));
+    h->k.st.calls++;
+    launch_kswv(h->k, x, d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase, (cudaStream_t)stream);
+}
+
+void *bsw_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    CK(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable));
+    return p;
+}
+void bsw_host_free(void *p) { if (p) CK(cudaFreeHost(p)); }
+
+static void stats_with_pending(Core &k, bsw_stats_t *out)
+{
+    long long cells = 0;
+    for (DevCtx &x : k.ctx) {
+        CK(cudaSetDevice(x.dev));
+        CK(cudaDeviceSynchronize());
+        unsigned long long c = 0;
+        CK(cudaMemcpy(&c, x.cells.p, sizeof c, cudaMemcpyDeviceToHost));
+        cells += (long long)c;
+    }
+    k.st.cells = cells;
+    *out = k.st;
+}
+static void stats_reset(Core &k)
+{
+    memset(&k.st, 0, sizeof k.st);
+    for (DevCtx &x : k.ctx) {
+        CK(cudaSetDevice(x.dev));
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
+    }
+}
+
+void bsw_get_stats(bsw_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
+void bsw_reset_stats(bsw_t *h) { stats_reset(h->k); }
+void bsw_set_timing(bsw_t *h, int on) { h->k.timing = on; }
+void kswv_get_stats(kswv_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
+void kswv_reset_stats(kswv_t *h) { stats_reset(h->k); }
+void kswv_set_timing(kswv_t *h, int on) { h->k.timing = on; }
+
+double bsw_measure_dpx_peak(int device, int which)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return 0.0;
+    CK(cudaSetDevice(device));
+    int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int threads = 1024, blocks = sms * 2, iters = 4096;
+    uint32_t *out = nullptr; CK(cudaMalloc(&out, (size_t)threads * blocks * 4));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        CK(cudaEventRecord(e0));
+        switch (which) {
+        case 0: dpx_peak_kernel<0><<<blocks, threads>>>(out, iters, 12345u + rep); break;
+        case 1: dpx_peak_kernel<1><<<blocks, threads>>>(out, iters, 12345u + rep); break;
+        case 2: dpx_peak_kernel<2><<<blocks, threads>>>(out, iters, 12345u + rep); break;
+        case 3: dpx_peak_kernel<3><<<blocks, threads>>>(out, iters, 12345u + rep); break;
+        default: dpx_peak_kernel<4><<<blocks, threads>>>(out, iters, 12345u + rep); break;
+        }
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+        /* thread-level instruction count: 64 per iteration (8 chains x 8 unrolled); WHICH==3 issues 2 per step */
+        double instr = (double)threads * blocks * iters * 64.0 * (which == 3 ? 2.0 : 1.0);
+        if (rep > 0) best = std::max(best, instr / (ms * 1e-3));
+    }
+    CK(cudaEventDestroy(e0)); CK(cudaEventDestroy(e1)); CK(cudaFree(out));
+    return best;
+}
+
+} /* extern "C" */

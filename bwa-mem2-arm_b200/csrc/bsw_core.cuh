@@ -28,8 +28,10 @@
 
 #if defined(__CUDACC__)
 #define BSW_HD __host__ __device__ __forceinline__
+#define BSW_HDM __host__ __device__ __forceinline__
 #else
 #define BSW_HD static inline
+#define BSW_HDM inline
 struct uint2 { uint32_t x, y; };
 static inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 r; r.x = x; r.y = y; return r; }
 struct int2 { int32_t x, y; };
@@ -58,6 +60,9 @@ __device__ __forceinline__ uint32_t p_addmax_relu(uint32_t a, uint32_t b, uint32
 __device__ __forceinline__ uint32_t p_add(uint32_t a, uint32_t b)                { return __vadd2(a, b); }
 __device__ __forceinline__ uint32_t p_maxu(uint32_t a, uint32_t b)               { return __vmaxu2(a, b); }
 __device__ __forceinline__ uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)   { return __byte_perm(a, b, s); }
+/* LUT index of both lanes in ONE LOP3: (q ^ t) | ((q | t) & 0x4444), truth table 0xBC */
+__device__ __forceinline__ uint32_t p_xsel(uint32_t q, uint32_t t)
+{ uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xBC;" : "=r"(r) : "r"(q), "r"(t), "r"(0x4444u)); return r; }
 #else
 static inline int16_t lo16(uint32_t v) { return (int16_t)(v & 0xffff); }
 static inline int16_t hi16(uint32_t v) { return (int16_t)(v >> 16); }
@@ -73,6 +78,7 @@ static inline uint32_t p_addmax_relu(uint32_t a, uint32_t b, uint32_t c)
 static inline uint32_t p_add(uint32_t a, uint32_t b) { return pk(lo16(a) + lo16(b), hi16(a) + hi16(b)); }
 static inline uint32_t p_maxu(uint32_t a, uint32_t b)
 { uint32_t l = (a & 0xffff) > (b & 0xffff) ? (a & 0xffff) : (b & 0xffff), h = (a >> 16) > (b >> 16) ? (a >> 16) : (b >> 16); return l | (h << 16); }
+static inline uint32_t p_xsel(uint32_t q, uint32_t t) { return (q ^ t) | ((q | t) & 0x4444u); }
 static inline uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)
 {
     uint64_t v = ((uint64_t)b << 32) | a; uint32_t r = 0;
@@ -221,7 +227,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                                 ((j_ >= rb[1] && j_ < re[1]) ? 0xffff0000u : 0u);       \
             uint2 v = he[j_ * S];                                                       \
             uint32_t q_ = qs[j_ * S];                                                   \
-            uint32_t x_ = (q_ ^ T) | ((q_ | T) & 0x4444u);                              \
+            uint32_t x_ = p_xsel(q_, T);                              \
             uint32_t s_ = p_perm(LUTLO, LUTHI, x_);                                     \
             uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);                                 \
             uint32_t h_ = p_max3(M_, v.y, f);                                           \
@@ -247,7 +253,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             for (int k = 0; k < nb; ++k) {
                 uint2 v = hp[k * S];
                 uint32_t q_ = qp[k * S];
-                uint32_t x_ = (q_ ^ T) | ((q_ | T) & 0x4444u);
+                uint32_t x_ = p_xsel(q_, T);
                 uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
                 uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);
                 uint32_t h_ = p_max3(M_, v.y, f);

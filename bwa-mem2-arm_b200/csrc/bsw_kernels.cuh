@@ -1,0 +1,293 @@
+/*
+ * bsw_kernels.cuh -- __global__ kernels of the BSW / kswv path (sm_100a).
+ *
+ * Launch sequence of one boundary call (all on one stream, DESIGN.md "Pipeline"):
+ *   1. prep_kernel      one thread per pair: admissibility for the packed kernel,
+ *                       radix key (query length major, target length minor),
+ *                       per-bin histogram (bin = 16 query columns).
+ *   2. cub radix sort   descending: longest queries first (heavy tiles first),
+ *                       pairs the packed kernel does not admit last (key 0).
+ *   3. plan_kernel      bin offsets -> tile table.  A tile = W warps x 64 pairs of
+ *                       one bin; W = how many warps' DP rows fit the block's
+ *                       shared memory at that query length.
+ *   4. *_packed_kernel  persistent blocks pull tiles from an atomic counter.
+ *   5. *_general_kernel 32-bit path for the (rare) pairs step 1 did not admit.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/bsw_cuda.h"
+#include "bsw_core.cuh"
+#include "kswv_core.cuh"
+
+namespace bswk {
+
+#define BSW_NBINS 16            /* bins of 16 elements: up to 256 elements per thread */
+#define BSW_WARP_ELEM_BYTES 320 /* per element per warp: 32 x (uint2 + uint16)        */
+
+struct Plan {
+    int hist[BSW_NBINS + 2];       /* [qb] = packed-admissible pairs with ceil((len2+1)/16) == qb */
+    int n_general;                 /* pairs routed to the general kernel */
+    int max_len1;                  /* over all pairs                      */
+    int max_len2_general;
+    int bad_pairs;                 /* contract violations seen by prep    */
+    int bin_start[BSW_NBINS + 2];  /* sorted position where bin qb starts (descending qb) */
+    int bin_warps[BSW_NBINS + 2];
+    int tile_prefix[BSW_NBINS + 2];/* tiles before bin qb (descending order) */
+    int ntiles, n_packed;
+    unsigned int tile_counter;
+    unsigned int pad_;
+};
+
+enum { MODE_BSW = 0, MODE_KSWV = 1 };
+
+/* ------------------------------------------------------------------ 1. prep */
+__global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Const c, int mode,
+                            int max_elems, int tier8_check,
+                            uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, Plan *plan)
+{
+    __shared__ int s_hist[BSW_NBINS + 2];
+    __shared__ int s_misc[4];
+    if (threadIdx.x < BSW_NBINS + 2) s_hist[threadIdx.x] = 0;
+    if (threadIdx.x < 4) s_misc[threadIdx.x] = 0;
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const int len1 = pairs[i].len1, len2 = pairs[i].len2, h0 = pairs[i].h0;
+        bool ok = (mode == MODE_BSW) ? packed_eligible(c, len1, len2, h0) : kswv_packed_eligible(c, len1, len2);
+        const int qb = (len2 + 1 + 15) >> 4;
+        if (ok && qb * 16 > max_elems) ok = false;
+        uint32_t key = 0;
+        if (ok) {
+            key = ((uint32_t)(len2 + 1) << 16) | (uint32_t)(len1 > 0xffff ? 0xffff : len1);
+            atomicAdd(&s_hist[qb], 1);
+        } else {
+            atomicAdd(&s_misc[0], 1);
+            atomicMax(&s_misc[2], len2);
+        }
+        atomicMax(&s_misc[1], len1);
+        bool bad = len1 < 0 || len2 < 0 || (mode == MODE_BSW && h0 <= 0);
+        if (tier8_check && (len1 >= BSW_MAX_SEQ_LEN8 || len2 >= BSW_MAX_SEQ_LEN8)) bad = true;
+        if (bad) atomicAdd(&s_misc[3], 1);
+        keys[i] = key; idx[i] = (uint32_t)i;
+    }
+    __syncthreads();
+    if (threadIdx.x < BSW_NBINS + 2 && s_hist[threadIdx.x]) atomicAdd(&plan->hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (threadIdx.x == 0) {
+        if (s_misc[0]) atomicAdd(&plan->n_general, s_misc[0]);
+        atomicMax(&plan->max_len1, s_misc[1]);
+        atomicMax(&plan->max_len2_general, s_misc[2]);
+        if (s_misc[3]) atomicAdd(&plan->bad_pairs, s_misc[3]);
+    }
+}
+
+/* ------------------------------------------------------------------ 3. plan */
+__global__ void plan_kernel(Plan *plan, int smem_bytes, int block_warps)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int pos = 0, tiles = 0;
+    for (int qb = BSW_NBINS; qb >= 1; --qb) {
+        const int cnt = plan->hist[qb];
+        int w = smem_bytes / (qb * 16 * BSW_WARP_ELEM_BYTES);
+        w = w > block_warps ? block_warps : w;
+        w = w < 1 ? 1 : w;                       /* prep guarantees qb*16 <= max_elems, so w >= 1 */
+        plan->bin_start[qb] = pos;
+        plan->bin_warps[qb] = w;
+        plan->tile_prefix[qb] = tiles;
+        pos += cnt;
+        tiles += (cnt + 64 * w - 1) / (64 * w);
+    }
+    plan->bin_start[0] = pos; plan->tile_prefix[0] = tiles;
+    plan->ntiles = tiles; plan->n_packed = pos;
+}
+
+/* tile -> (qb, first sorted slot, end slot of bin, warps) */
+__device__ __forceinline__ bool tile_lookup(const Plan *plan, int tile, int &qb, int &base, int &bin_end, int &W)
+{
+    if (tile >= plan->ntiles) return false;
+    qb = BSW_NBINS;
+    while (qb > 1 && tile >= plan->tile_prefix[qb - 1]) --qb;
+    W = plan->bin_warps[qb];
+    base = plan->bin_start[qb] + (tile - plan->tile_prefix[qb]) * 64 * W;
+    bin_end = plan->bin_start[qb - 1];
+    return true;
+}
+
+__device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pairs, int pi)
+{
+    PairIn p;
+    if (pi < 0) { p.idr = p.idq = p.len1 = p.len2 = p.h0 = 0; p.valid = 0; return p; }
+    p.idr = pairs[pi].idr; p.idq = pairs[pi].idq; p.len1 = pairs[pi].len1; p.len2 = pairs[pi].len2;
+    p.h0 = pairs[pi].h0; p.valid = 1;
+    return p;
+}
+
+/* ------------------------------------------------------------------ 4a. BSW packed */
+__global__ void __launch_bounds__(512, 1)
+bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+                  const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
+                  Plan *plan, Const c, int w, unsigned long long *cells)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int s_tile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned long long my_cells = 0;
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = (int)atomicAdd(&plan->tile_counter, 1u);
+        __syncthreads();
+        const int tile = s_tile;
+        __syncthreads();
+        int qb, base, bin_end, W;
+        if (!tile_lookup(plan, tile, qb, base, bin_end, W)) break;
+        if (warp < W) {
+            const int NE = qb * 16;
+            uint8_t *region = smem + (size_t)warp * NE * BSW_WARP_ELEM_BYTES;
+            uint2 *he = reinterpret_cast<uint2 *>(region) + lane;
+            uint16_t *qs = reinterpret_cast<uint16_t *>(region + (size_t)NE * 256) + lane;
+            const int slot = base + warp * 64 + lane * 2;
+            const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
+            const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
+            if (pa >= 0) {
+                PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+                PairOut oa, ob;
+                bsw_packed_thread<32>(c, w, A, B, ref, qer, he, qs, oa, ob);
+                int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
+                o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
+                my_cells += (unsigned long long)oa.cells;
+                if (pb >= 0) {
+                    o = reinterpret_cast<int2 *>(&pairs[pb].score);
+                    o[0] = make_int2(ob.score, ob.tle); o[1] = make_int2(ob.gtle, ob.qle); o[2] = make_int2(ob.gscore, ob.max_off);
+                    my_cells += (unsigned long long)ob.cells;
+                }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+/* ------------------------------------------------------------------ 5a. BSW general */
+__global__ void bsw_general_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+                                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
+                                   int first, int count, Const c, int w, int2 *eh, unsigned long long *cells)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long my_cells = 0;
+    if (g < count) {
+        const int pi = (int)sorted_idx[first + g];
+        PairIn P = load_pair(pairs, pi);
+        PairOut o;
+        bsw_general_thread<long long>(c, w, P, ref, qer, eh + g, (long long)count, o);
+        pairs[pi].score = o.score; pairs[pi].tle = o.tle; pairs[pi].gtle = o.gtle; pairs[pi].qle = o.qle;
+        pairs[pi].gscore = o.gscore; pairs[pi].max_off = o.max_off;
+        my_cells = (unsigned long long)o.cells;
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if ((threadIdx.x & 31) == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+/* ------------------------------------------------------------------ kswv result write-back */
+__device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const bsw_seqpair_t *__restrict__ pairs,
+                                           int pi, const KswOut &o, int phase)
+{
+    if (phase == 0) {
+        bsw_kswr_t r; r.score = o.score; r.te = o.te; r.qe = o.qe; r.score2 = o.score2; r.te2 = o.te2; r.tb = -1; r.qb = -1;
+        aln[pi] = r;
+    } else {
+        bsw_kswr_t *a = &aln[pairs[pi].regid];
+        if (a->score == o.score) { a->tb = a->te - o.te; a->qb = a->qe - o.qe; }
+    }
+}
+
+/* ------------------------------------------------------------------ 4b. kswv packed */
+__global__ void __launch_bounds__(512, 1)
+kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+                   const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
+                   const uint32_t *__restrict__ sorted_idx, Plan *plan, Const c, int is8, int phase,
+                   uint16_t *rowmax, long long rm_stride, unsigned long long *cells)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int s_tile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned long long my_cells = 0;
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = (int)atomicAdd(&plan->tile_counter, 1u);
+        __syncthreads();
+        const int tile = s_tile;
+        __syncthreads();
+        int qb, base, bin_end, W;
+        if (!tile_lookup(plan, tile, qb, base, bin_end, W)) break;
+        if (warp < W) {
+            const int NE = qb * 16;
+            uint8_t *region = smem + (size_t)warp * NE * BSW_WARP_ELEM_BYTES;
+            uint2 *he = reinterpret_cast<uint2 *>(region) + lane;
+            uint16_t *qs = reinterpret_cast<uint16_t *>(region + (size_t)NE * 256) + lane;
+            const int slot = base + warp * 64 + lane * 2;
+            const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
+            const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
+            if (pa >= 0) {
+                PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+                KswOut oa, ob;
+                kswv_packed_thread<32>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
+                kswv_store(aln, pairs, pa, oa, phase);
+                my_cells += (unsigned long long)oa.cells;
+                if (pb >= 0) { kswv_store(aln, pairs, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+/* ------------------------------------------------------------------ 5b. kswv general */
+__global__ void kswv_general_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+                                    const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
+                                    const uint32_t *__restrict__ sorted_idx, int first, int count,
+                                    Const c, int is8, int phase, int2 *he, int *rm, unsigned long long *cells)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long my_cells = 0;
+    if (g < count) {
+        const int pi = (int)sorted_idx[first + g];
+        PairIn P = load_pair(pairs, pi);
+        KswOut o;
+        kswv_general_thread<long long>(c, is8, P, ref, qer, he + g, (long long)count, rm + g, (long long)count, o);
+        kswv_store(aln, pairs, pi, o, phase);
+        my_cells = (unsigned long long)o.cells;
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if ((threadIdx.x & 31) == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+/* ------------------------------------------------------------------ DPX issue-rate microbenchmark */
+template <int WHICH>
+__global__ void dpx_peak_kernel(uint32_t *out, int iters, uint32_t seed)
+{
+    uint32_t a0 = seed + threadIdx.x, a1 = a0 * 3u, a2 = a0 * 5u, a3 = a0 * 7u,
+             a4 = a0 * 11u, a5 = a0 * 13u, a6 = a0 * 17u, a7 = a0 * 19u;
+    const uint32_t k1 = seed ^ 0x00030005u, k2 = seed ^ 0x00010002u;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (WHICH == 0) {
+                a0 = __vimax3_s16x2(a0, k1, k2); a1 = __vimax3_s16x2(a1, k1, k2); a2 = __vimax3_s16x2(a2, k1, k2); a3 = __vimax3_s16x2(a3, k1, k2);
+                a4 = __vimax3_s16x2(a4, k1, k2); a5 = __vimax3_s16x2(a5, k1, k2); a6 = __vimax3_s16x2(a6, k1, k2); a7 = __vimax3_s16x2(a7, k1, k2);
+            } else if (WHICH == 1) {
+                a0 = __viaddmax_s16x2(a0, k1, k2); a1 = __viaddmax_s16x2(a1, k1, k2); a2 = __viaddmax_s16x2(a2, k1, k2); a3 = __viaddmax_s16x2(a3, k1, k2);
+                a4 = __viaddmax_s16x2(a4, k1, k2); a5 = __viaddmax_s16x2(a5, k1, k2); a6 = __viaddmax_s16x2(a6, k1, k2); a7 = __viaddmax_s16x2(a7, k1, k2);
+            } else if (WHICH == 2) {
+                a0 = __vimax3_s16x2(a0, k1, k2); a1 = __viaddmax_s16x2_relu(a1, k1, k2); a2 = __viaddmin_s16x2(a2, k1, k2); a3 = __vimax3_s16x2(a3, k1, k2);
+                a4 = __viaddmax_s16x2_relu(a4, k1, k2); a5 = __viaddmin_s16x2(a5, k1, k2); a6 = __vimax3_s16x2(a6, k1, k2); a7 = __viaddmax_s16x2_relu(a7, k1, k2);
+            } else if (WHICH == 3) {   /* plain 32-bit integer add/logic on the same pipe, for comparison */
+                a0 = (a0 ^ k1) + k2; a1 = (a1 ^ k1) + k2; a2 = (a2 ^ k1) + k2; a3 = (a3 ^ k1) + k2;
+                a4 = (a4 ^ k1) + k2; a5 = (a5 ^ k1) + k2; a6 = (a6 ^ k1) + k2; a7 = (a7 ^ k1) + k2;
+            } else {                   /* VIADD.16x2 */
+                a0 = __vadd2(a0, k1); a1 = __vadd2(a1, k1); a2 = __vadd2(a2, k1); a3 = __vadd2(a3, k1);
+                a4 = __vadd2(a4, k1); a5 = __vadd2(a5, k1); a6 = __vadd2(a6, k1); a7 = __vadd2(a7, k1);
+            }
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+}
+
+} /* namespace bswk */

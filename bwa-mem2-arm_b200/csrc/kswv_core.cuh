@@ -1,0 +1,237 @@
+/*
+ * kswv_core.cuh -- per-thread dynamic programming of the batched mate-rescue
+ * local alignment (kswv::getScores8/16, bwa-mem2 src/kswv.cpp; semantics = bwa
+ * ksw_u8 / ksw_i16 evaluated in exact arithmetic).
+ *
+ * Same mapping as bsw_core.cuh: one thread owns two pairs in the two 16-bit
+ * lanes of each register and sweeps full rows (no band):
+ *     h  = max(Hd + s, e, f, 0)              VIADD.16x2 + VIMNMX3.S16x2.RELU
+ *     e' = max(h - oe_del, e - e_del, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
+ *     f' = max(h - oe_ins, f - e_ins, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
+ *     (imax, qe) = max over (h << 8 | 255-j) IMAD + VIMNMX.U16x2 (ties -> smallest j)
+ * Per-row maxima go to a [row][thread] scratch in HBM (coalesced 2-byte
+ * stores); the second-best scan of ksw_u8 (the `b` list) is replayed from it
+ * once te and score are final.
+ */
+#pragma once
+#include "bsw_core.cuh"
+
+namespace bswk {
+
+#define KSW_XBYTE_  0x10000
+#define KSW_XSTOP_  0x20000
+#define KSW_XSUBO_  0x40000
+#define KSW_XSTART_ 0x80000
+
+struct KswOut { int score, te, qe, score2, te2; long long cells; };
+
+BSW_HD bool kswv_packed_eligible(const Const &c, int len1, int len2)
+{
+    if (len1 < 0 || len2 < 0 || len2 > BSW_PACKED_MAX_QLEN) return false;
+    return (long long)mn(len1, len2) * c.a <= BSW_PACKED_MAX_SCORE;
+}
+
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ uint32_t p_max3_relu(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2_relu(a, b, c); }
+#else
+static inline uint32_t p_max3_relu(uint32_t a, uint32_t b, uint32_t c)
+{ return pk(imax(imax(imax(lo16(a), lo16(b)), lo16(c)), 0), imax(imax(imax(hi16(a), hi16(b)), hi16(c)), 0)); }
+#endif
+
+/* replay of ksw_u8's b-list rule over the stored row maxima (A.2) */
+struct BList {
+    int n, sc, row, low, high, score2, te2;
+    BSW_HDM void init(int lo, int hi) { n = 0; sc = 0; row = 0; low = lo; high = hi; score2 = -1; te2 = -1; }
+    BSW_HDM void flush() { if (n && (row < low || row > high) && sc > score2) { score2 = sc; te2 = row; } }
+    BSW_HDM void push(int imax, int i)
+    {
+        if (n == 0 || row + 1 != i) { flush(); n = 1; sc = imax; row = i; }
+        else if (sc < imax) { sc = imax; row = i; }
+    }
+};
+
+struct KState {
+    int qlen, tlen, idr, minsc, endsc, gmax, te, qe, rows, act;
+};
+
+/*
+ * he[j*S] = { H(i-1, j) packed, E(i, j) packed }, qs[j*S] = selector,
+ * rm[i*RS] = imaxA | imaxB << 8 (this thread's slot of the row-max scratch).
+ */
+template <int S>
+BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const PairIn &B,
+                               const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                               uint2 *he, uint16_t *qs, uint16_t *rm, long long RS,
+                               KswOut &oa, KswOut &ob)
+{
+    KState ks[2];
+    const PairIn *in[2] = { &A, &B };
+    const int shift = c.b > -c.ambig ? c.b : -c.ambig;       /* |min(mat)| */
+    const int mxs = c.maxsc;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const PairIn &x = *in[p];
+        const int xtra = x.h0;
+        ks[p].qlen = x.valid ? x.len2 : 0;
+        ks[p].tlen = x.valid ? x.len1 : 0;
+        ks[p].idr = x.idr;
+        ks[p].minsc = (xtra & KSW_XSUBO_) ? (xtra & 0xffff) : 0x10000;
+        ks[p].endsc = (xtra & KSW_XSTOP_) ? (xtra & 0xffff) : 0x10000;
+        ks[p].gmax = 0; ks[p].te = -1; ks[p].qe = -1; ks[p].rows = 0;
+        ks[p].act = (x.valid && x.len1 > 0) ? 1 : 0;
+    }
+    const int qmin = mn(ks[0].qlen, ks[1].qlen), qmax = mx(ks[0].qlen, ks[1].qlen);
+    for (int j = 0; j < qmax; ++j) {
+        he[j * S] = make_uint2(0u, 0u);
+        uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
+        uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
+        qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
+        qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+    }
+    const uint32_t LUTLO = lut_lo(c), LUTHI = lut_hi(c);
+    const uint32_t NEG_OE_DEL = pack2(-c.oe_del, -c.oe_del), NEG_OE_INS = pack2(-c.oe_ins, -c.oe_ins);
+    const uint32_t NEG_E_DEL = pack2(-c.e_del, -c.e_del), NEG_E_INS = pack2(-c.e_ins, -c.e_ins);
+    const uint32_t LONGER = ks[0].qlen > ks[1].qlen ? 0x0000ffffu : 0xffff0000u;
+
+    int i = 0;
+    while (ks[0].act | ks[1].act) {
+        uint32_t tb[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            uint32_t t = ks[p].act ? ref[ks[p].idr + i] : 0u;
+            tb[p] = t > 4u ? 4u : t;
+        }
+        const uint32_t T = tb[0] * 0x0011u | tb[1] * 0x1100u;
+        const uint32_t ACT = (ks[0].act ? 0x0000ffffu : 0u) | (ks[1].act ? 0xffff0000u : 0u);
+        uint32_t f = 0, hd = 0, key = 0;
+        uint32_t jv = 0x00ff00ffu;                    /* 255 - j per lane */
+        int j = 0;
+        if (ACT == 0xffffffffu) {
+#pragma unroll 4
+            for (; j < qmin; ++j) {
+                uint2 v = he[j * S];
+                uint32_t q_ = qs[j * S];
+                uint32_t x_ = p_xsel(q_, T);
+                uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
+                uint32_t h_ = p_max3_relu(p_add(hd, s_), v.y, f);
+                uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));
+                f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS));
+                hd = v.x;
+                he[j * S] = make_uint2(h_, en);
+                key = p_maxu(key, (h_ << 8) + jv);
+                jv -= 0x00010001u;
+            }
+        }
+        /* one lane finished, or the tail of the longer query: masked cells */
+        for (; j < qmax; ++j) {
+            const uint32_t MK = ACT & (j < qmin ? 0xffffffffu : LONGER);
+            uint2 v = he[j * S];
+            uint32_t q_ = qs[j * S];
+            uint32_t x_ = p_xsel(q_, T);
+            uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
+            uint32_t h_ = p_max3_relu(p_add(hd, s_), v.y, f) & MK;
+            uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL)) & MK;
+            f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS)) & MK;
+            hd = v.x & MK;
+            he[j * S] = make_uint2(h_, en);
+            key = p_maxu(key, ((h_ << 8) + jv) & MK);
+            jv -= 0x00010001u;
+        }
+        {
+            const int ia = ks[0].act ? (int)((key >> 8) & 0xff) : 0;
+            const int ib = ks[1].act ? (int)(key >> 24) : 0;
+            rm[(long long)i * RS] = (uint16_t)(ia | (ib << 8));
+        }
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            KState &s = ks[p];
+            if (!s.act) continue;
+            const int kp = half_u(key, p);
+            const int imax = s.qlen > 0 ? (kp >> 8) : 0;
+            s.rows = i + 1;
+            if (imax > s.gmax) {
+                s.gmax = imax; s.te = i; s.qe = 255 - (kp & 0xff);
+                if ((is8 && s.gmax + shift >= 255) || s.gmax >= s.endsc) { s.act = 0; continue; }
+            }
+            if (i + 1 >= s.tlen) s.act = 0;
+        }
+        ++i;
+    }
+
+    KswOut *out[2] = { &oa, &ob };
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        KState &s = ks[p];
+        KswOut &o = *out[p];
+        const bool ovf = is8 && s.gmax + shift >= 255;
+        o.score = ovf ? 255 : s.gmax; o.te = s.te; o.qe = -1; o.score2 = -1; o.te2 = -1;
+        o.cells = (long long)s.rows * s.qlen;
+        if (!ovf) {
+            /* ksw_u8: qe = smallest j attaining max(Hmax); Hmax stays all-zero when gmax == 0 */
+            o.qe = s.qlen > 0 ? (s.gmax > 0 ? s.qe : 0) : -1;
+            if (s.minsc < 0x10000) {
+                BList bl; const int d = (o.score + mxs - 1) / mxs;
+                bl.init(s.te - d, s.te + d);
+                for (int r = 0; r < s.rows; ++r) {
+                    const int v = rm[(long long)r * RS];
+                    const int im = p ? (v >> 8) : (v & 0xff);
+                    if (im >= s.minsc) bl.push(im, r);
+                }
+                bl.flush();
+                o.score2 = bl.score2; o.te2 = bl.te2;
+            }
+        }
+    }
+}
+
+/* general 32-bit path: one thread, one pair; H/E rows and row maxima in HBM */
+template <typename IDX>
+BSW_HD void kswv_general_thread(const Const &c, int is8, const PairIn &P,
+                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                                int2 *he, IDX S, int *rm, IDX RS, KswOut &o)
+{
+    const int qlen = P.len2, tlen = P.len1, xtra = P.h0;
+    const uint8_t *query = qer + P.idq, *target = ref + P.idr;
+    const int shift = c.b > -c.ambig ? c.b : -c.ambig, mxs = c.maxsc;
+    const int minsc = (xtra & KSW_XSUBO_) ? (xtra & 0xffff) : 0x10000;
+    const int endsc = (xtra & KSW_XSTOP_) ? (xtra & 0xffff) : 0x10000;
+    int gmax = 0, te = -1, qe = -1, rows = 0;
+    for (int j = 0; j < qlen; ++j) he[(IDX)j * S] = make_int2(0, 0);
+    for (int i = 0; i < tlen; ++i) {
+        int f = 0, hd = 0, imax = 0, jmax = -1;
+        int t = target[i]; t = t > 4 ? 4 : t;
+        for (int j = 0; j < qlen; ++j) {
+            int2 v = he[(IDX)j * S];
+            int q = query[j]; q = q > 4 ? 4 : q;
+            int sc = (q == 4 || t == 4) ? c.ambig : (q == t ? c.a : -c.b);
+            int h = hd + sc, e = v.y, tt;
+            hd = v.x;
+            h = h > 0 ? h : 0; h = h > e ? h : e; h = h > f ? h : f;
+            if (h > imax) { imax = h; jmax = j; }
+            e -= c.e_del; tt = h - c.oe_del; e = e > tt ? e : tt; e = e > 0 ? e : 0;
+            f -= c.e_ins; tt = h - c.oe_ins; f = f > tt ? f : tt; f = f > 0 ? f : 0;
+            he[(IDX)j * S] = make_int2(h, e);
+        }
+        rm[(IDX)i * RS] = imax;
+        rows = i + 1;
+        if (imax > gmax) {
+            gmax = imax; te = i; qe = jmax;
+            if ((is8 && gmax + shift >= 255) || gmax >= endsc) break;
+        }
+    }
+    const bool ovf = is8 && gmax + shift >= 255;
+    o.score = ovf ? 255 : gmax; o.te = te; o.qe = -1; o.score2 = -1; o.te2 = -1;
+    o.cells = (long long)rows * qlen;
+    if (!ovf) {
+        o.qe = qlen > 0 ? (gmax > 0 ? qe : 0) : -1;
+        if (minsc < 0x10000) {
+            BList bl; const int d = (o.score + mxs - 1) / mxs;
+            bl.init(te - d, te + d);
+            for (int r = 0; r < rows; ++r) { const int im = rm[(IDX)r * RS]; if (im >= minsc) bl.push(im, r); }
+            bl.flush();
+            o.score2 = bl.score2; o.te2 = bl.te2;
+        }
+    }
+}
+
+} /* namespace bswk */

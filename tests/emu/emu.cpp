@@ -6,6 +6,7 @@
 #include <cstring>
 #include <cstdint>
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core.cuh"
+#include "../../bwa-mem2-arm_b200/csrc/kswv_core.cuh"
 #include "../../include/bsw_cuda.h"
 
 using namespace bswk;
@@ -50,6 +51,43 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         std::vector<int2> eh(P.len2 + 2);
         bsw_general_thread<int>(c, w, P, ref, qer, eh.data(), 1, o);
         put(pairs[i], o); if (cells_out) cells_out[i] = o.cells;
+    }
+    return (int)el.size();
+}
+
+
+static void kput(bsw_kswr_t *aln, const bsw_seqpair_t &sp, int i, const KswOut &o, int phase)
+{
+    if (phase == 0) { bsw_kswr_t r = { o.score, o.te, o.qe, o.score2, o.te2, -1, -1 }; aln[i] = r; }
+    else { bsw_kswr_t *a = &aln[sp.regid]; if (a->score == o.score) { a->tb = a->te - o.te; a->qb = a->qe - o.qe; } }
+}
+
+int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln, int n,
+             int o_del, int e_del, int o_ins, int e_ins, int a, int b, int ambig,
+             int is8, int phase, int force_general, long long *cells_out)
+{
+    Const c = mk(o_del, e_del, o_ins, e_ins, 0, 0, a, b, ambig);
+    std::vector<int> el, ge;
+    for (int i = 0; i < n; ++i)
+        (!force_general && kswv_packed_eligible(c, pairs[i].len1, pairs[i].len2) ? el : ge).push_back(i);
+    for (size_t k = 0; k < el.size(); k += 2) {
+        PairIn A, B; KswOut oa, ob;
+        int ia = el[k], ib = k + 1 < el.size() ? el[k + 1] : -1;
+        A = { pairs[ia].idr, pairs[ia].idq, pairs[ia].len1, pairs[ia].len2, pairs[ia].h0, 1 };
+        if (ib >= 0) B = { pairs[ib].idr, pairs[ib].idq, pairs[ib].len1, pairs[ib].len2, pairs[ib].h0, 1 };
+        else B = { 0, 0, 0, 0, 0, 0 };
+        int qm = A.len2 > B.len2 ? A.len2 : B.len2, tm = A.len1 > B.len1 ? A.len1 : B.len1;
+        std::vector<uint2> he(qm + 2); std::vector<uint16_t> qs(qm + 2), rm(tm + 2);
+        kswv_packed_thread<1>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
+        kput(aln, pairs[ia], ia, oa, phase); if (cells_out) cells_out[ia] = oa.cells;
+        if (ib >= 0) { kput(aln, pairs[ib], ib, ob, phase); if (cells_out) cells_out[ib] = ob.cells; }
+    }
+    for (int i : ge) {
+        PairIn P = { pairs[i].idr, pairs[i].idq, pairs[i].len1, pairs[i].len2, pairs[i].h0, 1 };
+        KswOut o;
+        std::vector<int2> he(P.len2 + 2); std::vector<int> rm(P.len1 + 2);
+        kswv_general_thread<int>(c, is8, P, ref, qer, he.data(), 1, rm.data(), 1, o);
+        kput(aln, pairs[i], i, o, phase); if (cells_out) cells_out[i] = o.cells;
     }
     return (int)el.size();
 }

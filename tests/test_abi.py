@@ -1,0 +1,51 @@
+"""The C-ABI library loads and exports every symbol include/bsw_cuda.h declares
+(no compute call: this runs in the GPU-less container)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    txt = open(os.path.join(ROOT, "include", "bsw_cuda.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    names = set(re.findall(r"\b((?:bsw|kswv)_[A-Za-z0-9_]+)\s*\(", txt))
+    return sorted(names)
+
+
+def test_header_symbols_exported(bsw):
+    L = C.CDLL(bsw.LIB_PATH)
+    declared = _declared_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/bsw_cuda.h but not exported"
+    assert set(declared) == set(bsw.EXPORTS)
+
+
+def test_struct_layouts(bsw):
+    # bandedSWA.h SeqPair: 14 x int32; ksw.h kswr_t: 7 x int32
+    assert bsw.SEQPAIR.itemsize == 56 and bsw.KSWR.itemsize == 28
+    assert bsw.SEQPAIR.names[8:] == ("score", "tle", "gtle", "qle", "gscore", "max_off")
+    assert bsw.SEQPAIR.fields["score"][1] == 32
+    assert bsw.KSWR.names == ("score", "te", "qe", "score2", "te2", "tb", "qb")
+
+
+def test_version_and_device_count(bsw):
+    assert b"sm_100a" in bsw.lib().bsw_version()
+    assert bsw.device_count() >= 0
+
+
+def test_product_does_not_touch_oracle():
+    """The product path must not import, link or execute anything under oracle/."""
+    pkg = os.path.join(ROOT, "bwa-mem2-arm_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".cu", ".cuh", ".h", ".py", ".cpp")) or f == "Makefile":
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in txt.lower() or f in ("bsw_core.cuh", "kswv_core.cuh"), f
+    for f in ("bsw_core.cuh", "kswv_core.cuh"):
+        txt = open(os.path.join(pkg, "csrc", f)).read()
+        assert "#include \"oracle" not in txt and "liboracle" not in txt

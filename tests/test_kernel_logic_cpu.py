@@ -1,0 +1,84 @@
+"""CPU check of the CUDA kernels' per-thread DP (bsw_core.cuh / kswv_core.cuh compiled for
+the host with emulated DPX ops) against the oracle.  This validates the packed-lane logic
+(masks, band trimming, key packing) in a container without a GPU; the real parity tests,
+through the C ABI on a B200, are in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import common
+import emu
+
+
+def _check_bsw(ora, pairs, ref, qer, **kw):
+    prm = ora.make_params(zdrop=kw.get("zdrop", 100), end_bonus=kw.get("end_bonus", 5))
+    o = pairs.copy()
+    _, oc = ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4, True)
+    for fg in (0, 1):
+        e, ec, _ = emu.bsw(pairs, ref, qer, force_general=fg, **kw)
+        bad = common.diff_fields(o, e, common.BSW_FIELDS) | (oc != ec)
+        assert not bad.any(), common.describe_first(o, e, bad)
+
+
+def test_bsw_edge_cases(ora):
+    p, r, q = common.edge_case_pairs()
+    for w in (100, 7, 1):
+        _check_bsw(ora, p, r, q, w=w)
+
+
+def test_bsw_c1_shape(ora):
+    (L, lr, lq), (R, rr, rq) = common.bsw_c1(4000)
+    _check_bsw(ora, L, lr, lq)
+    _check_bsw(ora, R, rr, rq)
+
+
+def test_bsw_c3_shape_zdrop(ora):
+    d = ora.gen_bsw(1500, read_len=250, seed=0xC3, div=0.05)
+    L, lr, lq = d["left"]
+    _check_bsw(ora, L, lr, lq)
+    _check_bsw(ora, L, lr, lq, w=10, zdrop=20)
+
+
+@pytest.mark.parametrize("cfg", [(0, 40, 0, 60, 0.8, 0.02), (1, 200, 1, 300, 0.6, 0.05),
+                                 (50, 255, 50, 400, 0.9, 0.001), (1, 30, 1, 30, 0.3, 0.2)])
+def test_bsw_random(ora, cfg):
+    q0, q1, t0, t1, sim, pn = cfg
+    P, r, q = ora.gen_random(1500, q0, q1, t0, t1, h0min=1, h0max=50, sim=sim, p_n=pn, seed=q1)
+    _check_bsw(ora, P, r, q)
+    _check_bsw(ora, P, r, q, w=5, zdrop=10)
+    _check_bsw(ora, P, r, q, w=1, zdrop=0, end_bonus=0)
+
+
+def _check_kswv(ora, pairs, ref, qer, is8):
+    prm = ora.make_params()
+    for fg in (0, 1):
+        ao = np.zeros(len(pairs), ora.KSWR)
+        ae = np.zeros(len(pairs), ora.KSWR)
+        _, oc = ora.kswv_batch(pairs, ref, qer, ao, prm, is8, 0, 4, True)
+        ec, _ = emu.kswv(pairs, ref, qer, ae, is8, 0, force_general=fg)
+        assert (ao == ae).all() and (oc == ec).all()
+        p1, r1, q1 = ora.kswv_phase1_inputs(pairs, ref, qer, ao)
+        ora.kswv_batch(p1, r1, q1, ao, prm, is8, 1, 4)
+        emu.kswv(p1, r1, q1, ae, is8, 1, force_general=fg)
+        assert (ao == ae).all()
+
+
+def test_kswv_c4_shape(ora):
+    P, r, q = ora.gen_kswv(1200)
+    _check_kswv(ora, P, r, q, 1)
+    P, r, q = ora.gen_kswv(400, qlen=250, tmin=400, tmax=700, seed=5)
+    _check_kswv(ora, P, r, q, 0)
+
+
+def test_kswv_overflow_and_tandem(ora):
+    P, r, q = ora.gen_kswv(200, qlen=255, tmin=300, tmax=400, seed=9, div=0.0,
+                           xtra=ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 19)
+    _check_kswv(ora, P, r, q, 1)
+    P, r, q = ora.gen_kswv(800, qlen=60, tmin=200, tmax=400, seed=11, p_contain=0.9, div=0.05)
+    for i in range(len(P)):
+        o, l = int(P["idr"][i]), int(P["len1"][i])
+        h = l // 2
+        r[o + h:o + 2 * h] = r[o:o + h]
+    _check_kswv(ora, P, r, q, 1)
+    P, r, q = ora.gen_random(1000, 0, 40, 0, 80, sim=0.7, p_n=0.05, seed=3)
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 5
+    _check_kswv(ora, P, r, q, 1)
