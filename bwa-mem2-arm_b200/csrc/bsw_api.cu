@@ -120,11 +120,11 @@ void core_init(Core &k, int mode)
     }
     /* launch shape of the packed kernels (DESIGN.md "occupancy"): blocks_per_sm persistent
      * blocks share the SM's shared memory; block_warps bounds the warps of one tile. */
-    k.blocks_per_sm = std::max(1, env_int("BSW_CUDA_BLOCKS_PER_SM", 1));
-    k.block_warps = std::min(16, std::max(1, env_int("BSW_CUDA_BLOCK_WARPS", 16)));
+    k.blocks_per_sm = std::max(1, env_int("BSW_CUDA_BLOCKS_PER_SM", 4));
+    k.block_warps = std::min(16, std::max(1, env_int("BSW_CUDA_BLOCK_WARPS", 4)));
     int optin = k.ctx[0].smem_optin;                    /* 227 KB on sm_100 */
     int per_block = (optin + 1024) / k.blocks_per_sm - 1024;
-    per_block = std::min(per_block, optin);
+    per_block = std::min(per_block, optin - 1024);     /* room for the kernels' static shared memory */
     int kb = env_int("BSW_CUDA_SMEM_KB", 0);
     if (kb > 0) per_block = std::min(per_block, kb * 1024);
     k.smem_bytes = per_block & ~15;

@@ -8,7 +8,7 @@
  * 32-bit register, and sweeps them row-synchronously, exactly like one
  * 2-lane slice of the reference's inter-sequence vector kernels.  A warp is a
  * 64-pair vector.  All cell arithmetic is packed signed 16-bit DPX:
- *     M  = min(Hd + s, 2*Hd)                 VIADDMNMX.S16x2   (zero gate of A.1)
+ *     M  = min(Hd + s, (a+1)*Hd)             IMAD + VIADDMNMX.S16x2 (zero gate of A.1)
  *     h  = max3(M, e, f)                     VIMNMX3.S16x2
  *     e' = max(M - oe_del, e - e_del, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
  *     f' = max(M - oe_ins, f - e_ins, 0)     VIADD.16x2 + VIADDMNMX.S16x2.RELU
@@ -59,7 +59,10 @@ __device__ __forceinline__ uint32_t p_max3(uint32_t a, uint32_t b, uint32_t c)  
 __device__ __forceinline__ uint32_t p_addmax_relu(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2_relu(a, b, c); }
 __device__ __forceinline__ uint32_t p_add(uint32_t a, uint32_t b)                { return __vadd2(a, b); }
 __device__ __forceinline__ uint32_t p_maxu(uint32_t a, uint32_t b)               { return __vmaxu2(a, b); }
-__device__ __forceinline__ uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)   { return __byte_perm(a, b, s); }
+/* raw PRMT (default mode): selector nibble bit 3 replicates the sign of the selected byte.
+ * NOT __byte_perm, which masks the selector with 0x7777 and so drops the sign replication. */
+__device__ __forceinline__ uint32_t p_perm(uint32_t a, uint32_t b, uint32_t s)
+{ uint32_t r; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s)); return r; }
 /* LUT index of both lanes in ONE LOP3: (q ^ t) | ((q | t) & 0x4444), truth table 0xBC */
 __device__ __forceinline__ uint32_t p_xsel(uint32_t q, uint32_t t)
 { uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xBC;" : "=r"(r) : "r"(q), "r"(t), "r"(0x4444u)); return r; }
@@ -109,6 +112,7 @@ BSW_HD bool packed_eligible(const Const &c, int len1, int len2, int h0)
     if (len1 < 0 || len2 < 0 || h0 <= 0) return false;
     if (len2 > BSW_PACKED_MAX_QLEN) return false;
     long long bound = (long long)h0 + (long long)mn(len1, len2) * c.a;
+    if (c.a > 120 || c.b > 120) return false;
     return bound <= BSW_PACKED_MAX_SCORE;
 }
 
@@ -192,6 +196,9 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
     const uint32_t NEG_OE_DEL = pack2(-c.oe_del, -c.oe_del), NEG_OE_INS = pack2(-c.oe_ins, -c.oe_ins);
     const uint32_t NEG_E_DEL = pack2(-c.e_del, -c.e_del), NEG_E_INS = pack2(-c.e_ins, -c.e_ins);
     const int BIG = 0x3fffffff;
+    /* zero gate of A.1 (M = Hd ? Hd + s : 0) as M = min(Hd + s, (a+1)*Hd): exact because
+     * s <= a <= a*Hd for Hd >= 1, and (a+1)*0 = 0 caps a dead cell at 0.  Lanes hold <= 255. */
+    const uint32_t GATE = (uint32_t)(c.a + 1);
 
     int i = 0;
     while (ps[0].act | ps[1].act) {
@@ -229,7 +236,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             uint32_t q_ = qs[j_ * S];                                                   \
             uint32_t x_ = p_xsel(q_, T);                              \
             uint32_t s_ = p_perm(LUTLO, LUTHI, x_);                                     \
-            uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);                                 \
+            uint32_t M_ = p_addmin(v.x, s_, v.x * GATE);                                 \
             uint32_t h_ = p_max3(M_, v.y, f);                                           \
             uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));         \
             uint32_t fn = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));           \
@@ -255,7 +262,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 uint32_t q_ = qp[k * S];
                 uint32_t x_ = p_xsel(q_, T);
                 uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-                uint32_t M_ = p_addmin(v.x, s_, v.x + v.x);
+                uint32_t M_ = p_addmin(v.x, s_, v.x * GATE);
                 uint32_t h_ = p_max3(M_, v.y, f);
                 uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));
                 f = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));

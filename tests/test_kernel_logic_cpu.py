@@ -10,7 +10,7 @@ import emu
 
 
 def _check_bsw(ora, pairs, ref, qer, **kw):
-    prm = ora.make_params(zdrop=kw.get("zdrop", 100), end_bonus=kw.get("end_bonus", 5))
+    prm = ora.make_params(**{k: v for k, v in kw.items() if k != "w"})
     o = pairs.copy()
     _, oc = ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4, True)
     for fg in (0, 1):
@@ -46,6 +46,12 @@ def test_bsw_random(ora, cfg):
     _check_bsw(ora, P, r, q)
     _check_bsw(ora, P, r, q, w=5, zdrop=10)
     _check_bsw(ora, P, r, q, w=1, zdrop=0, end_bonus=0)
+
+
+def test_bsw_scoring_variants(ora):
+    P, r, q = ora.gen_random(1500, 1, 120, 1, 200, h0min=1, h0max=60, sim=0.85, p_n=0.02, seed=31)
+    for (od, ed, oi, ei, zd, eb, a, b) in ((4, 2, 7, 1, 30, 0, 2, 3), (1, 1, 1, 1, 0, 9, 1, 9), (12, 3, 5, 2, 50, 5, 1, 1), (5, 2, 5, 2, 40, 3, 3, 2)):
+        _check_bsw(ora, P, r, q, w=37, o_del=od, e_del=ed, o_ins=oi, e_ins=ei, zdrop=zd, end_bonus=eb, a=a, b=b)
 
 
 def _check_kswv(ora, pairs, ref, qer, is8):
