@@ -218,6 +218,7 @@ def main():
             if not (o[f] == samp[f]).all():
                 raise SystemExit(f"PARITY FAILURE on the CPU-baseline sample, field {f}")
         chk = bswb200.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        chk.set_cell_counting(True)
         g = samp_in.copy()
         chk.getScores16(g, lr, lq, ns, 1, W_BAND)
         if chk.stats()["cells"] != cpu_cells:
@@ -238,6 +239,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---------------- DP cells of one step (counting variant of the kernel, outside the timed region) ----
+    sw.set_cell_counting(True)
+    sw.reset_stats()
+    one_step_resident()
+    torch.cuda.synchronize()
+    cells_step = sw.stats()["cells"]
+    sw.set_cell_counting(False)
+
     # ---------------- resident timing ("value") ----------------
     for _ in range(args.warmup):
         one_step_resident()
@@ -254,7 +263,6 @@ def main():
     barrier()
     ms_total = e0.elapsed_time(e1)
     st = sw.stats()
-    cells_step = st["cells"] // args.steps
     launches = st["kernel_launches"]
 
     # DP-kernel-only time for the roofline (CUDA events around the DP kernels on the library's stream)

@@ -27,7 +27,7 @@ EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
     "bsw_dev_getScores", "kswv_dev_getScores", "bsw_host_alloc", "bsw_host_free",
-    "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing",
+    "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
 )
@@ -81,7 +81,7 @@ def lib():
         f.argtypes = [vp, C.POINTER(Stats)]
     for f in (L.bsw_reset_stats, L.kswv_reset_stats):
         f.argtypes = [vp]
-    for f in (L.bsw_set_timing, L.kswv_set_timing):
+    for f in (L.bsw_set_timing, L.kswv_set_timing, L.bsw_set_cell_counting):
         f.argtypes = [vp, C.c_int]
     L.bsw_measure_dpx_peak.restype = C.c_double
     L.bsw_measure_dpx_peak.argtypes = [C.c_int, C.c_int]
@@ -160,6 +160,9 @@ class BandedPairWiseSW:
 
     def set_timing(self, on=True):
         self._L.bsw_set_timing(self._h, int(on))
+
+    def set_cell_counting(self, on=True):
+        self._L.bsw_set_cell_counting(self._h, int(on))
 
 
 class kswv:

@@ -64,7 +64,7 @@ struct Core {
     std::vector<DevCtx> ctx;
     bsw_stats_t st;
     int timing = 0;
-    int smem_bytes = 0, block_warps = 16, blocks_per_sm = 1;
+    int count_cells = 0;
     int mode = MODE_BSW;
 };
 
@@ -118,20 +118,18 @@ void core_init(Core &k, int mode)
         x.cells.reserve(sizeof(unsigned long long));
         CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
     }
-    /* launch shape of the packed kernels (DESIGN.md "occupancy"): blocks_per_sm persistent
-     * blocks share the SM's shared memory; block_warps bounds the warps of one tile. */
-    k.blocks_per_sm = std::max(1, env_int("BSW_CUDA_BLOCKS_PER_SM", 4));
-    k.block_warps = std::min(16, std::max(1, env_int("BSW_CUDA_BLOCK_WARPS", 4)));
-    int optin = k.ctx[0].smem_optin;                    /* 227 KB on sm_100 */
-    int per_block = (optin + 1024) / k.blocks_per_sm - 1024;
-    per_block = std::min(per_block, optin - 1024);     /* room for the kernels' static shared memory */
-    int kb = env_int("BSW_CUDA_SMEM_KB", 0);
-    if (kb > 0) per_block = std::min(per_block, kb * 1024);
-    k.smem_bytes = per_block & ~15;
+    k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
+    /* packed kernels: one warp per block, dynamic shared memory = NE x 320 B (NE <= 256) */
+    const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
     for (DevCtx &x : k.ctx) {
         CK(cudaSetDevice(x.dev));
-        CK(cudaFuncSetAttribute(bsw_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem_bytes));
-        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem_bytes));
+        if (max_smem > x.smem_optin) die("device shared memory too small for the packed kernels");
+        CK(cudaFuncSetAttribute(bsw_packed_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(bsw_packed_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(bsw_packed_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        CK(cudaFuncSetAttribute(bsw_packed_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     }
 }
 
@@ -175,17 +173,15 @@ const Plan *run_plan(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, int n, cu
     x.cubtmp.reserve(tmp_bytes);
     Plan *d_plan = (Plan *)x.plan.p;
     CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));
-    const int max_elems = std::min(BSW_NBINS * 16, k.smem_bytes / BSW_WARP_ELEM_BYTES / 16 * 16);
+    const int max_elems = BSW_NBINS * 16;
     prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, n, k.c, k.mode, max_elems, tier8_check,
                                                  (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
     CK(cudaGetLastError());
     CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
                                                  (uint32_t *)x.idx_a.p, (uint32_t *)x.idx_b.p, n, 0, 25, s));
-    plan_kernel<<<1, 32, 0, s>>>(d_plan, k.smem_bytes, k.block_warps);
-    CK(cudaGetLastError());
     CK(cudaMemcpyAsync(x.h_plan, d_plan, sizeof(Plan), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    k.st.kernel_launches += 2 + 8;    /* prep + plan + the sort's internal launches (upper bound of cub's onesweep path) */
+    k.st.kernel_launches += 1 + 8;    /* prep + the sort's internal launches (upper bound of cub's onesweep path) */
     if (x.h_plan->bad_pairs) {
         fprintf(stderr, "[bsw-b200] fatal: %d pair(s) violate the call contract (negative length, h0 <= 0, or "
                         ">= %d bases in getScores8)\n", x.h_plan->bad_pairs, BSW_MAX_SEQ_LEN8);
@@ -199,15 +195,22 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
 {
     if (n <= 0) return;
     const Plan *pl = run_plan(k, x, d_pairs, n, s, tier8_check);
-    Plan *d_plan = (Plan *)x.plan.p;
     const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
-    if (pl->ntiles > 0) {
-        int grid = std::min(pl->ntiles, x.sm_count * k.blocks_per_sm);
-        bsw_packed_kernel<<<grid, k.block_warps * 32, k.smem_bytes, s>>>(d_pairs, d_ref, d_qer, sorted, d_plan, k.c, w,
-                                                                          (unsigned long long *)x.cells.p);
+    int n_packed = 0;
+    for (int qb = BSW_NBINS; qb >= 1; --qb) {            /* longest queries first */
+        const int cnt = pl->hist[qb];
+        if (cnt <= 0) continue;
+        const int NE = qb * 16, grid = (cnt + 63) / 64;
+        if (k.count_cells)
+            bsw_packed_kernel<true><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+                                                                             NE, k.c, w, (unsigned long long *)x.cells.p);
+        else
+            bsw_packed_kernel<false><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+                                                                              NE, k.c, w, (unsigned long long *)x.cells.p);
         CK(cudaGetLastError());
         k.st.kernel_launches++;
+        n_packed += cnt;
     }
     if (pl->n_general > 0) {
         /* bounded scratch: at most ~1 GiB of eh rows per launch */
@@ -216,7 +219,7 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
         x.scratch.reserve((size_t)chunk * per_pair);
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, sorted, pl->n_packed + first, cnt,
+            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed + first, cnt,
                                                               k.c, w, (int2 *)x.scratch.p, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -226,7 +229,7 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
         CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
         float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
     }
-    k.st.pairs += n; k.st.pairs_packed += pl->n_packed; k.st.pairs_general += pl->n_general;
+    k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
 }
 
 void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
@@ -234,18 +237,25 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
 {
     if (n <= 0) return;
     const Plan *pl = run_plan(k, x, d_pairs, n, s, 0);
-    Plan *d_plan = (Plan *)x.plan.p;
     const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
-    if (pl->ntiles > 0) {
-        const long long stride = pl->n_packed;
+    int n_packed = 0;
+    for (int qb = 1; qb <= BSW_NBINS; ++qb) n_packed += pl->hist[qb];
+    if (n_packed > 0) {
+        const long long stride = n_packed;
         x.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
-        int grid = std::min(pl->ntiles, x.sm_count * k.blocks_per_sm);
-        kswv_packed_kernel<<<grid, k.block_warps * 32, k.smem_bytes, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, d_plan,
+        int first = 0;
+        for (int qb = BSW_NBINS; qb >= 1; --qb) {
+            const int cnt = pl->hist[qb];
+            if (cnt <= 0) continue;
+            const int NE = qb * 16, grid = (cnt + 63) / 64;
+            kswv_packed_kernel<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
                                                                          k.c, is8, phase, (uint16_t *)x.rowmax.p, stride,
                                                                          (unsigned long long *)x.cells.p);
-        CK(cudaGetLastError());
-        k.st.kernel_launches++;
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+            first += cnt;
+        }
     }
     if (pl->n_general > 0) {
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
@@ -255,7 +265,7 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
         int *rm = (int *)((char *)x.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, pl->n_packed + first, cnt,
+            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, n_packed + first, cnt,
                                                                k.c, is8, phase, he, rm, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -265,7 +275,7 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
         CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
         float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
     }
-    k.st.pairs += n; k.st.pairs_packed += pl->n_packed; k.st.pairs_general += pl->n_general;
+    k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
 }
 
 /* byte extents [lo, hi) of the sequence buffers touched by pairs[first, first+cnt) */
@@ -492,6 +502,7 @@ static void stats_reset(Core &k)
 void bsw_get_stats(bsw_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
 void bsw_reset_stats(bsw_t *h) { stats_reset(h->k); }
 void bsw_set_timing(bsw_t *h, int on) { h->k.timing = on; }
+void bsw_set_cell_counting(bsw_t *h, int on) { h->k.count_cells = on; }
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
 void kswv_reset_stats(kswv_t *h) { stats_reset(h->k); }
 void kswv_set_timing(kswv_t *h, int on) { h->k.timing = on; }

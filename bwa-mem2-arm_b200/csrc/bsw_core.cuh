@@ -137,17 +137,101 @@ BSW_HD uint32_t lut_hi(const Const &c)
 /* per-pair scalar state of the row loop */
 struct PState {
     int qlen, tlen, h0, w, idr;
-    int beg, end, max, max_i, max_j, max_ie, gscore, max_off;
-    int act;
+    int end, max, max_i, max_j, max_ie, gscore, max_off;
+    int act, clean;
+    int beg;             /* true (trimmed) beg: only maintained when COUNT */
     long long cells;
 };
+
+struct RowCtx { uint32_t T, LUTLO, LUTHI, GATE, NOD, NOI, NED, NEI; };
+
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
+/* keeps a warp-uniform constant in a vector register (PRMT cannot take a uniform register as data) */
+__device__ __forceinline__ uint32_t launder(uint32_t v) { uint32_t r; asm volatile("mov.b32 %0, %1;" : "=r"(r) : "r"(v)); return r; }
+#else
+static inline uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return p_maxu(p_maxu(a, b), c); }
+static inline uint32_t launder(uint32_t v) { return v; }
+#endif
+
+/* one DP cell of both lanes (A.1 inner loop body) */
+BSW_HD void bsw_cell(const RowCtx &r, uint2 v, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
+{
+    const uint32_t x = p_xsel(q, r.T);
+    const uint32_t s = p_perm(r.LUTLO, r.LUTHI, x);
+    const uint32_t M = p_addmin(v.x, s, v.x * r.GATE);
+    h = p_max3(M, v.y, f);
+    en = p_addmax_relu(M, r.NOD, p_add(v.y, r.NED));
+    f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
+}
+
+/*
+ * Unmasked sweep of columns [j0, j1) for both lanes, software-pipelined in groups of four
+ * columns: the next group's {H,E} and selectors are loaded before the current group's
+ * dependent chain (f, h1, key) is evaluated.
+ * key = max over (h << 8 | j): row maximum and its LAST column (ties -> larger j).
+ */
+template <int S>
+BSW_HD void bsw_sweep(const RowCtx &r, uint2 *he, const uint16_t *qs, int j0, int j1,
+                      uint32_t &f, uint32_t &h1, uint32_t &key)
+{
+    const int n = j1 - j0;
+    if (n <= 0) return;
+    uint2 *hp = he + j0 * S;
+    const uint16_t *qp = qs + j0 * S;
+    const uint32_t c0 = (uint32_t)j0 * 0x00010001u, c1 = c0 + 0x00010001u, c2 = c0 + 0x00020002u, c3 = c0 + 0x00030003u;
+    int k = 0;
+#define BSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                              \
+    {                                                                                          \
+        uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                               \
+        bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = make_uint2(h1, ea);                  \
+        bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = make_uint2(ha, eb);                  \
+        bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = make_uint2(hb, ec);                  \
+        bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = make_uint2(hc, ed);                  \
+        h1 = hd;                                                                               \
+        const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
+        key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                                      \
+    }
+    if (n >= 4) {
+        uint2 v0 = hp[0], v1 = hp[S], v2 = hp[2 * S], v3 = hp[3 * S];
+        uint32_t q0 = qp[0], q1 = qp[S], q2 = qp[2 * S], q3 = qp[3 * S];
+        while (k + 8 <= n) {
+            const uint2 w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
+            const uint32_t r0 = qp[(k + 4) * S], r1 = qp[(k + 5) * S], r2 = qp[(k + 6) * S], r3 = qp[(k + 7) * S];
+            BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
+            v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
+            k += 4;
+        }
+        BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
+        k += 4;
+    }
+#undef BSW_GROUP
+    for (; k < n; ++k) {
+        uint32_t h, en;
+        bsw_cell(r, hp[k * S], qp[k * S], f, h, en);
+        hp[k * S] = make_uint2(h1, en);
+        h1 = h;
+        key = p_maxu(key, (h << 8) + c0 + (uint32_t)k * 0x00010001u);
+    }
+}
 
 /*
  * One thread, two pairs.  he[j*S] = { H(i-1, j-1) packed, E(i, j) packed },
  * qs[j*S] = PRMT selector of query column j for both lanes.  S = element stride
  * (32 in the kernel: [column][lane]).
+ *
+ * Exactness notes (all relative to A.1):
+ *  - left trimming is value-neutral, so the sweep starts at a lazily advanced common start
+ *    `t` (every entry left of t is zero in both lanes) instead of each lane's exact `beg`;
+ *  - right trimming is value-affecting: a lane's f chain is cut at its exact `end`; beyond it
+ *    the lane keeps sweeping over zero-state entries (writes zeros over zeros) while the
+ *    longer lane finishes, which is exact as long as everything right of `end` is zero
+ *    ("clean" lane: no initial-row value survives right of row 0's range).  Lanes that are
+ *    not clean, or whose band limit is crossed, take the masked path;
+ *  - a lane that has terminated is zeroed once, after which it computes zeros for free.
+ * COUNT additionally tracks the exact `beg` to report the oracle's DP-cell count.
  */
-template <int S>
+template <int S, bool COUNT>
 BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                               const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                               uint2 *he, uint16_t *qs, PairOut &oa, PairOut &ob)
@@ -166,12 +250,13 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
         ps[p].max = ps[p].h0; ps[p].max_i = -1; ps[p].max_j = -1; ps[p].max_ie = -1;
         ps[p].gscore = -1; ps[p].max_off = 0; ps[p].cells = 0;
         ps[p].act = (x.valid && x.len1 > 0) ? 1 : 0;
+        ps[p].clean = 1;
     }
 
     /* ---- first row of H (A.1), E = 0, query selectors ---- */
     {
         const int qmax = mx(ps[0].qlen, ps[1].qlen);
-        int hp0 = 0, hp1 = 0;
+        int hp0 = 0, hp1 = 0, lastnz0 = 0, lastnz1 = 0;
         for (int j = 0; j <= qmax; ++j) {
             int hv[2];
 #pragma unroll
@@ -184,136 +269,186 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 hv[p] = v;
             }
             hp0 = hv[0]; hp1 = hv[1];
+            if (hv[0]) lastnz0 = j;
+            if (hv[1]) lastnz1 = j;
             he[j * S] = make_uint2(pack2(hv[0], hv[1]), 0u);
             uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
             uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
             qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
             qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
         }
+        /* clean: every non-zero initial entry is inside row 0's range [0, min(qlen, w+1)] */
+        ps[0].clean = lastnz0 <= mn(ps[0].qlen, ps[0].w + 1);
+        ps[1].clean = lastnz1 <= mn(ps[1].qlen, ps[1].w + 1);
     }
 
-    const uint32_t LUTLO = lut_lo(c), LUTHI = lut_hi(c);
-    const uint32_t NEG_OE_DEL = pack2(-c.oe_del, -c.oe_del), NEG_OE_INS = pack2(-c.oe_ins, -c.oe_ins);
-    const uint32_t NEG_E_DEL = pack2(-c.e_del, -c.e_del), NEG_E_INS = pack2(-c.e_ins, -c.e_ins);
-    const int BIG = 0x3fffffff;
+    RowCtx r;
+    r.LUTLO = launder(lut_lo(c)); r.LUTHI = launder(lut_hi(c));
+    r.NOD = pack2(-c.oe_del, -c.oe_del); r.NOI = pack2(-c.oe_ins, -c.oe_ins);
+    r.NED = pack2(-c.e_del, -c.e_del);   r.NEI = pack2(-c.e_ins, -c.e_ins);
     /* zero gate of A.1 (M = Hd ? Hd + s : 0) as M = min(Hd + s, (a+1)*Hd): exact because
      * s <= a <= a*Hd for Hd >= 1, and (a+1)*0 = 0 caps a dead cell at 0.  Lanes hold <= 255. */
-    const uint32_t GATE = (uint32_t)(c.a + 1);
+    r.GATE = (uint32_t)(c.a + 1);
+    const int BIG = 0x3fffffff;
 
+    uint32_t tnext[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) tnext[p] = ps[p].act ? ref[ps[p].idr] : 0u;
+
+    int t = 0;          /* lazy common start: all entries < t are zero in both lanes */
     int i = 0;
     while (ps[0].act | ps[1].act) {
-        int rb[2], re[2], h1i[2];
+        int sp[2], ep[2], h1i[2], lb[2];
         uint32_t tb[2];
+        int died = 0;                              /* lanes that terminated at row start (empty range) */
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             PState &s = ps[p];
-            if (s.act) {
-                if (s.beg < i - s.w) s.beg = i - s.w;
-                if (s.end > i + s.w + 1) s.end = i + s.w + 1;
-                if (s.end > s.qlen) s.end = s.qlen;
-                int h1 = 0;
-                if (s.beg == 0) { h1 = s.h0 - (c.o_del + c.e_del * (i + 1)); if (h1 < 0) h1 = 0; }
-                h1i[p] = h1;
-                const bool some = s.beg < s.end;
-                rb[p] = some ? s.beg : BIG; re[p] = some ? s.end : 0;
-                uint32_t t = ref[s.idr + i];
-                tb[p] = t > 4u ? 4u : t;
-                if (some) s.cells += s.end - s.beg;
-            } else { rb[p] = BIG; re[p] = 0; h1i[p] = 0; tb[p] = 0; }
+            sp[p] = BIG; ep[p] = 0; h1i[p] = 0; tb[p] = 0; lb[p] = 0;
+            if (!s.act) continue;
+            lb[p] = i - s.w > 0 ? i - s.w : 0;
+            if (s.end > i + s.w + 1) s.end = i + s.w + 1;
+            if (s.end > s.qlen) s.end = s.qlen;
+            if (COUNT) { if (s.beg < lb[p]) s.beg = lb[p]; if (s.end > s.beg) s.cells += s.end - s.beg; }
+            const int st = t > lb[p] ? t : lb[p];
+            int h1 = 0;
+            if (st == 0) { h1 = s.h0 - (c.o_del + c.e_del * (i + 1)); if (h1 < 0) h1 = 0; }
+            const uint32_t tt = tnext[p];
+            tb[p] = tt > 4u ? 4u : tt;
+            if (i + 1 < s.tlen) tnext[p] = ref[s.idr + i + 1];
+            if (st >= s.end) {
+                /* no cell in this row: m == 0, the lane stops here (A.1: gscore check, then break) */
+                const int jafter = lb[p] < s.end ? s.end : lb[p];
+                if (jafter == s.qlen) {
+                    s.max_ie = s.gscore > h1 ? s.max_ie : i;
+                    s.gscore = s.gscore > h1 ? s.gscore : h1;
+                }
+                s.act = 0; died |= 1 << p;
+                continue;
+            }
+            sp[p] = st; ep[p] = s.end; h1i[p] = h1;
         }
-        const int jlo = mn(rb[0], rb[1]), jhi = mx(re[0], re[1]);
-        const int c0 = mx(rb[0], rb[1]), c1 = mn(re[0], re[1]);
-        const uint32_t T = tb[0] * 0x0011u | tb[1] * 0x1100u;
+        if (died) {
+            if (!(ps[0].act | ps[1].act)) break;
+            /* zero the dead lane so that it computes zeros from now on */
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+                if (died & (1 << p)) {
+                    const uint32_t keep = p ? 0x0000ffffu : 0xffff0000u;
+                    for (int j = 0; j <= ps[p].qlen; ++j) { uint2 v = he[j * S]; v.x &= keep; v.y &= keep; he[j * S] = v; }
+                }
+        }
+        r.T = tb[0] * 0x0011u | tb[1] * 0x1100u;
         uint32_t f = 0, key = 0, h1 = pack2(h1i[0], h1i[1]);
+        int h1cut = 0, cut = -1;                   /* lane whose f chain was cut before the other's end */
 
-        /* generic masked cell: lanes outside their [beg,end) are left untouched */
+        /* generic masked cell: lanes outside their [sp, ep) are left untouched */
 #define BSW_CELL_MASKED(J)                                                              \
         {                                                                               \
             const int j_ = (J);                                                         \
-            const uint32_t MK = ((j_ >= rb[0] && j_ < re[0]) ? 0x0000ffffu : 0u) |      \
-                                ((j_ >= rb[1] && j_ < re[1]) ? 0xffff0000u : 0u);       \
+            const uint32_t MK = ((j_ >= sp[0] && j_ < ep[0]) ? 0x0000ffffu : 0u) |      \
+                                ((j_ >= sp[1] && j_ < ep[1]) ? 0xffff0000u : 0u);       \
             uint2 v = he[j_ * S];                                                       \
-            uint32_t q_ = qs[j_ * S];                                                   \
-            uint32_t x_ = p_xsel(q_, T);                              \
-            uint32_t s_ = p_perm(LUTLO, LUTHI, x_);                                     \
-            uint32_t M_ = p_addmin(v.x, s_, v.x * GATE);                                 \
-            uint32_t h_ = p_max3(M_, v.y, f);                                           \
-            uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));         \
-            uint32_t fn = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));           \
-            uint32_t kk = ((h_ & MK) << 8) + ((uint32_t)j_ * 0x00010001u);              \
+            uint32_t h_, en, fn = f;                                                    \
+            bsw_cell(r, v, qs[j_ * S], fn, h_, en);                                     \
             he[j_ * S] = make_uint2((h1 & MK) | (v.x & ~MK), (en & MK) | (v.y & ~MK));  \
             f = fn & MK;                                                                \
             h1 = (h_ & MK) | (h1 & ~MK);                                                \
-            key = p_maxu(key, kk & MK);                                                 \
+            key = p_maxu(key, (((h_ & MK) << 8) + ((uint32_t)j_ * 0x00010001u)) & MK);  \
         }
 
-        int j = jlo;
-        const int head_end = mn(c0, jhi);
-        for (; j < head_end; ++j) BSW_CELL_MASKED(j)
-        /* both lanes in range: no masks */
-        if (c1 > c0) {
-            uint2 *hp = he + c0 * S;
-            const uint16_t *qp = qs + c0 * S;
-            uint32_t jv = (uint32_t)c0 * 0x00010001u;
-            const int nb = c1 - c0;
-#pragma unroll 4
-            for (int k = 0; k < nb; ++k) {
-                uint2 v = hp[k * S];
-                uint32_t q_ = qp[k * S];
-                uint32_t x_ = p_xsel(q_, T);
-                uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-                uint32_t M_ = p_addmin(v.x, s_, v.x * GATE);
-                uint32_t h_ = p_max3(M_, v.y, f);
-                uint32_t en = p_addmax_relu(M_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));
-                f = p_addmax_relu(M_, NEG_OE_INS, p_add(f, NEG_E_INS));
-                hp[k * S] = make_uint2(h1, en);
-                h1 = h_;
-                key = p_maxu(key, (h_ << 8) + jv);
-                jv += 0x00010001u;
+        if (ps[0].act && ps[1].act) {
+            const int ls = mn(sp[0], sp[1]), hs = mx(sp[0], sp[1]);
+            const int e1 = mn(ep[0], ep[1]), e2 = mx(ep[0], ep[1]);
+            int j = ls;
+            const int head_end = mn(hs, e2);
+            for (; j < head_end; ++j) BSW_CELL_MASKED(j)
+            if (hs < e1) { bsw_sweep<S>(r, he, qs, hs, e1, f, h1, key); j = e1; }
+            if (j < hs) j = hs;
+            if (j < e2) {
+                const int sh = ep[0] < ep[1] ? 0 : 1;              /* lane that ends first */
+                const int sh_clean = sh ? ps[1].clean : ps[0].clean, sh_w = sh ? ps[1].w : ps[0].w;
+                const int sh_qlen = sh ? ps[1].qlen : ps[0].qlen;
+                const bool lazy = sh_clean && j >= e1 && e2 <= i + sh_w + 1;
+                if (lazy) {
+                    const uint32_t keep = sh ? 0x0000ffffu : 0xffff0000u;
+                    cut = sh; h1cut = half_s(h1, sh);
+                    f &= keep;
+                    if (e1 == sh_qlen) h1 &= keep;                  /* entry qlen is never read: keep it zero */
+                    bsw_sweep<S>(r, he, qs, j, e2, f, h1, key);
+                } else {
+                    for (; j < e2; ++j) BSW_CELL_MASKED(j)
+                }
             }
-            j = c1;
+        } else {
+            /* the other lane is dead and zeroed */
+            bsw_sweep<S>(r, he, qs, ps[0].act ? sp[0] : sp[1], ps[0].act ? ep[0] : ep[1], f, h1, key);
         }
-        if (j < c0) j = c0;            /* nothing lives in [c1, c0) when the ranges are disjoint */
-        for (; j < jhi; ++j) BSW_CELL_MASKED(j)
 #undef BSW_CELL_MASKED
 
         /* ---- per-pair row epilogue (A.1) ---- */
+        died = 0;
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             PState &s = ps[p];
             if (!s.act) continue;
             const uint32_t hm = p ? 0xffff0000u : 0x0000ffffu;
-            const int h1p = half_s(h1, p);
+            const int h1p = (cut == p) ? h1cut : half_s(h1, p);
             const int kp = half_u(key, p);
             const int m = kp >> 8, mj = kp & 0xff;
-            {   /* eh[end].h = h1; eh[end].e = 0 */
+            if (cut != p) {   /* eh[end].h = h1; eh[end].e = 0 (a cut lane wrote it during the lazy sweep) */
                 uint2 v = he[s.end * S];
-                v.x = (v.x & ~hm) | (h1 & hm);
+                v.x = (v.x & ~hm) | ((s.end == s.qlen && s.clean) ? 0u : (pack2(h1p, h1p) & hm));
                 v.y = v.y & ~hm;
                 he[s.end * S] = v;
             }
-            const int jafter = s.beg < s.end ? s.end : s.beg;
-            if (jafter == s.qlen) {
+            if (s.end == s.qlen) {         /* a computing lane has beg < end, so A.1's j after the loop is end */
                 s.max_ie = s.gscore > h1p ? s.max_ie : i;
                 s.gscore = s.gscore > h1p ? s.gscore : h1p;
             }
-            if (m == 0) { s.act = 0; continue; }
-            if (m > s.max) {
-                int off = mj - i; off = off < 0 ? -off : off;
-                s.max = m; s.max_i = i; s.max_j = mj;
-                s.max_off = s.max_off > off ? s.max_off : off;
-            } else if (c.zdrop > 0) {
-                const int di = i - s.max_i, dj = mj - s.max_j;
-                if (di > dj) { if (s.max - m - (di - dj) * c.e_del > c.zdrop) { s.act = 0; continue; } }
-                else         { if (s.max - m - (dj - di) * c.e_ins > c.zdrop) { s.act = 0; continue; } }
+            bool stop = (m == 0);
+            if (!stop) {
+                if (m > s.max) {
+                    int off = mj - i; off = off < 0 ? -off : off;
+                    s.max = m; s.max_i = i; s.max_j = mj;
+                    s.max_off = s.max_off > off ? s.max_off : off;
+                } else if (c.zdrop > 0) {
+                    const int di = i - s.max_i, dj = mj - s.max_j;
+                    if (di > dj) stop = s.max - m - (di - dj) * c.e_del > c.zdrop;
+                    else         stop = s.max - m - (dj - di) * c.e_ins > c.zdrop;
+                }
             }
-            int jj = s.beg;
-            while (jj < s.end) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; ++jj; }
-            s.beg = jj;
-            jj = s.end;
-            while (jj >= s.beg) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; --jj; }
-            s.end = jj + 2 < s.qlen ? jj + 2 : s.qlen;
-            if (i + 1 >= s.tlen) s.act = 0;
+            if (!stop) {
+                if (COUNT) {
+                    int jj = s.beg;
+                    while (jj < s.end) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; ++jj; }
+                    s.beg = jj;
+                }
+                int jj = s.end;
+                if (h1p == 0) {
+                    /* m > 0 guarantees a non-zero entry at or right of the sweep start */
+                    --jj;
+                    while (jj >= 0) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; --jj; }
+                }
+                s.end = jj + 2 < s.qlen ? jj + 2 : s.qlen;
+                if (i + 1 >= s.tlen) stop = true;
+            }
+            if (stop) { s.act = 0; died |= 1 << p; }
+        }
+        if (died) {
+            if (!(ps[0].act | ps[1].act)) break;
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+                if (died & (1 << p)) {
+                    const uint32_t keep = p ? 0x0000ffffu : 0xffff0000u;
+                    for (int j = 0; j <= ps[p].qlen; ++j) { uint2 v = he[j * S]; v.x &= keep; v.y &= keep; he[j * S] = v; }
+                }
+        }
+        /* lazy left trim: skip leading columns that are zero in both lanes (dead lanes are zero) */
+        {
+            const int lim = mn(ps[0].act ? ps[0].end : BIG, ps[1].act ? ps[1].end : BIG);
+            int steps = 0;
+            while (steps < 4 && t < lim) { uint2 v = he[t * S]; if (v.x | v.y) break; ++t; ++steps; }
         }
         ++i;
     }

@@ -7,10 +7,11 @@
  *                       per-bin histogram (bin = 16 query columns).
  *   2. cub radix sort   descending: longest queries first (heavy tiles first),
  *                       pairs the packed kernel does not admit last (key 0).
- *   3. plan_kernel      bin offsets -> tile table.  A tile = W warps x 64 pairs of
- *                       one bin; W = how many warps' DP rows fit the block's
- *                       shared memory at that query length.
- *   4. *_packed_kernel  persistent blocks pull tiles from an atomic counter.
+ *   3. histogram read-back (one 200-byte D2H): the host derives each bin's sorted range.
+ *   4. *_packed_kernel  one launch per non-empty bin, longest queries first.  A block is ONE
+ *                       warp = 64 pairs (2 per thread); its dynamic shared memory holds exactly
+ *                       that bin's DP rows (NE x 320 B), so the number of resident warps per SM
+ *                       is set by the query length, with no block-level barrier anywhere.
  *   5. *_general_kernel 32-bit path for the (rare) pairs step 1 did not admit.
  */
 #pragma once
@@ -31,12 +32,6 @@ struct Plan {
     int max_len1;                  /* over all pairs                      */
     int max_len2_general;
     int bad_pairs;                 /* contract violations seen by prep    */
-    int bin_start[BSW_NBINS + 2];  /* sorted position where bin qb starts (descending qb) */
-    int bin_warps[BSW_NBINS + 2];
-    int tile_prefix[BSW_NBINS + 2];/* tiles before bin qb (descending order) */
-    int ntiles, n_packed;
-    unsigned int tile_counter;
-    unsigned int pad_;
 };
 
 enum { MODE_BSW = 0, MODE_KSWV = 1 };
@@ -81,38 +76,6 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
     }
 }
 
-/* ------------------------------------------------------------------ 3. plan */
-__global__ void plan_kernel(Plan *plan, int smem_bytes, int block_warps)
-{
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    int pos = 0, tiles = 0;
-    for (int qb = BSW_NBINS; qb >= 1; --qb) {
-        const int cnt = plan->hist[qb];
-        int w = smem_bytes / (qb * 16 * BSW_WARP_ELEM_BYTES);
-        w = w > block_warps ? block_warps : w;
-        w = w < 1 ? 1 : w;                       /* prep guarantees qb*16 <= max_elems, so w >= 1 */
-        plan->bin_start[qb] = pos;
-        plan->bin_warps[qb] = w;
-        plan->tile_prefix[qb] = tiles;
-        pos += cnt;
-        tiles += (cnt + 64 * w - 1) / (64 * w);
-    }
-    plan->bin_start[0] = pos; plan->tile_prefix[0] = tiles;
-    plan->ntiles = tiles; plan->n_packed = pos;
-}
-
-/* tile -> (qb, first sorted slot, end slot of bin, warps) */
-__device__ __forceinline__ bool tile_lookup(const Plan *plan, int tile, int &qb, int &base, int &bin_end, int &W)
-{
-    if (tile >= plan->ntiles) return false;
-    qb = BSW_NBINS;
-    while (qb > 1 && tile >= plan->tile_prefix[qb - 1]) --qb;
-    W = plan->bin_warps[qb];
-    base = plan->bin_start[qb] + (tile - plan->tile_prefix[qb]) * 64 * W;
-    bin_end = plan->bin_start[qb - 1];
-    return true;
-}
-
 __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pairs, int pi)
 {
     PairIn p;
@@ -123,47 +86,37 @@ __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pa
 }
 
 /* ------------------------------------------------------------------ 4a. BSW packed */
-__global__ void __launch_bounds__(512, 1)
+template <bool COUNT>
+__global__ void __launch_bounds__(32)
 bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
-                  Plan *plan, Const c, int w, unsigned long long *cells)
+                  int first, int bin_end, int NE, Const c, int w, unsigned long long *cells)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_tile;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lane = threadIdx.x;
+    uint2 *he = reinterpret_cast<uint2 *>(smem) + lane;
+    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 256) + lane;
+    const int slot = first + blockIdx.x * 64 + lane * 2;
+    const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
+    const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
     unsigned long long my_cells = 0;
-    for (;;) {
-        if (threadIdx.x == 0) s_tile = (int)atomicAdd(&plan->tile_counter, 1u);
-        __syncthreads();
-        const int tile = s_tile;
-        __syncthreads();
-        int qb, base, bin_end, W;
-        if (!tile_lookup(plan, tile, qb, base, bin_end, W)) break;
-        if (warp < W) {
-            const int NE = qb * 16;
-            uint8_t *region = smem + (size_t)warp * NE * BSW_WARP_ELEM_BYTES;
-            uint2 *he = reinterpret_cast<uint2 *>(region) + lane;
-            uint16_t *qs = reinterpret_cast<uint16_t *>(region + (size_t)NE * 256) + lane;
-            const int slot = base + warp * 64 + lane * 2;
-            const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
-            const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
-            if (pa >= 0) {
-                PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
-                PairOut oa, ob;
-                bsw_packed_thread<32>(c, w, A, B, ref, qer, he, qs, oa, ob);
-                int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
-                o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
-                my_cells += (unsigned long long)oa.cells;
-                if (pb >= 0) {
-                    o = reinterpret_cast<int2 *>(&pairs[pb].score);
-                    o[0] = make_int2(ob.score, ob.tle); o[1] = make_int2(ob.gtle, ob.qle); o[2] = make_int2(ob.gscore, ob.max_off);
-                    my_cells += (unsigned long long)ob.cells;
-                }
-            }
+    if (pa >= 0) {
+        PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+        PairOut oa, ob;
+        bsw_packed_thread<32, COUNT>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
+        o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
+        my_cells += (unsigned long long)oa.cells;
+        if (pb >= 0) {
+            o = reinterpret_cast<int2 *>(&pairs[pb].score);
+            o[0] = make_int2(ob.score, ob.tle); o[1] = make_int2(ob.gtle, ob.qle); o[2] = make_int2(ob.gscore, ob.max_off);
+            my_cells += (unsigned long long)ob.cells;
         }
     }
-    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
-    if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+        if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+    }
 }
 
 /* ------------------------------------------------------------------ 5a. BSW general */
@@ -200,40 +153,27 @@ __device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const b
 }
 
 /* ------------------------------------------------------------------ 4b. kswv packed */
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(32)
 kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                    const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
-                   const uint32_t *__restrict__ sorted_idx, Plan *plan, Const c, int is8, int phase,
+                   const uint32_t *__restrict__ sorted_idx, int first, int bin_end, int NE, Const c, int is8, int phase,
                    uint16_t *rowmax, long long rm_stride, unsigned long long *cells)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_tile;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lane = threadIdx.x;
+    uint2 *he = reinterpret_cast<uint2 *>(smem) + lane;
+    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 256) + lane;
+    const int slot = first + blockIdx.x * 64 + lane * 2;
+    const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
+    const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
     unsigned long long my_cells = 0;
-    for (;;) {
-        if (threadIdx.x == 0) s_tile = (int)atomicAdd(&plan->tile_counter, 1u);
-        __syncthreads();
-        const int tile = s_tile;
-        __syncthreads();
-        int qb, base, bin_end, W;
-        if (!tile_lookup(plan, tile, qb, base, bin_end, W)) break;
-        if (warp < W) {
-            const int NE = qb * 16;
-            uint8_t *region = smem + (size_t)warp * NE * BSW_WARP_ELEM_BYTES;
-            uint2 *he = reinterpret_cast<uint2 *>(region) + lane;
-            uint16_t *qs = reinterpret_cast<uint16_t *>(region + (size_t)NE * 256) + lane;
-            const int slot = base + warp * 64 + lane * 2;
-            const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
-            const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
-            if (pa >= 0) {
-                PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
-                KswOut oa, ob;
-                kswv_packed_thread<32>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
-                kswv_store(aln, pairs, pa, oa, phase);
-                my_cells += (unsigned long long)oa.cells;
-                if (pb >= 0) { kswv_store(aln, pairs, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
-            }
-        }
+    if (pa >= 0) {
+        PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+        KswOut oa, ob;
+        kswv_packed_thread<32>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
+        kswv_store(aln, pairs, pa, oa, phase);
+        my_cells += (unsigned long long)oa.cells;
+        if (pb >= 0) { kswv_store(aln, pairs, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
     }
     for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
     if (lane == 0 && my_cells) atomicAdd(cells, my_cells);

@@ -139,7 +139,8 @@ typedef struct bsw_stats {
     int64_t pairs;            /* pairs processed                             */
     int64_t pairs_packed;     /* pairs served by the packed s16x2 kernel     */
     int64_t pairs_general;    /* pairs served by the general 32-bit kernel   */
-    int64_t cells;            /* DP cells evaluated, oracle definition (8d)  */
+    int64_t cells;            /* DP cells evaluated, oracle definition (8d); BSW counts them
+                                 only while bsw_set_cell_counting(h,1) is on    */
     int64_t kernel_launches;  /* CUDA kernels launched by this library       */
     int64_t h2d_bytes, d2h_bytes;
     double  kernel_ms;        /* device time of the DP kernels (CUDA events), only
@@ -148,6 +149,9 @@ typedef struct bsw_stats {
 void bsw_get_stats(bsw_t *h, bsw_stats_t *out);
 void bsw_reset_stats(bsw_t *h);
 void bsw_set_timing(bsw_t *h, int on);
+/* exact oracle-definition DP-cell counting for BSW (tracks the exact trimmed `beg` per row;
+ * ~10% slower, results unchanged).  Off by default; BSW_CUDA_COUNT_CELLS=1 turns it on. */
+void bsw_set_cell_counting(bsw_t *h, int on);
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out);
 void kswv_reset_stats(kswv_t *h);
 void kswv_set_timing(kswv_t *h, int on);

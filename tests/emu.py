@@ -29,11 +29,11 @@ def _p(a):
 
 
 def bsw(pairs, ref, qer, w=100, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=100, end_bonus=5, a=1, b=4,
-        force_general=0):
+        force_general=0, count=True):
     out = pairs.copy()
     cells = np.zeros(len(out), np.int64)
     npk = lib().emu_bsw(_p(out), _p(ref), _p(qer), len(out), o_del, e_del, o_ins, e_ins, zdrop, end_bonus,
-                        a, b, -1, w, force_general, _p(cells))
+                        a, b, -1, w, force_general, _p(cells) if count else None)
     return out, cells, npk
 
 

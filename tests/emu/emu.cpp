@@ -29,6 +29,7 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
             int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
             int a, int b, int ambig, int w, int force_general, long long *cells_out)
 {
+    const bool count_cells = cells_out != nullptr;
     Const c = mk(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig);
     std::vector<int> el, ge;
     for (int i = 0; i < n; ++i)
@@ -40,8 +41,9 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         if (ib >= 0) B = { pairs[ib].idr, pairs[ib].idq, pairs[ib].len1, pairs[ib].len2, pairs[ib].h0, 1 };
         else B = { 0, 0, 0, 0, 0, 0 };
         int qm = A.len2 > B.len2 ? A.len2 : B.len2;
-        std::vector<uint2> he(qm + 2); std::vector<uint16_t> qs(qm + 2);
-        bsw_packed_thread<1>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+        std::vector<uint2> he(qm + 8); std::vector<uint16_t> qs(qm + 8);
+        if (count_cells) bsw_packed_thread<1, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+        else bsw_packed_thread<1, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
     }

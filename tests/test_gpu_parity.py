@@ -183,12 +183,17 @@ def test_mixed_lengths_and_cells(ora, sw):
                                           (97, 100, 200, 100, 300, 0.95), (1, 0, 0, 0, 0, 0.5), (45, 200, 255, 1, 600, 0.6))]
     P, r, q = common.concat_workloads(parts)
     o, cells = _oracle_bsw(ora, P, r, q)
-    sw.reset_stats()
-    g = P.copy()
-    sw.getScores16(g, r, q, len(g), 1, 100)
-    _assert_same(o, g)
-    st = sw.stats()
-    assert st["cells"] == int(cells.sum()) and st["pairs"] == len(P)
+    for counting in (True, False):           # the counting variant tracks the exact trimmed beg as well
+        sw.set_cell_counting(counting)
+        sw.reset_stats()
+        g = P.copy()
+        sw.getScores16(g, r, q, len(g), 1, 100)
+        _assert_same(o, g)
+        st = sw.stats()
+        assert st["pairs"] == len(P)
+        if counting:
+            assert st["cells"] == int(cells.sum())
+    sw.set_cell_counting(False)
 
 
 def test_scoring_variants(ora, bsw):

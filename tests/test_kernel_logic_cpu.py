@@ -13,9 +13,11 @@ def _check_bsw(ora, pairs, ref, qer, **kw):
     prm = ora.make_params(**{k: v for k, v in kw.items() if k != "w"})
     o = pairs.copy()
     _, oc = ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4, True)
-    for fg in (0, 1):
-        e, ec, _ = emu.bsw(pairs, ref, qer, force_general=fg, **kw)
-        bad = common.diff_fields(o, e, common.BSW_FIELDS) | (oc != ec)
+    for fg, count in ((0, True), (0, False), (1, True)):
+        e, ec, _ = emu.bsw(pairs, ref, qer, force_general=fg, count=count, **kw)
+        bad = common.diff_fields(o, e, common.BSW_FIELDS)
+        if count:
+            bad |= oc != ec
         assert not bad.any(), common.describe_first(o, e, bad)
 
 
