@@ -54,6 +54,10 @@ struct DevCtx {
     int dev = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    /* one stream per query-length bin: the bins' kernels run concurrently, so one bin's tail wave
+     * overlaps the next bin's blocks (fork/join on events around them) */
+    cudaStream_t bin_stream[BSW_NBINS + 1] = {};
+    cudaEvent_t fork_ev = nullptr, bin_ev[BSW_NBINS + 1] = {};
     int sm_count = 0, smem_optin = 0;
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax, cells;
     Plan *h_plan = nullptr;          /* pinned mailbox */
@@ -111,6 +115,16 @@ void core_init(Core &k, int mode)
         CK(cudaSetDevice(x.dev));
         CK(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
         CK(cudaEventCreate(&x.ev0)); CK(cudaEventCreate(&x.ev1));
+        {
+            int lo = 0, hi = 0;                       /* numerically lowest = highest priority */
+            CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            CK(cudaEventCreateWithFlags(&x.fork_ev, cudaEventDisableTiming));
+            for (int qb = 1; qb <= BSW_NBINS; ++qb) {
+                int pr = hi + (BSW_NBINS - qb) * (lo - hi) / BSW_NBINS;   /* long queries first */
+                CK(cudaStreamCreateWithPriority(&x.bin_stream[qb], cudaStreamNonBlocking, pr));
+                CK(cudaEventCreateWithFlags(&x.bin_ev[qb], cudaEventDisableTiming));
+            }
+        }
         CK(cudaDeviceGetAttribute(&x.sm_count, cudaDevAttrMultiProcessorCount, x.dev));
         CK(cudaDeviceGetAttribute(&x.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, x.dev));
         CK(cudaHostAlloc((void **)&x.h_plan, sizeof(Plan), cudaHostAllocDefault));
@@ -143,6 +157,8 @@ void core_destroy(Core &k)
         x.cubtmp.release(); x.plan.release(); x.scratch.release(); x.rowmax.release(); x.cells.release();
         if (x.h_plan) cudaFreeHost(x.h_plan);
         cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
+        if (x.fork_ev) cudaEventDestroy(x.fork_ev);
+        for (int qb = 1; qb <= BSW_NBINS; ++qb) { if (x.bin_stream[qb]) cudaStreamDestroy(x.bin_stream[qb]); if (x.bin_ev[qb]) cudaEventDestroy(x.bin_ev[qb]); }
         cudaStreamDestroy(x.stream);
     }
     k.ctx.clear();
@@ -198,17 +214,22 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
     const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
+    CK(cudaEventRecord(x.fork_ev, s));
     for (int qb = BSW_NBINS; qb >= 1; --qb) {            /* longest queries first */
         const int cnt = pl->hist[qb];
         if (cnt <= 0) continue;
         const int NE = qb * 16, grid = (cnt + 63) / 64;
+        cudaStream_t bs = x.bin_stream[qb];
+        CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
         if (k.count_cells)
-            bsw_packed_kernel<true><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
-                                                                             NE, k.c, w, (unsigned long long *)x.cells.p);
-        else
-            bsw_packed_kernel<false><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+            bsw_packed_kernel<true><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
                                                                               NE, k.c, w, (unsigned long long *)x.cells.p);
+        else
+            bsw_packed_kernel<false><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+                                                                               NE, k.c, w, (unsigned long long *)x.cells.p);
         CK(cudaGetLastError());
+        CK(cudaEventRecord(x.bin_ev[qb], bs));
+        CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
         k.st.kernel_launches++;
         n_packed += cnt;
     }
@@ -245,14 +266,19 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
         const long long stride = n_packed;
         x.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
         int first = 0;
+        CK(cudaEventRecord(x.fork_ev, s));
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
             const int cnt = pl->hist[qb];
             if (cnt <= 0) continue;
             const int NE = qb * 16, grid = (cnt + 63) / 64;
-            kswv_packed_kernel<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
-                                                                         k.c, is8, phase, (uint16_t *)x.rowmax.p, stride,
-                                                                         (unsigned long long *)x.cells.p);
+            cudaStream_t bs = x.bin_stream[qb];
+            CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+            kswv_packed_kernel<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
+                                                                          k.c, is8, phase, (uint16_t *)x.rowmax.p, stride,
+                                                                          (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
+            CK(cudaEventRecord(x.bin_ev[qb], bs));
+            CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
             k.st.kernel_launches++;
             first += cnt;
         }
@@ -314,8 +340,8 @@ void host_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t 
         if (s.cnt <= 0) continue;
         CK(cudaSetDevice(x.dev));
         x.pairs.reserve((size_t)s.cnt * sizeof(bsw_seqpair_t));
-        x.ref.reserve((size_t)(s.rhi - s.rlo) + 16);
-        x.qer.reserve((size_t)(s.qhi - s.qlo) + 16);
+        x.ref.reserve((size_t)(s.rhi - s.rlo) + 64);
+        x.qer.reserve((size_t)(s.qhi - s.qlo) + 64);
         CK(cudaMemcpyAsync(x.pairs.p, pairs + s.first, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, x.stream));
         if (s.rhi > s.rlo) CK(cudaMemcpyAsync(x.ref.p, ref + s.rlo, (size_t)(s.rhi - s.rlo), cudaMemcpyHostToDevice, x.stream));
         if (s.qhi > s.qlo) CK(cudaMemcpyAsync(x.qer.p, qer + s.qlo, (size_t)(s.qhi - s.qlo), cudaMemcpyHostToDevice, x.stream));

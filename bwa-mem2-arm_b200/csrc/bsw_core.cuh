@@ -25,6 +25,7 @@
  */
 #pragma once
 #include <stdint.h>
+#include <stddef.h>
 
 #if defined(__CUDACC__)
 #define BSW_HD __host__ __device__ __forceinline__
@@ -291,9 +292,18 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
     r.GATE = (uint32_t)(c.a + 1);
     const int BIG = 0x3fffffff;
 
-    uint32_t tnext[2];
+    /* target bases: aligned 32-bit words of the reference buffer, fetched one word (4 rows) ahead;
+     * reads stay within 8 bytes of the pair's last base (the boundary layer pads the buffers). */
+    uint32_t wcur[2], wnxt[2];
 #pragma unroll
-    for (int p = 0; p < 2; ++p) tnext[p] = ps[p].act ? ref[ps[p].idr] : 0u;
+    for (int p = 0; p < 2; ++p) {
+        wcur[p] = wnxt[p] = 0u;
+        if (ps[p].act) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(ref + ps[p].idr);
+            const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+            wcur[p] = wp[0]; wnxt[p] = wp[1];
+        }
+    }
 
     int t = 0;          /* lazy common start: all entries < t are zero in both lanes */
     int i = 0;
@@ -313,9 +323,15 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             const int st = t > lb[p] ? t : lb[p];
             int h1 = 0;
             if (st == 0) { h1 = s.h0 - (c.o_del + c.e_del * (i + 1)); if (h1 < 0) h1 = 0; }
-            const uint32_t tt = tnext[p];
-            tb[p] = tt > 4u ? 4u : tt;
-            if (i + 1 < s.tlen) tnext[p] = ref[s.idr + i + 1];
+            {
+                const uintptr_t adr = reinterpret_cast<uintptr_t>(ref + s.idr) + (uintptr_t)i;
+                const uint32_t tt = (wcur[p] >> (8 * (int)(adr & 3))) & 0xffu;
+                tb[p] = tt > 4u ? 4u : tt;
+                if ((adr & 3) == 3) {            /* next row starts a new word: rotate, fetch the one after */
+                    wcur[p] = wnxt[p];
+                    wnxt[p] = reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3)[2];
+                }
+            }
             if (st >= s.end) {
                 /* no cell in this row: m == 0, the lane stops here (A.1: gscore check, then break) */
                 const int jafter = lb[p] < s.end ? s.end : lb[p];
@@ -386,6 +402,22 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
         }
 #undef BSW_CELL_MASKED
 
+        /* eh[end] = { h1, 0 }.  When the sweep ended at one common column for both live lanes (equal
+         * ends, a lazily extended short lane -- whose half of h1 is 0 there --, or a single live lane
+         * next to a zeroed dead one) this is one plain store. */
+        bool plain_end = false;
+        {
+            const int ea = ps[0].act ? ep[0] : -1, eb = ps[1].act ? ep[1] : -1;
+            const int ee = ea > eb ? ea : eb;
+            const bool same = (ea < 0 || eb < 0 || ea == eb || cut >= 0);
+            if (same && ee >= 0) {
+                uint32_t hv = h1;
+                if (ps[0].act && ea == ps[0].qlen && ps[0].clean && ea == ee) hv &= 0xffff0000u;   /* entry qlen: keep zero */
+                if (ps[1].act && eb == ps[1].qlen && ps[1].clean && eb == ee) hv &= 0x0000ffffu;
+                he[ee * S] = make_uint2(hv, 0u);
+                plain_end = true;
+            }
+        }
         /* ---- per-pair row epilogue (A.1) ---- */
         died = 0;
 #pragma unroll
@@ -396,7 +428,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             const int h1p = (cut == p) ? h1cut : half_s(h1, p);
             const int kp = half_u(key, p);
             const int m = kp >> 8, mj = kp & 0xff;
-            if (cut != p) {   /* eh[end].h = h1; eh[end].e = 0 (a cut lane wrote it during the lazy sweep) */
+            if (cut != p && !plain_end) {   /* eh[end].h = h1; eh[end].e = 0 (a cut lane wrote it during the lazy sweep) */
                 uint2 v = he[s.end * S];
                 v.x = (v.x & ~hm) | ((s.end == s.qlen && s.clean) ? 0u : (pack2(h1p, h1p) & hm));
                 v.y = v.y & ~hm;

@@ -54,7 +54,11 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
         if (ok && qb * 16 > max_elems) ok = false;
         uint32_t key = 0;
         if (ok) {
-            key = ((uint32_t)(len2 + 1) << 16) | (uint32_t)(len1 > 0xffff ? 0xffff : len1);
+            /* query length major (sets the bin), then target length and h0, so that the two pairs a
+             * thread carries terminate, trim and widen alike */
+            const uint32_t l1 = (uint32_t)(len1 >> 1) > 255u ? 255u : (uint32_t)(len1 >> 1);
+            const uint32_t hh = mode == MODE_BSW ? ((uint32_t)h0 > 255u ? 255u : (uint32_t)h0) : 0u;
+            key = ((uint32_t)(len2 + 1) << 16) | (l1 << 8) | hh;
             atomicAdd(&s_hist[qb], 1);
         } else {
             atomicAdd(&s_misc[0], 1);
