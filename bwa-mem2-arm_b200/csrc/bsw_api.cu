@@ -133,7 +133,7 @@ void core_init(Core &k, int mode)
         CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
     }
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
-    /* packed kernels: one warp per block, dynamic shared memory = NE x 320 B (NE <= 256) */
+    /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
     const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
     for (DevCtx &x : k.ctx) {
         CK(cudaSetDevice(x.dev));

@@ -15,9 +15,9 @@
  *     (m, mj) = max over (h << 8 | j)        IMAD + VIMNMX.U16x2  (ties -> last j)
  * The substitution score of both lanes comes from one LOP3 + one PRMT used as
  * an 8-entry byte LUT with sign replication.
- * The DP row (H shifted by one column, E) lives in shared memory as
- * [column][thread] uint2, so every access is bank-conflict free no matter
- * which column a thread is at; rows are never re-read from HBM.
+ * The DP row (H shifted by one column, E) lives in shared memory as one 32-bit
+ * word per [column][thread] (st_pack), so every access is bank-conflict free no
+ * matter which column a thread is at; rows are never re-read from HBM.
  *
  * The functions are __host__ __device__: tests/emu builds them with g++ (DPX
  * emulated in plain C) to check the kernel logic against the oracle without a
@@ -156,13 +156,23 @@ static inline uint32_t launder(uint32_t v) { return v; }
 #endif
 
 /* one DP cell of both lanes (A.1 inner loop body) */
-BSW_HD void bsw_cell(const RowCtx &r, uint2 v, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
+/* DP row state of one column, both lanes, in ONE 32-bit word: lane A = bits 0..15, lane B = bits
+ * 16..31, each lane = H(i-1, j-1) in its low byte and E(i, j) in its high byte.  The packed kernel
+ * only admits pairs whose values fit 8 bits (packed_eligible), so nothing is lost; the row costs
+ * 4 B + a 2 B selector per column per thread of shared memory instead of 8 B + 2 B, which is what
+ * sets the number of resident warps per SM (DESIGN.md "occupancy"). */
+BSW_HD uint32_t st_h(uint32_t w) { return w & 0x00ff00ffu; }
+BSW_HD uint32_t st_e(uint32_t w) { return (w >> 8) & 0x00ff00ffu; }
+BSW_HD uint32_t st_pack(uint32_t h, uint32_t e) { return e * 256u + h; }
+
+BSW_HD void bsw_cell(const RowCtx &r, uint32_t w, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
 {
+    const uint32_t hs = st_h(w), e = st_e(w);
     const uint32_t x = p_xsel(q, r.T);
     const uint32_t s = p_perm(r.LUTLO, r.LUTHI, x);
-    const uint32_t M = p_addmin(v.x, s, v.x * r.GATE);
-    h = p_max3(M, v.y, f);
-    en = p_addmax_relu(M, r.NOD, p_add(v.y, r.NED));
+    const uint32_t M = p_addmin(hs, s, hs * r.GATE);
+    h = p_max3(M, e, f);
+    en = p_addmax_relu(M, r.NOD, p_add(e, r.NED));
     f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
 }
 
@@ -173,31 +183,31 @@ BSW_HD void bsw_cell(const RowCtx &r, uint2 v, uint32_t q, uint32_t &f, uint32_t
  * key = max over (h << 8 | j): row maximum and its LAST column (ties -> larger j).
  */
 template <int S>
-BSW_HD void bsw_sweep(const RowCtx &r, uint2 *he, const uint16_t *qs, int j0, int j1,
+BSW_HD void bsw_sweep(const RowCtx &r, uint32_t *he, const uint16_t *qs, int j0, int j1,
                       uint32_t &f, uint32_t &h1, uint32_t &key)
 {
     const int n = j1 - j0;
     if (n <= 0) return;
-    uint2 *hp = he + j0 * S;
+    uint32_t *hp = he + j0 * S;
     const uint16_t *qp = qs + j0 * S;
     const uint32_t c0 = (uint32_t)j0 * 0x00010001u, c1 = c0 + 0x00010001u, c2 = c0 + 0x00020002u, c3 = c0 + 0x00030003u;
     int k = 0;
 #define BSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                              \
     {                                                                                          \
         uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                               \
-        bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = make_uint2(h1, ea);                  \
-        bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = make_uint2(ha, eb);                  \
-        bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = make_uint2(hb, ec);                  \
-        bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = make_uint2(hc, ed);                  \
+        bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);                  \
+        bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);                  \
+        bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);                  \
+        bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);                  \
         h1 = hd;                                                                               \
         const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
         key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                                      \
     }
     if (n >= 4) {
-        uint2 v0 = hp[0], v1 = hp[S], v2 = hp[2 * S], v3 = hp[3 * S];
+        uint32_t v0 = hp[0], v1 = hp[S], v2 = hp[2 * S], v3 = hp[3 * S];
         uint32_t q0 = qp[0], q1 = qp[S], q2 = qp[2 * S], q3 = qp[3 * S];
         while (k + 8 <= n) {
-            const uint2 w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
+            const uint32_t w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
             const uint32_t r0 = qp[(k + 4) * S], r1 = qp[(k + 5) * S], r2 = qp[(k + 6) * S], r3 = qp[(k + 7) * S];
             BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
             v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
@@ -210,14 +220,14 @@ BSW_HD void bsw_sweep(const RowCtx &r, uint2 *he, const uint16_t *qs, int j0, in
     for (; k < n; ++k) {
         uint32_t h, en;
         bsw_cell(r, hp[k * S], qp[k * S], f, h, en);
-        hp[k * S] = make_uint2(h1, en);
+        hp[k * S] = st_pack(h1, en);
         h1 = h;
         key = p_maxu(key, (h << 8) + c0 + (uint32_t)k * 0x00010001u);
     }
 }
 
 /*
- * One thread, two pairs.  he[j*S] = { H(i-1, j-1) packed, E(i, j) packed },
+ * One thread, two pairs.  he[j*S] = row state word of column j (see st_pack),
  * qs[j*S] = PRMT selector of query column j for both lanes.  S = element stride
  * (32 in the kernel: [column][lane]).
  *
@@ -235,7 +245,7 @@ BSW_HD void bsw_sweep(const RowCtx &r, uint2 *he, const uint16_t *qs, int j0, in
 template <int S, bool COUNT>
 BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                               const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                              uint2 *he, uint16_t *qs, PairOut &oa, PairOut &ob)
+                              uint32_t *he, uint16_t *qs, PairOut &oa, PairOut &ob)
 {
     PState ps[2];
     const PairIn *in[2] = { &A, &B };
@@ -272,7 +282,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             hp0 = hv[0]; hp1 = hv[1];
             if (hv[0]) lastnz0 = j;
             if (hv[1]) lastnz1 = j;
-            he[j * S] = make_uint2(pack2(hv[0], hv[1]), 0u);
+            he[j * S] = pack2(hv[0], hv[1]);
             uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
             uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
             qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
@@ -351,7 +361,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             for (int p = 0; p < 2; ++p)
                 if (died & (1 << p)) {
                     const uint32_t keep = p ? 0x0000ffffu : 0xffff0000u;
-                    for (int j = 0; j <= ps[p].qlen; ++j) { uint2 v = he[j * S]; v.x &= keep; v.y &= keep; he[j * S] = v; }
+                    for (int j = 0; j <= ps[p].qlen; ++j) he[j * S] &= keep;
                 }
         }
         r.T = tb[0] * 0x0011u | tb[1] * 0x1100u;
@@ -364,10 +374,10 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             const int j_ = (J);                                                         \
             const uint32_t MK = ((j_ >= sp[0] && j_ < ep[0]) ? 0x0000ffffu : 0u) |      \
                                 ((j_ >= sp[1] && j_ < ep[1]) ? 0xffff0000u : 0u);       \
-            uint2 v = he[j_ * S];                                                       \
+            const uint32_t v = he[j_ * S];                                              \
             uint32_t h_, en, fn = f;                                                    \
             bsw_cell(r, v, qs[j_ * S], fn, h_, en);                                     \
-            he[j_ * S] = make_uint2((h1 & MK) | (v.x & ~MK), (en & MK) | (v.y & ~MK));  \
+            he[j_ * S] = st_pack(h1 & MK, en & MK) | (v & ~MK);                         \
             f = fn & MK;                                                                \
             h1 = (h_ & MK) | (h1 & ~MK);                                                \
             key = p_maxu(key, (((h_ & MK) << 8) + ((uint32_t)j_ * 0x00010001u)) & MK);  \
@@ -414,7 +424,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 uint32_t hv = h1;
                 if (ps[0].act && ea == ps[0].qlen && ps[0].clean && ea == ee) hv &= 0xffff0000u;   /* entry qlen: keep zero */
                 if (ps[1].act && eb == ps[1].qlen && ps[1].clean && eb == ee) hv &= 0x0000ffffu;
-                he[ee * S] = make_uint2(hv, 0u);
+                he[ee * S] = hv;
                 plain_end = true;
             }
         }
@@ -429,10 +439,8 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             const int kp = half_u(key, p);
             const int m = kp >> 8, mj = kp & 0xff;
             if (cut != p && !plain_end) {   /* eh[end].h = h1; eh[end].e = 0 (a cut lane wrote it during the lazy sweep) */
-                uint2 v = he[s.end * S];
-                v.x = (v.x & ~hm) | ((s.end == s.qlen && s.clean) ? 0u : (pack2(h1p, h1p) & hm));
-                v.y = v.y & ~hm;
-                he[s.end * S] = v;
+                const uint32_t v = he[s.end * S];
+                he[s.end * S] = (v & ~hm) | ((s.end == s.qlen && s.clean) ? 0u : (pack2(h1p, h1p) & hm));
             }
             if (s.end == s.qlen) {         /* a computing lane has beg < end, so A.1's j after the loop is end */
                 s.max_ie = s.gscore > h1p ? s.max_ie : i;
@@ -453,14 +461,14 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             if (!stop) {
                 if (COUNT) {
                     int jj = s.beg;
-                    while (jj < s.end) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; ++jj; }
+                    while (jj < s.end) { if (he[jj * S] & hm) break; ++jj; }
                     s.beg = jj;
                 }
                 int jj = s.end;
                 if (h1p == 0) {
                     /* m > 0 guarantees a non-zero entry at or right of the sweep start */
                     --jj;
-                    while (jj >= 0) { uint2 v = he[jj * S]; if ((v.x | v.y) & hm) break; --jj; }
+                    while (jj >= 0) { if (he[jj * S] & hm) break; --jj; }
                 }
                 s.end = jj + 2 < s.qlen ? jj + 2 : s.qlen;
                 if (i + 1 >= s.tlen) stop = true;
@@ -473,14 +481,14 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             for (int p = 0; p < 2; ++p)
                 if (died & (1 << p)) {
                     const uint32_t keep = p ? 0x0000ffffu : 0xffff0000u;
-                    for (int j = 0; j <= ps[p].qlen; ++j) { uint2 v = he[j * S]; v.x &= keep; v.y &= keep; he[j * S] = v; }
+                    for (int j = 0; j <= ps[p].qlen; ++j) he[j * S] &= keep;
                 }
         }
         /* lazy left trim: skip leading columns that are zero in both lanes (dead lanes are zero) */
         {
             const int lim = mn(ps[0].act ? ps[0].end : BIG, ps[1].act ? ps[1].end : BIG);
             int steps = 0;
-            while (steps < 4 && t < lim) { uint2 v = he[t * S]; if (v.x | v.y) break; ++t; ++steps; }
+            while (steps < 4 && t < lim) { if (he[t * S]) break; ++t; ++steps; }
         }
         ++i;
     }

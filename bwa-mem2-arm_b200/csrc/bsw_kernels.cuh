@@ -10,7 +10,7 @@
  *   3. histogram read-back (one 200-byte D2H): the host derives each bin's sorted range.
  *   4. *_packed_kernel  one launch per non-empty bin, longest queries first.  A block is ONE
  *                       warp = 64 pairs (2 per thread); its dynamic shared memory holds exactly
- *                       that bin's DP rows (NE x 320 B), so the number of resident warps per SM
+ *                       that bin's DP rows (NE x 192 B), so the number of resident warps per SM
  *                       is set by the query length, with no block-level barrier anywhere.
  *   5. *_general_kernel 32-bit path for the (rare) pairs step 1 did not admit.
  */
@@ -24,7 +24,7 @@
 namespace bswk {
 
 #define BSW_NBINS 16            /* bins of 16 elements: up to 256 elements per thread */
-#define BSW_WARP_ELEM_BYTES 320 /* per element per warp: 32 x (uint2 + uint16)        */
+#define BSW_WARP_ELEM_BYTES 192 /* per element per warp: 32 x (state word + uint16 selector) */
 
 struct Plan {
     int hist[BSW_NBINS + 2];       /* [qb] = packed-admissible pairs with ceil((len2+1)/16) == qb */
@@ -98,8 +98,8 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int lane = threadIdx.x;
-    uint2 *he = reinterpret_cast<uint2 *>(smem) + lane;
-    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 256) + lane;
+    uint32_t *he = reinterpret_cast<uint32_t *>(smem) + lane;
+    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 128) + lane;
     const int slot = first + blockIdx.x * 64 + lane * 2;
     const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
     const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
@@ -165,8 +165,8 @@ kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__res
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int lane = threadIdx.x;
-    uint2 *he = reinterpret_cast<uint2 *>(smem) + lane;
-    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 256) + lane;
+    uint32_t *he = reinterpret_cast<uint32_t *>(smem) + lane;
+    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 128) + lane;
     const int slot = first + blockIdx.x * 64 + lane * 2;
     const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
     const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;

@@ -55,13 +55,13 @@ struct KState {
 };
 
 /*
- * he[j*S] = { H(i-1, j) packed, E(i, j) packed }, qs[j*S] = selector,
+ * he[j*S] = row state word (st_pack: H(i-1, j) low byte, E(i, j) high byte of each lane), qs[j*S] = selector,
  * rm[i*RS] = imaxA | imaxB << 8 (this thread's slot of the row-max scratch).
  */
 template <int S>
 BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const PairIn &B,
                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                               uint2 *he, uint16_t *qs, uint16_t *rm, long long RS,
+                               uint32_t *he, uint16_t *qs, uint16_t *rm, long long RS,
                                KswOut &oa, KswOut &ob)
 {
     KState ks[2];
@@ -82,7 +82,7 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
     }
     const int qmin = mn(ks[0].qlen, ks[1].qlen), qmax = mx(ks[0].qlen, ks[1].qlen);
     for (int j = 0; j < qmax; ++j) {
-        he[j * S] = make_uint2(0u, 0u);
+        he[j * S] = 0u;
         uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
         uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
         qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
@@ -109,15 +109,16 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
         if (ACT == 0xffffffffu) {
 #pragma unroll 4
             for (; j < qmin; ++j) {
-                uint2 v = he[j * S];
+                const uint32_t wv = he[j * S];
+                const uint32_t ve = st_e(wv);
                 uint32_t q_ = qs[j * S];
                 uint32_t x_ = p_xsel(q_, T);
                 uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-                uint32_t h_ = p_max3_relu(p_add(hd, s_), v.y, f);
-                uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL));
+                uint32_t h_ = p_max3_relu(p_add(hd, s_), ve, f);
+                uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(ve, NEG_E_DEL));
                 f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS));
-                hd = v.x;
-                he[j * S] = make_uint2(h_, en);
+                hd = st_h(wv);
+                he[j * S] = st_pack(h_, en);
                 key = p_maxu(key, (h_ << 8) + jv);
                 jv -= 0x00010001u;
             }
@@ -125,15 +126,16 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
         /* one lane finished, or the tail of the longer query: masked cells */
         for (; j < qmax; ++j) {
             const uint32_t MK = ACT & (j < qmin ? 0xffffffffu : LONGER);
-            uint2 v = he[j * S];
+            const uint32_t wv = he[j * S];
+            const uint32_t ve = st_e(wv);
             uint32_t q_ = qs[j * S];
             uint32_t x_ = p_xsel(q_, T);
             uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-            uint32_t h_ = p_max3_relu(p_add(hd, s_), v.y, f) & MK;
-            uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(v.y, NEG_E_DEL)) & MK;
+            uint32_t h_ = p_max3_relu(p_add(hd, s_), ve, f) & MK;
+            uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(ve, NEG_E_DEL)) & MK;
             f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS)) & MK;
-            hd = v.x & MK;
-            he[j * S] = make_uint2(h_, en);
+            hd = st_h(wv) & MK;
+            he[j * S] = st_pack(h_, en);
             key = p_maxu(key, ((h_ << 8) + jv) & MK);
             jv -= 0x00010001u;
         }
