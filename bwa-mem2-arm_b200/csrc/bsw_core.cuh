@@ -161,13 +161,19 @@ static inline uint32_t launder(uint32_t v) { return v; }
  * only admits pairs whose values fit 8 bits (packed_eligible), so nothing is lost; the row costs
  * 4 B + a 2 B selector per column per thread of shared memory instead of 8 B + 2 B, which is what
  * sets the number of resident warps per SM (DESIGN.md "occupancy"). */
+#if defined(__CUDA_ARCH__)
+/* E of both lanes in one PRMT (ALU pipe); H and the re-pack as IMADs (FMA pipe, which idles here) */
+__device__ __forceinline__ uint32_t st_e(uint32_t w) { return p_perm(w, 0u, 0x4341u); }
+#else
+static inline uint32_t st_e(uint32_t w) { return (w >> 8) & 0x00ff00ffu; }
+#endif
+BSW_HD uint32_t st_h2(uint32_t w, uint32_t e) { return w - e * 256u; }
 BSW_HD uint32_t st_h(uint32_t w) { return w & 0x00ff00ffu; }
-BSW_HD uint32_t st_e(uint32_t w) { return (w >> 8) & 0x00ff00ffu; }
 BSW_HD uint32_t st_pack(uint32_t h, uint32_t e) { return e * 256u + h; }
 
 BSW_HD void bsw_cell(const RowCtx &r, uint32_t w, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
 {
-    const uint32_t hs = st_h(w), e = st_e(w);
+    const uint32_t e = st_e(w), hs = st_h2(w, e);
     const uint32_t x = p_xsel(q, r.T);
     const uint32_t s = p_perm(r.LUTLO, r.LUTHI, x);
     const uint32_t M = p_addmin(hs, s, hs * r.GATE);
@@ -176,53 +182,89 @@ BSW_HD void bsw_cell(const RowCtx &r, uint32_t w, uint32_t q, uint32_t &f, uint3
     f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
 }
 
+/* up to four cells with a bound and the f-cut check: used for the group that holds the cut column
+ * and for the final partial group of a sweep (everything else runs the unchecked BSW_GROUP) */
+template <int S>
+BSW_HD void bsw_group_generic(const RowCtx &r, uint32_t *hp, int k, int cnt, int kcut, uint32_t keepf, uint32_t keeph,
+                              uint32_t v0, uint32_t v1, uint32_t v2, uint32_t v3,
+                              uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3, uint32_t cbase,
+                              uint32_t &f, uint32_t &h1, uint32_t &key, uint32_t &h1save)
+{
+    const uint32_t vv[4] = { v0, v1, v2, v3 }, qq[4] = { q0, q1, q2, q3 };
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        if (c < cnt) {
+            if (k + c == kcut) { h1save = h1; f &= keepf; h1 &= keeph; }
+            uint32_t h, en;
+            bsw_cell(r, vv[c], qq[c], f, h, en);
+            hp[(k + c) * S] = st_pack(h1, en);
+            h1 = h;
+            key = p_maxu(key, (h << 8) + cbase + (uint32_t)(k + c) * 0x00010001u);
+        }
+    }
+}
+
 /*
  * Unmasked sweep of columns [j0, j1) for both lanes, software-pipelined in groups of four
- * columns: the next group's {H,E} and selectors are loaded before the current group's
+ * columns: the next group's state words and selectors are loaded before the current group's
  * dependent chain (f, h1, key) is evaluated.
  * key = max over (h << 8 | j): row maximum and its LAST column (ties -> larger j).
+ * jcut (j0 <= jcut < j1, or < 0 for none): before column jcut the running h1 is saved to h1save,
+ * f &= keepf and h1 &= keeph -- the exact right-trim cut of the lane that ends first, after which
+ * that lane sweeps on over zero-state entries.
  */
 template <int S>
-BSW_HD void bsw_sweep(const RowCtx &r, uint32_t *he, const uint16_t *qs, int j0, int j1,
-                      uint32_t &f, uint32_t &h1, uint32_t &key)
+BSW_HD void bsw_sweep_cut(const RowCtx &r, uint32_t *he, const uint16_t *qs, int j0, int j1,
+                          int jcut, uint32_t keepf, uint32_t keeph,
+                          uint32_t &f, uint32_t &h1, uint32_t &key, uint32_t &h1save)
 {
     const int n = j1 - j0;
     if (n <= 0) return;
     uint32_t *hp = he + j0 * S;
     const uint16_t *qp = qs + j0 * S;
     const uint32_t c0 = (uint32_t)j0 * 0x00010001u, c1 = c0 + 0x00010001u, c2 = c0 + 0x00020002u, c3 = c0 + 0x00030003u;
+    const int kcut = jcut - j0;                       /* relative cut column (negative: none) */
+    const int n4 = n & ~3;
     int k = 0;
+    int stop = kcut >= 0 ? (kcut & ~3) : n4;          /* unchecked groups run up to the group holding the cut */
+    for (;;) {
+        if (k < stop) {
+            uint32_t v0 = hp[k * S], v1 = hp[(k + 1) * S], v2 = hp[(k + 2) * S], v3 = hp[(k + 3) * S];
+            uint32_t q0 = qp[k * S], q1 = qp[(k + 1) * S], q2 = qp[(k + 2) * S], q3 = qp[(k + 3) * S];
 #define BSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                              \
-    {                                                                                          \
-        uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                               \
-        bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);                  \
-        bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);                  \
-        bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);                  \
-        bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);                  \
-        h1 = hd;                                                                               \
-        const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
-        key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                                      \
-    }
-    if (n >= 4) {
-        uint32_t v0 = hp[0], v1 = hp[S], v2 = hp[2 * S], v3 = hp[3 * S];
-        uint32_t q0 = qp[0], q1 = qp[S], q2 = qp[2 * S], q3 = qp[3 * S];
-        while (k + 8 <= n) {
-            const uint32_t w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
-            const uint32_t r0 = qp[(k + 4) * S], r1 = qp[(k + 5) * S], r2 = qp[(k + 6) * S], r3 = qp[(k + 7) * S];
+            {                                                                                  \
+                uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                       \
+                bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);             \
+                bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);             \
+                bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);             \
+                bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);             \
+                h1 = hd;                                                                       \
+                const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
+                key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                              \
+            }
+            while (k + 8 <= stop) {
+                const uint32_t w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
+                const uint32_t r0 = qp[(k + 4) * S], r1 = qp[(k + 5) * S], r2 = qp[(k + 6) * S], r3 = qp[(k + 7) * S];
+                BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
+                v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
+                k += 4;
+            }
             BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
-            v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
             k += 4;
-        }
-        BSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
-        k += 4;
-    }
 #undef BSW_GROUP
-    for (; k < n; ++k) {
-        uint32_t h, en;
-        bsw_cell(r, hp[k * S], qp[k * S], f, h, en);
-        hp[k * S] = st_pack(h1, en);
-        h1 = h;
-        key = p_maxu(key, (h << 8) + c0 + (uint32_t)k * 0x00010001u);
+        }
+        if (k >= n) break;
+        {   /* the group holding the cut column, or the final partial group */
+            const int cnt = n - k < 4 ? n - k : 4;
+            const uint32_t v0 = hp[k * S], q0 = qp[k * S];
+            const uint32_t v1 = cnt > 1 ? hp[(k + 1) * S] : 0u, q1 = cnt > 1 ? qp[(k + 1) * S] : 0u;
+            const uint32_t v2 = cnt > 2 ? hp[(k + 2) * S] : 0u, q2 = cnt > 2 ? qp[(k + 2) * S] : 0u;
+            const uint32_t v3 = cnt > 3 ? hp[(k + 3) * S] : 0u, q3 = cnt > 3 ? qp[(k + 3) * S] : 0u;
+            bsw_group_generic<S>(r, hp, k, cnt, kcut, keepf, keeph, v0, v1, v2, v3, q0, q1, q2, q3, c0, f, h1, key, h1save);
+            k += cnt;
+        }
+        if (k >= n) break;
+        stop = n4;
     }
 }
 
@@ -383,32 +425,42 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             key = p_maxu(key, (((h_ & MK) << 8) + ((uint32_t)j_ * 0x00010001u)) & MK);  \
         }
 
+        uint32_t h1s = 0;                          /* running h1 saved at the cut */
         if (ps[0].act && ps[1].act) {
             const int ls = mn(sp[0], sp[1]), hs = mx(sp[0], sp[1]);
             const int e1 = mn(ep[0], ep[1]), e2 = mx(ep[0], ep[1]);
-            int j = ls;
-            const int head_end = mn(hs, e2);
-            for (; j < head_end; ++j) BSW_CELL_MASKED(j)
-            if (hs < e1) { bsw_sweep<S>(r, he, qs, hs, e1, f, h1, key); j = e1; }
-            if (j < hs) j = hs;
-            if (j < e2) {
-                const int sh = ep[0] < ep[1] ? 0 : 1;              /* lane that ends first */
-                const int sh_clean = sh ? ps[1].clean : ps[0].clean, sh_w = sh ? ps[1].w : ps[0].w;
-                const int sh_qlen = sh ? ps[1].qlen : ps[0].qlen;
-                const bool lazy = sh_clean && j >= e1 && e2 <= i + sh_w + 1;
-                if (lazy) {
-                    const uint32_t keep = sh ? 0x0000ffffu : 0xffff0000u;
-                    cut = sh; h1cut = half_s(h1, sh);
-                    f &= keep;
-                    if (e1 == sh_qlen) h1 &= keep;                  /* entry qlen is never read: keep it zero */
-                    bsw_sweep<S>(r, he, qs, j, e2, f, h1, key);
-                } else {
-                    for (; j < e2; ++j) BSW_CELL_MASKED(j)
+            const int sh = ep[0] < ep[1] ? 0 : 1;                  /* lane that ends first */
+            const int sh_clean = sh ? ps[1].clean : ps[0].clean, sh_w = sh ? ps[1].w : ps[0].w;
+            const int sh_qlen = sh ? ps[1].qlen : ps[0].qlen;
+            const uint32_t keep = sh ? 0x0000ffffu : 0xffff0000u;
+            const bool lazy = e1 == e2 || (sh_clean && e2 <= i + sh_w + 1);
+            if (ls == hs && lazy && hs < e1) {
+                /* common case: one sweep, the short lane's f chain cut at its exact end */
+                const int jcut = e1 < e2 ? e1 : -1;
+                if (jcut >= 0) cut = sh;
+                bsw_sweep_cut<S>(r, he, qs, hs, e2, jcut, keep, e1 == sh_qlen ? keep : 0xffffffffu, f, h1, key, h1s);
+            } else {
+                int j = ls;
+                const int head_end = mn(hs, e2);
+                for (; j < head_end; ++j) BSW_CELL_MASKED(j)
+                if (hs < e1) { bsw_sweep_cut<S>(r, he, qs, hs, e1, -1, 0u, 0u, f, h1, key, h1s); j = e1; }
+                if (j < hs) j = hs;
+                if (j < e2) {
+                    if (lazy && j >= e1) {
+                        cut = sh; h1s = h1;
+                        f &= keep;
+                        if (e1 == sh_qlen) h1 &= keep;              /* entry qlen is never read: keep it zero */
+                        uint32_t dummy = 0;
+                        bsw_sweep_cut<S>(r, he, qs, j, e2, -1, 0u, 0u, f, h1, key, dummy);
+                    } else {
+                        for (; j < e2; ++j) BSW_CELL_MASKED(j)
+                    }
                 }
             }
+            h1cut = half_s(h1s, sh);
         } else {
             /* the other lane is dead and zeroed */
-            bsw_sweep<S>(r, he, qs, ps[0].act ? sp[0] : sp[1], ps[0].act ? ep[0] : ep[1], f, h1, key);
+            bsw_sweep_cut<S>(r, he, qs, ps[0].act ? sp[0] : sp[1], ps[0].act ? ep[0] : ep[1], -1, 0u, 0u, f, h1, key, h1s);
         }
 #undef BSW_CELL_MASKED
 
@@ -485,10 +537,10 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 }
         }
         /* lazy left trim: skip leading columns that are zero in both lanes (dead lanes are zero) */
-        {
+        if ((i & 3) == 3) {
             const int lim = mn(ps[0].act ? ps[0].end : BIG, ps[1].act ? ps[1].end : BIG);
             int steps = 0;
-            while (steps < 4 && t < lim) { if (he[t * S]) break; ++t; ++steps; }
+            while (steps < 8 && t < lim) { if (he[t * S]) break; ++t; ++steps; }
         }
         ++i;
     }
