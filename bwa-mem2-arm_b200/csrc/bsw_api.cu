@@ -50,6 +50,16 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+#define BSW_NSLOT 3
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
+    Plan *h_plan = nullptr;          /* pinned mailbox */
+    /* host-side bookkeeping of the chunk in flight */
+    int first = 0, cnt = 0; bool busy = false;
+};
+
 struct DevCtx {
     int dev = 0;
     cudaStream_t stream = nullptr;
@@ -59,8 +69,10 @@ struct DevCtx {
     cudaStream_t bin_stream[BSW_NBINS + 1] = {};
     cudaEvent_t fork_ev = nullptr, bin_ev[BSW_NBINS + 1] = {};
     int sm_count = 0, smem_optin = 0;
-    DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax, cells;
-    Plan *h_plan = nullptr;          /* pinned mailbox */
+    DevBuf cells;
+    /* in-flight chunk slots of the host-pointer path: while chunk c computes, chunk c+1 uploads and
+     * chunk c-1 downloads (one stream, one set of scratch buffers and one pinned mailbox per slot) */
+    Slot slot[BSW_NSLOT];
 };
 
 struct Core {
@@ -69,6 +81,7 @@ struct Core {
     bsw_stats_t st;
     int timing = 0;
     int count_cells = 0;
+    int chunk_pairs = 1 << 19;
     int mode = MODE_BSW;
 };
 
@@ -127,12 +140,17 @@ void core_init(Core &k, int mode)
         }
         CK(cudaDeviceGetAttribute(&x.sm_count, cudaDevAttrMultiProcessorCount, x.dev));
         CK(cudaDeviceGetAttribute(&x.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, x.dev));
-        CK(cudaHostAlloc((void **)&x.h_plan, sizeof(Plan), cudaHostAllocDefault));
-        x.plan.reserve(sizeof(Plan));
+        for (Slot &sl : x.slot) {
+            CK(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+            CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
+            sl.plan.reserve(sizeof(Plan));
+        }
         x.cells.reserve(sizeof(unsigned long long));
         CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
     }
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
+    k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
     const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
     for (DevCtx &x : k.ctx) {
@@ -152,10 +170,16 @@ void core_destroy(Core &k)
     for (DevCtx &x : k.ctx) {
         cudaSetDevice(x.dev);
         cudaStreamSynchronize(x.stream);
-        x.pairs.release(); x.ref.release(); x.qer.release(); x.aln.release();
-        x.keys_a.release(); x.keys_b.release(); x.idx_a.release(); x.idx_b.release();
-        x.cubtmp.release(); x.plan.release(); x.scratch.release(); x.rowmax.release(); x.cells.release();
-        if (x.h_plan) cudaFreeHost(x.h_plan);
+        for (Slot &sl : x.slot) {
+            if (sl.stream) cudaStreamSynchronize(sl.stream);
+            sl.pairs.release(); sl.ref.release(); sl.qer.release(); sl.aln.release();
+            sl.keys_a.release(); sl.keys_b.release(); sl.idx_a.release(); sl.idx_b.release();
+            sl.cubtmp.release(); sl.plan.release(); sl.scratch.release(); sl.rowmax.release();
+            if (sl.h_plan) cudaFreeHost(sl.h_plan);
+            if (sl.done) cudaEventDestroy(sl.done);
+            if (sl.stream) cudaStreamDestroy(sl.stream);
+        }
+        x.cells.release();
         cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
         if (x.fork_ev) cudaEventDestroy(x.fork_ev);
         for (int qb = 1; qb <= BSW_NBINS; ++qb) { if (x.bin_stream[qb]) cudaStreamDestroy(x.bin_stream[qb]); if (x.bin_ev[qb]) cudaEventDestroy(x.bin_ev[qb]); }
@@ -179,7 +203,7 @@ Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_
 }
 
 /* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
-const Plan *run_plan(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
 {
     x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
     x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
@@ -206,12 +230,12 @@ const Plan *run_plan(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, int n, cu
     return x.h_plan;
 }
 
-void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+void launch_bsw(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
                 int n, int w, cudaStream_t s, int tier8_check)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, x, d_pairs, n, s, tier8_check);
-    const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
+    const Plan *pl = run_plan(k, sl, d_pairs, n, s, tier8_check);
+    const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     CK(cudaEventRecord(x.fork_ev, s));
@@ -237,11 +261,11 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
         /* bounded scratch: at most ~1 GiB of eh rows per launch */
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2);
         int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));
-        x.scratch.reserve((size_t)chunk * per_pair);
+        sl.scratch.reserve((size_t)chunk * per_pair);
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
             bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed + first, cnt,
-                                                              k.c, w, (int2 *)x.scratch.p, (unsigned long long *)x.cells.p);
+                                                              k.c, w, (int2 *)sl.scratch.p, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
         }
@@ -253,18 +277,18 @@ void launch_bsw(Core &k, DevCtx &x, bsw_seqpair_t *d_pairs, const uint8_t *d_ref
     k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
 }
 
-void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
                  bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, x, d_pairs, n, s, 0);
-    const uint32_t *sorted = (const uint32_t *)x.idx_b.p;
+    const Plan *pl = run_plan(k, sl, d_pairs, n, s, 0);
+    const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     for (int qb = 1; qb <= BSW_NBINS; ++qb) n_packed += pl->hist[qb];
     if (n_packed > 0) {
         const long long stride = n_packed;
-        x.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
+        sl.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
         int first = 0;
         CK(cudaEventRecord(x.fork_ev, s));
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
@@ -274,7 +298,7 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
             cudaStream_t bs = x.bin_stream[qb];
             CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             kswv_packed_kernel<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
-                                                                          k.c, is8, phase, (uint16_t *)x.rowmax.p, stride,
+                                                                          k.c, is8, phase, (uint16_t *)sl.rowmax.p, stride,
                                                                           (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             CK(cudaEventRecord(x.bin_ev[qb], bs));
@@ -286,9 +310,9 @@ void launch_kswv(Core &k, DevCtx &x, const bsw_seqpair_t *d_pairs, const uint8_t
     if (pl->n_general > 0) {
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
         int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));
-        x.scratch.reserve((size_t)chunk * per_pair);
-        int2 *he = (int2 *)x.scratch.p;
-        int *rm = (int *)((char *)x.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
+        sl.scratch.reserve((size_t)chunk * per_pair);
+        int2 *he = (int2 *)sl.scratch.p;
+        int *rm = (int *)((char *)sl.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
             kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, n_packed + first, cnt,
@@ -316,87 +340,124 @@ void extents(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long lo
     if (qhi <= qlo) { qlo = 0; qhi = 0; }
 }
 
-/* host-pointer call: shard, copy in, compute, copy out.  Synchronous. */
-void host_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
-               int n, int w, int is8, int phase, int tier8_check)
+/* ---- BSW host-pointer call: chunked, pipelined, sharded ---------------------------------------
+ * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
+ * devices.  Each chunk uploads only the byte ranges of the sequence buffers its pairs touch, so the
+ * H2D copy of chunk c+1 and the D2H copy of chunk c-1 overlap the kernels of chunk c (three slots per
+ * device).  Results land directly in the caller's SeqPair array.  Synchronous on return. */
+void slot_retire(Core &k, DevCtx &x, Slot &sl)
+{
+    if (!sl.busy) return;
+    CK(cudaSetDevice(x.dev));
+    CK(cudaEventSynchronize(sl.done));
+    sl.busy = false;
+    (void)k;
+}
+
+void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check)
 {
     k.st.calls++;
     if (n <= 0) return;
     if (!pairs || !ref || !qer) die("null buffer passed to getScores");
     const int nd = (int)k.ctx.size();
-    struct Slice { int first, cnt; long long rlo, rhi, qlo, qhi; };
+    const int chunk = std::max(1024, k.chunk_pairs);
+    int ci = 0;
+    for (int first = 0; first < n; first += chunk, ++ci) {
+        const int cnt = std::min(chunk, n - first);
+        DevCtx &x = k.ctx[ci % nd];
+        Slot &sl = x.slot[(ci / nd) % BSW_NSLOT];
+        slot_retire(k, x, sl);                    /* its previous chunk must have landed */
+        long long rlo, rhi, qlo, qhi;
+        extents(pairs, first, cnt, rlo, rhi, qlo, qhi);
+        CK(cudaSetDevice(x.dev));
+        sl.pairs.reserve((size_t)cnt * sizeof(bsw_seqpair_t));
+        sl.ref.reserve((size_t)(rhi - rlo) + 64);
+        sl.qer.reserve((size_t)(qhi - qlo) + 64);
+        CK(cudaMemcpyAsync(sl.pairs.p, pairs + first, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
+        if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
+        if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
+        k.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
+        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
+        launch_bsw(k, x, sl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - rlo, (const uint8_t *)sl.qer.p - qlo,
+                   cnt, w, sl.stream, tier8_check);
+        CK(cudaMemcpyAsync(pairs + first, sl.pairs.p, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, sl.stream));
+        CK(cudaEventRecord(sl.done, sl.stream));
+        sl.busy = true;
+        k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t);
+    }
+    for (DevCtx &x : k.ctx)
+        for (Slot &sl : x.slot) slot_retire(k, x, sl);
+}
+
+/* ---- kswv host-pointer call: one slice per device (slot 0), synchronous -------------------------- */
+void host_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
+                    int n, int is8, int phase)
+{
+    k.st.calls++;
+    if (n <= 0) return;
+    if (!pairs || !ref || !qer || !aln) die("null buffer passed to kswv getScores");
+    const int nd = (int)k.ctx.size();
+    struct Slice { int first, cnt; long long rlo, rhi, qlo, qhi; int alo, ahi; };
     std::vector<Slice> sl(nd);
     for (int d = 0; d < nd; ++d) {
-        sl[d].first = (int)((long long)n * d / nd);
-        sl[d].cnt = (int)((long long)n * (d + 1) / nd) - sl[d].first;
-        if (sl[d].cnt > 0) extents(pairs, sl[d].first, sl[d].cnt, sl[d].rlo, sl[d].rhi, sl[d].qlo, sl[d].qhi);
-    }
-    /* kswv phase 1 refines aln[regid]: regid may point anywhere in aln, so every device gets the
-     * entries its slice names (we send the span [min regid, max regid]). */
-    std::vector<std::pair<int, int>> aspan(nd, {0, 0});
-    for (int d = 0; d < nd; ++d) {
-        DevCtx &x = k.ctx[d];
-        const Slice &s = sl[d];
+        Slice &s = sl[d];
+        s.first = (int)((long long)n * d / nd);
+        s.cnt = (int)((long long)n * (d + 1) / nd) - s.first;
         if (s.cnt <= 0) continue;
+        extents(pairs, s.first, s.cnt, s.rlo, s.rhi, s.qlo, s.qhi);
+        DevCtx &x = k.ctx[d];
+        Slot &t = x.slot[0];
         CK(cudaSetDevice(x.dev));
-        x.pairs.reserve((size_t)s.cnt * sizeof(bsw_seqpair_t));
-        x.ref.reserve((size_t)(s.rhi - s.rlo) + 64);
-        x.qer.reserve((size_t)(s.qhi - s.qlo) + 64);
-        CK(cudaMemcpyAsync(x.pairs.p, pairs + s.first, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, x.stream));
-        if (s.rhi > s.rlo) CK(cudaMemcpyAsync(x.ref.p, ref + s.rlo, (size_t)(s.rhi - s.rlo), cudaMemcpyHostToDevice, x.stream));
-        if (s.qhi > s.qlo) CK(cudaMemcpyAsync(x.qer.p, qer + s.qlo, (size_t)(s.qhi - s.qlo), cudaMemcpyHostToDevice, x.stream));
+        t.pairs.reserve((size_t)s.cnt * sizeof(bsw_seqpair_t));
+        t.ref.reserve((size_t)(s.rhi - s.rlo) + 64);
+        t.qer.reserve((size_t)(s.qhi - s.qlo) + 64);
+        CK(cudaMemcpyAsync(t.pairs.p, pairs + s.first, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, t.stream));
+        if (s.rhi > s.rlo) CK(cudaMemcpyAsync(t.ref.p, ref + s.rlo, (size_t)(s.rhi - s.rlo), cudaMemcpyHostToDevice, t.stream));
+        if (s.qhi > s.qlo) CK(cudaMemcpyAsync(t.qer.p, qer + s.qlo, (size_t)(s.qhi - s.qlo), cudaMemcpyHostToDevice, t.stream));
         k.st.h2d_bytes += (int64_t)s.cnt * sizeof(bsw_seqpair_t) + (s.rhi - s.rlo) + (s.qhi - s.qlo);
-        if (k.mode == MODE_KSWV) {
-            if (!aln) die("null aln passed to kswv getScores");
-            if (phase == 0) { aspan[d] = { s.first, s.first + s.cnt }; x.aln.reserve((size_t)s.cnt * sizeof(bsw_kswr_t)); }
-            else {
-                int lo = 0x7fffffff, hi = -1;
-                for (int i = s.first; i < s.first + s.cnt; ++i) { lo = std::min(lo, pairs[i].regid); hi = std::max(hi, pairs[i].regid); }
-                if (lo < 0) die("kswv phase 1: negative regid");
-                aspan[d] = { lo, hi + 1 };
-                x.aln.reserve((size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t));
-                CK(cudaMemcpyAsync(x.aln.p, aln + lo, (size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t), cudaMemcpyHostToDevice, x.stream));
-                k.st.h2d_bytes += (int64_t)(hi + 1 - lo) * sizeof(bsw_kswr_t);
-            }
+        if (phase == 0) { s.alo = s.first; s.ahi = s.first + s.cnt; t.aln.reserve((size_t)s.cnt * sizeof(bsw_kswr_t)); }
+        else {
+            /* phase 1 refines aln[regid]: send the span [min regid, max regid] this slice names */
+            int lo = 0x7fffffff, hi = -1;
+            for (int i = s.first; i < s.first + s.cnt; ++i) { lo = std::min(lo, pairs[i].regid); hi = std::max(hi, pairs[i].regid); }
+            if (lo < 0) die("kswv phase 1: negative regid");
+            s.alo = lo; s.ahi = hi + 1;
+            t.aln.reserve((size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t));
+            CK(cudaMemcpyAsync(t.aln.p, aln + lo, (size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t), cudaMemcpyHostToDevice, t.stream));
+            k.st.h2d_bytes += (int64_t)(hi + 1 - lo) * sizeof(bsw_kswr_t);
         }
     }
     for (int d = 0; d < nd; ++d) {
-        DevCtx &x = k.ctx[d];
         const Slice &s = sl[d];
         if (s.cnt <= 0) continue;
+        DevCtx &x = k.ctx[d];
+        Slot &t = x.slot[0];
         CK(cudaSetDevice(x.dev));
-        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
-        const uint8_t *d_ref = (const uint8_t *)x.ref.p - s.rlo;
-        const uint8_t *d_qer = (const uint8_t *)x.qer.p - s.qlo;
-        if (k.mode == MODE_BSW) {
-            launch_bsw(k, x, (bsw_seqpair_t *)x.pairs.p, d_ref, d_qer, s.cnt, w, x.stream, tier8_check);
-            CK(cudaMemcpyAsync(pairs + s.first, x.pairs.p, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, x.stream));
-            k.st.d2h_bytes += (int64_t)s.cnt * sizeof(bsw_seqpair_t);
+        const uint8_t *d_ref = (const uint8_t *)t.ref.p - s.rlo;
+        const uint8_t *d_qer = (const uint8_t *)t.qer.p - s.qlo;
+        /* phase 0 indexes aln by slice-local pair index; phase 1 by regid, rebased to the span */
+        bsw_kswr_t *d_aln = (bsw_kswr_t *)t.aln.p - (phase == 0 ? 0 : s.alo);
+        launch_kswv(k, x, t, (const bsw_seqpair_t *)t.pairs.p, d_ref, d_qer, d_aln, s.cnt, is8, phase, t.stream);
+        const size_t cnt = (size_t)(s.ahi - s.alo);
+        if (phase == 0) {
+            CK(cudaMemcpyAsync(aln + s.alo, t.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, t.stream));
         } else {
-            /* phase 0 indexes aln by slice-local pair index; phase 1 by regid, rebased to the span */
-            bsw_kswr_t *d_aln = (bsw_kswr_t *)x.aln.p - (phase == 0 ? 0 : aspan[d].first);
-            launch_kswv(k, x, (const bsw_seqpair_t *)x.pairs.p, d_ref, d_qer, d_aln, s.cnt, is8, phase, x.stream);
-            size_t cnt = (size_t)(aspan[d].second - aspan[d].first);
-            if (phase == 0) {
-                CK(cudaMemcpyAsync(aln + aspan[d].first, x.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, x.stream));
-            } else {
-                /* only tb/qb of the named entries change; copy back through a bounce so other devices'
-                 * entries inside the span are not clobbered */
-                std::vector<bsw_kswr_t> tmp(cnt);
-                CK(cudaMemcpyAsync(tmp.data(), x.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, x.stream));
-                CK(cudaStreamSynchronize(x.stream));
-                for (int i = s.first; i < s.first + s.cnt; ++i) {
-                    int r = pairs[i].regid;
-                    aln[r].tb = tmp[r - aspan[d].first].tb; aln[r].qb = tmp[r - aspan[d].first].qb;
-                }
+            /* only tb/qb of the named entries change; copy back through a bounce so that entries of
+             * other devices inside the span are not clobbered */
+            std::vector<bsw_kswr_t> tmp(cnt);
+            CK(cudaMemcpyAsync(tmp.data(), t.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, t.stream));
+            CK(cudaStreamSynchronize(t.stream));
+            for (int i = s.first; i < s.first + s.cnt; ++i) {
+                const int r = pairs[i].regid;
+                aln[r].tb = tmp[r - s.alo].tb; aln[r].qb = tmp[r - s.alo].qb;
             }
-            k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_kswr_t);
         }
+        k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_kswr_t);
     }
     for (int d = 0; d < nd; ++d) {
         if (sl[d].cnt <= 0) continue;
         CK(cudaSetDevice(k.ctx[d].dev));
-        CK(cudaStreamSynchronize(k.ctx[d].stream));
+        CK(cudaStreamSynchronize(k.ctx[d].slot[0].stream));
     }
 }
 
@@ -432,21 +493,21 @@ void bsw_getScores8(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef
                     int32_t numPairs, uint16_t numThreads, int32_t w)
 {
     (void)numThreads;
-    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 1);
+    host_call_bsw(h->k, pairArray, seqBufRef, seqBufQer, numPairs, w, 1);
 }
 
 void bsw_getScores16(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
                      int32_t numPairs, uint16_t numThreads, int32_t w)
 {
     (void)numThreads;
-    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 0);
+    host_call_bsw(h->k, pairArray, seqBufRef, seqBufQer, numPairs, w, 0);
 }
 
 void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
                                 int32_t numPairs, int nthreads, int32_t w)
 {
     (void)nthreads;
-    host_call(h->k, pairArray, seqBufRef, seqBufQer, nullptr, numPairs, w, 0, 0, 0);
+    host_call_bsw(h->k, pairArray, seqBufRef, seqBufQer, numPairs, w, 0);
 }
 
 void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
@@ -455,7 +516,7 @@ void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_se
     DevCtx &x = h->k.ctx[0];
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
-    launch_bsw(h->k, x, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
+    launch_bsw(h->k, x, x.slot[0], d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
 }
 
 kswv_t *kswv_create(int o_del, int e_del, int o_ins, int e_ins, int8_t w_match, int8_t w_mismatch,
@@ -475,14 +536,14 @@ void kswv_getScores8(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufR
                      bsw_kswr_t *aln, int32_t numPairs, uint16_t numThreads, int phase)
 {
     (void)numThreads;
-    host_call(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 0, 1, phase, 0);
+    host_call_kswv(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 1, phase);
 }
 
 void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
                       bsw_kswr_t *aln, int32_t numPairs, uint16_t numThreads, int phase)
 {
     (void)numThreads;
-    host_call(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 0, 0, phase, 0);
+    host_call_kswv(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, 0, phase);
 }
 
 void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
@@ -491,7 +552,7 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
     DevCtx &x = h->k.ctx[0];
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
-    launch_kswv(h->k, x, d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase, (cudaStream_t)stream);
+    launch_kswv(h->k, x, x.slot[0], d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase, (cudaStream_t)stream);
 }
 
 void *bsw_host_alloc(size_t bytes)
