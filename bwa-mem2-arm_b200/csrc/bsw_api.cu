@@ -203,7 +203,7 @@ Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_
 }
 
 /* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
-const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
 {
     x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
     x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
@@ -220,8 +220,13 @@ const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cuda
     CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
                                                  (uint32_t *)x.idx_a.p, (uint32_t *)x.idx_b.p, n, 0, 25, s));
     CK(cudaMemcpyAsync(x.h_plan, d_plan, sizeof(Plan), cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
     k.st.kernel_launches += 1 + 8;    /* prep + the sort's internal launches (upper bound of cub's onesweep path) */
+}
+
+/* blocks until the histogram of plan_enqueue has landed in the slot's pinned mailbox */
+const Plan *plan_wait(Slot &x, cudaStream_t s)
+{
+    CK(cudaStreamSynchronize(s));
     if (x.h_plan->bad_pairs) {
         fprintf(stderr, "[bsw-b200] fatal: %d pair(s) violate the call contract (negative length, h0 <= 0, or "
                         ">= %d bases in getScores8)\n", x.h_plan->bad_pairs, BSW_MAX_SEQ_LEN8);
@@ -230,11 +235,26 @@ const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cuda
     return x.h_plan;
 }
 
+const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+{
+    plan_enqueue(k, x, d_pairs, n, s, tier8_check);
+    return plan_wait(x, s);
+}
+
+void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
+                   const uint8_t *d_qer, int n, int w, cudaStream_t s);
+
 void launch_bsw(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
                 int n, int w, cudaStream_t s, int tier8_check)
 {
     if (n <= 0) return;
     const Plan *pl = run_plan(k, sl, d_pairs, n, s, tier8_check);
+    launch_bsw_dp(k, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
+}
+
+void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
+                   const uint8_t *d_qer, int n, int w, cudaStream_t s)
+{
     const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
@@ -361,29 +381,48 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
     if (!pairs || !ref || !qer) die("null buffer passed to getScores");
     const int nd = (int)k.ctx.size();
     const int chunk = std::max(1024, k.chunk_pairs);
-    int ci = 0;
-    for (int first = 0; first < n; first += chunk, ++ci) {
-        const int cnt = std::min(chunk, n - first);
-        DevCtx &x = k.ctx[ci % nd];
-        Slot &sl = x.slot[(ci / nd) % BSW_NSLOT];
-        slot_retire(k, x, sl);                    /* its previous chunk must have landed */
-        long long rlo, rhi, qlo, qhi;
-        extents(pairs, first, cnt, rlo, rhi, qlo, qhi);
-        CK(cudaSetDevice(x.dev));
-        sl.pairs.reserve((size_t)cnt * sizeof(bsw_seqpair_t));
-        sl.ref.reserve((size_t)(rhi - rlo) + 64);
-        sl.qer.reserve((size_t)(qhi - qlo) + 64);
-        CK(cudaMemcpyAsync(sl.pairs.p, pairs + first, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
-        if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
-        if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
-        k.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
-        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
-        launch_bsw(k, x, sl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - rlo, (const uint8_t *)sl.qer.p - qlo,
-                   cnt, w, sl.stream, tier8_check);
-        CK(cudaMemcpyAsync(pairs + first, sl.pairs.p, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, sl.stream));
-        CK(cudaEventRecord(sl.done, sl.stream));
+    const int nchunks = (n + chunk - 1) / chunk;
+    struct Job { int first, cnt; long long rlo, qlo; DevCtx *x; Slot *sl; };
+    std::vector<Job> jobs(nchunks);
+    /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
+    auto stage_a = [&](int ci) {
+        Job &j = jobs[ci];
+        j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
+        j.x = &k.ctx[ci % nd]; j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
+        slot_retire(k, *j.x, *j.sl);              /* its previous chunk must have landed */
+        long long rhi, qhi;
+        extents(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
+        Slot &sl = *j.sl;
+        CK(cudaSetDevice(j.x->dev));
+        sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
+        sl.ref.reserve((size_t)(rhi - j.rlo) + 64);
+        sl.qer.reserve((size_t)(qhi - j.qlo) + 64);
+        CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
+        if (rhi > j.rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + j.rlo, (size_t)(rhi - j.rlo), cudaMemcpyHostToDevice, sl.stream));
+        if (qhi > j.qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + j.qlo, (size_t)(qhi - j.qlo), cudaMemcpyHostToDevice, sl.stream));
+        k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - j.rlo) + (qhi - j.qlo);
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, j.cnt, sl.stream, tier8_check);
         sl.busy = true;
-        k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t);
+    };
+    /* stage B: wait for the histogram, launch the DP kernels, download the results */
+    auto stage_b = [&](int ci) {
+        Job &j = jobs[ci];
+        Slot &sl = *j.sl;
+        CK(cudaSetDevice(j.x->dev));
+        const Plan *pl = plan_wait(sl, sl.stream);
+        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
+        launch_bsw_dp(k, *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - j.rlo,
+                      (const uint8_t *)sl.qer.p - j.qlo, j.cnt, w, sl.stream);
+        CK(cudaMemcpyAsync(pairs + j.first, sl.pairs.p, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, sl.stream));
+        CK(cudaEventRecord(sl.done, sl.stream));
+        k.st.d2h_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);
+    };
+    /* chunk c+nd is uploading while chunk c waits for its histogram: the copy engine never idles */
+    const int ahead = nd;
+    for (int ci = 0; ci < std::min(ahead, nchunks); ++ci) stage_a(ci);
+    for (int ci = 0; ci < nchunks; ++ci) {
+        if (ci + ahead < nchunks) stage_a(ci + ahead);
+        stage_b(ci);
     }
     for (DevCtx &x : k.ctx)
         for (Slot &sl : x.slot) slot_retire(k, x, sl);
