@@ -30,6 +30,7 @@
 #define BSW_CUDA_H
 
 #include <stdint.h>
+#include <stddef.h>
 
 #ifdef __cplusplus
 extern "C" {
