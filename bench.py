@@ -66,25 +66,35 @@ def host_threads():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md): one
+    streaming `nvidia-smi -lms 50` process, read line by line."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.stop_flag, self.rows = index, False, []
+        self.index, self.stop_flag, self.rows, self.proc = index, False, [], None
 
     def run(self):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
-        while not self.stop_flag:
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "50"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                self.rows.append([x.strip() for x in line.strip().split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc is not None:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                self.proc.terminate()
             except Exception:
                 pass
-            time.sleep(0.1)
+        self.join(timeout=2)
 
     def summary(self):
         sm, mx, reasons = [], 0, set()
@@ -273,8 +283,6 @@ def main():
     kst = sw.stats()
     sw.set_timing(False)
     kernel_ms_step = kst["kernel_ms"]
-    sampler.stop_flag = True
-    sampler.join(timeout=2)
 
     # ---------------- end-to-end through the C ABI on pinned host buffers ("e2e") ----------------
     keep = []
@@ -303,14 +311,11 @@ def main():
     est = sw.stats()
     barrier()
 
-    # ---------------- reduce over ranks ----------------
-    vals = torch.tensor([ms_total, e2e_ms, kernel_ms_step], dtype=torch.float64, device="cuda")
-    sums = torch.tensor([float(cells_step), float(npairs)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
-        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-    ms_total, e2e_ms, kernel_ms_step = [float(x) for x in vals.tolist()]
-    cells_all, pairs_all = [float(x) for x in sums.tolist()]
+    sampler.stop()
+    # ---------------- reduce over ranks: max of the times, sum of the work ----------------
+    import sharding
+    (ms_total, e2e_ms, kernel_ms_step), (cells_all, pairs_all) = sharding.reduce_step_stats(
+        dist if world > 1 else None, torch, "cuda", [ms_total, e2e_ms, kernel_ms_step], [float(cells_step), float(npairs)])
 
     if rank == 0:
         ms_step = ms_total / args.steps
