@@ -147,12 +147,19 @@ struct PState {
 struct RowCtx { uint32_t T, LUTLO, LUTHI, GATE, NOD, NOI, NED, NEI; };
 
 #if defined(__CUDA_ARCH__)
+/* predicated in-place global load: w = *p iff c (the register keeps its value otherwise) */
+__device__ __forceinline__ void ld_if(uint32_t &w, const uint32_t *p, bool c)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q ld.global.nc.u32 %0, [%1]; }"
+                 : "+r"(w) : "l"(p), "r"((uint32_t)c));
+}
 __device__ __forceinline__ uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
 /* keeps a warp-uniform constant in a vector register (PRMT cannot take a uniform register as data) */
 __device__ __forceinline__ uint32_t launder(uint32_t v) { uint32_t r; asm volatile("mov.b32 %0, %1;" : "=r"(r) : "r"(v)); return r; }
 #else
 static inline uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return p_maxu(p_maxu(a, b), c); }
 static inline uint32_t launder(uint32_t v) { return v; }
+static inline void ld_if(uint32_t &w, const uint32_t *p, bool c) { if (c) w = *p; }
 #endif
 
 /* one DP cell of both lanes (A.1 inner loop body) */
@@ -345,7 +352,9 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
     const int BIG = 0x3fffffff;
 
     /* target bases: aligned 32-bit words of the reference buffer, fetched one word (4 rows) ahead;
-     * reads stay within 8 bytes of the pair's last base (the boundary layer pads the buffers). */
+     * reads stay within 8 bytes of the pair's last base (the boundary layer pads the buffers).
+     * The refill is a predicated IN-PLACE load (ld_if): written as `if (c) w = *p` the compiler loads
+     * into a temporary and moves it, and the move waits for the load (13 % of kernel time, profile r1f). */
     uint32_t wcur[2], wnxt[2];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
@@ -379,10 +388,9 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 const uintptr_t adr = reinterpret_cast<uintptr_t>(ref + s.idr) + (uintptr_t)i;
                 const uint32_t tt = (wcur[p] >> (8 * (int)(adr & 3))) & 0xffu;
                 tb[p] = tt > 4u ? 4u : tt;
-                if ((adr & 3) == 3) {            /* next row starts a new word: rotate, fetch the one after */
-                    wcur[p] = wnxt[p];
-                    wnxt[p] = reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3)[2];
-                }
+                const bool cross = (adr & 3) == 3;   /* next row starts a new word: rotate, fetch the one after */
+                if (cross) wcur[p] = wnxt[p];
+                ld_if(wnxt[p], reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3) + 2, cross);
             }
             if (st >= s.end) {
                 /* no cell in this row: m == 0, the lane stops here (A.1: gscore check, then break) */
