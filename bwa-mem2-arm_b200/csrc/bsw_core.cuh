@@ -148,10 +148,10 @@ struct RowCtx { uint32_t T, LUTLO, LUTHI, GATE, NOD, NOI, NED, NEI; };
 
 #if defined(__CUDA_ARCH__)
 /* predicated in-place global load: w = *p iff c (the register keeps its value otherwise) */
-__device__ __forceinline__ void ld_if(uint32_t &w, const uint32_t *p, bool c)
-{
-    asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q ld.global.nc.u32 %0, [%1]; }"
-                 : "+r"(w) : "l"(p), "r"((uint32_t)c));
+__device__ __forceinline__ void rot_ld_if(uint32_t &cur, uint32_t &nxt, const uint32_t *p, bool c)
+{   /* if (c) { cur = nxt; nxt = *p; } with both steps predicated: nxt is only READ on rows that rotate */
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %3, 0; @q mov.b32 %0, %1; @q ld.global.nc.u32 %1, [%2]; }"
+                 : "+r"(cur), "+r"(nxt) : "l"(p), "r"((uint32_t)c));
 }
 __device__ __forceinline__ uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
 /* keeps a warp-uniform constant in a vector register (PRMT cannot take a uniform register as data) */
@@ -159,7 +159,7 @@ __device__ __forceinline__ uint32_t launder(uint32_t v) { uint32_t r; asm volati
 #else
 static inline uint32_t p_max3u(uint32_t a, uint32_t b, uint32_t c) { return p_maxu(p_maxu(a, b), c); }
 static inline uint32_t launder(uint32_t v) { return v; }
-static inline void ld_if(uint32_t &w, const uint32_t *p, bool c) { if (c) w = *p; }
+static inline void rot_ld_if(uint32_t &cur, uint32_t &nxt, const uint32_t *p, bool c) { if (c) { cur = nxt; nxt = *p; } }
 #endif
 
 /* one DP cell of both lanes (A.1 inner loop body) */
@@ -313,29 +313,56 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
         ps[p].clean = 1;
     }
 
-    /* ---- first row of H (A.1), E = 0, query selectors ---- */
+    /* ---- first row of H (A.1), E = 0, query selectors ----
+     * The query bases are read as aligned 32-bit words, one word (4 columns) ahead of their use
+     * (funnel-shifted to the pair's byte offset): a byte load per column stalls on every column
+     * (10.8 % of the kernel time in profile r1g).  Reads stay within 12 bytes of the last base. */
     {
         const int qmax = mx(ps[0].qlen, ps[1].qlen);
         int hp0 = 0, hp1 = 0, lastnz0 = 0, lastnz1 = 0;
-        for (int j = 0; j <= qmax; ++j) {
-            int hv[2];
+        const uint32_t *wq[2]; int shq[2]; uint32_t cw0[2], cw1[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const PairIn &x = *in[p];
+            const uintptr_t aq = reinterpret_cast<uintptr_t>(qer + (x.valid ? x.idq : 0));
+            wq[p] = reinterpret_cast<const uint32_t *>(aq & ~(uintptr_t)3);
+            shq[p] = (int)(aq & 3) * 8;
+            cw0[p] = cw1[p] = 0u;
+            if (x.valid && x.len2 > 0) { cw0[p] = wq[p][0]; cw1[p] = wq[p][1]; }
+        }
+        for (int j0 = 0; j0 <= qmax; j0 += 4) {
+            uint32_t nw[2], by[2];
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
-                int prev = p ? hp1 : hp0, v;
-                if (j > ps[p].qlen) v = 0;
-                else if (j == 0) v = ps[p].h0;
-                else if (j == 1) v = ps[p].h0 > c.oe_ins ? ps[p].h0 - c.oe_ins : 0;
-                else v = prev > c.e_ins ? prev - c.e_ins : 0;
-                hv[p] = v;
+                const PairIn &x = *in[p];
+                nw[p] = (x.valid && j0 + 4 < x.len2) ? wq[p][(j0 >> 2) + 2] : 0u;
+                by[p] = shq[p] ? ((cw0[p] >> shq[p]) | (cw1[p] << (32 - shq[p]))) : cw0[p];
             }
-            hp0 = hv[0]; hp1 = hv[1];
-            if (hv[0]) lastnz0 = j;
-            if (hv[1]) lastnz1 = j;
-            he[j * S] = pack2(hv[0], hv[1]);
-            uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
-            uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
-            qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
-            qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = j0 + u;
+                if (j <= qmax) {
+                    int hv[2];
+#pragma unroll
+                    for (int p = 0; p < 2; ++p) {
+                        int prev = p ? hp1 : hp0, v;
+                        if (j > ps[p].qlen) v = 0;
+                        else if (j == 0) v = ps[p].h0;
+                        else if (j == 1) v = ps[p].h0 > c.oe_ins ? ps[p].h0 - c.oe_ins : 0;
+                        else v = prev > c.e_ins ? prev - c.e_ins : 0;
+                        hv[p] = v;
+                    }
+                    hp0 = hv[0]; hp1 = hv[1];
+                    if (hv[0]) lastnz0 = j;
+                    if (hv[1]) lastnz1 = j;
+                    he[j * S] = pack2(hv[0], hv[1]);
+                    uint32_t qa = (A.valid && j < A.len2) ? ((by[0] >> (8 * u)) & 0xffu) : 0u;
+                    uint32_t qb = (B.valid && j < B.len2) ? ((by[1] >> (8 * u)) & 0xffu) : 0u;
+                    qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
+                    qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+                }
+            }
+            cw0[0] = cw1[0]; cw1[0] = nw[0]; cw0[1] = cw1[1]; cw1[1] = nw[1];
         }
         /* clean: every non-zero initial entry is inside row 0's range [0, min(qlen, w+1)] */
         ps[0].clean = lastnz0 <= mn(ps[0].qlen, ps[0].w + 1);
@@ -353,7 +380,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
 
     /* target bases: aligned 32-bit words of the reference buffer, fetched one word (4 rows) ahead;
      * reads stay within 8 bytes of the pair's last base (the boundary layer pads the buffers).
-     * The refill is a predicated IN-PLACE load (ld_if): written as `if (c) w = *p` the compiler loads
+     * The refill is a predicated IN-PLACE rotate + load (rot_ld_if): written as `if (c) w = *p` the compiler loads
      * into a temporary and moves it, and the move waits for the load (13 % of kernel time, profile r1f). */
     uint32_t wcur[2], wnxt[2];
 #pragma unroll
@@ -389,8 +416,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 const uint32_t tt = (wcur[p] >> (8 * (int)(adr & 3))) & 0xffu;
                 tb[p] = tt > 4u ? 4u : tt;
                 const bool cross = (adr & 3) == 3;   /* next row starts a new word: rotate, fetch the one after */
-                if (cross) wcur[p] = wnxt[p];
-                ld_if(wnxt[p], reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3) + 2, cross);
+                rot_ld_if(wcur[p], wnxt[p], reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3) + 2, cross);
             }
             if (st >= s.end) {
                 /* no cell in this row: m == 0, the lane stops here (A.1: gscore check, then break) */
