@@ -81,48 +81,114 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
         ks[p].act = (x.valid && x.len1 > 0) ? 1 : 0;
     }
     const int qmin = mn(ks[0].qlen, ks[1].qlen), qmax = mx(ks[0].qlen, ks[1].qlen);
-    for (int j = 0; j < qmax; ++j) {
-        he[j * S] = 0u;
-        uint32_t qa = (A.valid && j < A.len2) ? qer[A.idq + j] : 0u;
-        uint32_t qb = (B.valid && j < B.len2) ? qer[B.idq + j] : 0u;
-        qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
-        qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+    /* row state = 0; query selectors from aligned 32-bit words fetched one word ahead (see bsw_core.cuh) */
+    {
+        const uint32_t *wq[2]; int shq[2]; uint32_t cw0[2], cw1[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const PairIn &x = *in[p];
+            const uintptr_t aq = reinterpret_cast<uintptr_t>(qer + (x.valid ? x.idq : 0));
+            wq[p] = reinterpret_cast<const uint32_t *>(aq & ~(uintptr_t)3);
+            shq[p] = (int)(aq & 3) * 8;
+            cw0[p] = cw1[p] = 0u;
+            if (x.valid && x.len2 > 0) { cw0[p] = wq[p][0]; cw1[p] = wq[p][1]; }
+        }
+        for (int j0 = 0; j0 < qmax; j0 += 4) {
+            uint32_t nw[2], by[2];
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                const PairIn &x = *in[p];
+                nw[p] = (x.valid && j0 + 4 < x.len2) ? wq[p][(j0 >> 2) + 2] : 0u;
+                by[p] = shq[p] ? ((cw0[p] >> shq[p]) | (cw1[p] << (32 - shq[p]))) : cw0[p];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = j0 + u;
+                if (j < qmax) {
+                    he[j * S] = 0u;
+                    uint32_t qa = (A.valid && j < A.len2) ? ((by[0] >> (8 * u)) & 0xffu) : 0u;
+                    uint32_t qb = (B.valid && j < B.len2) ? ((by[1] >> (8 * u)) & 0xffu) : 0u;
+                    qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
+                    qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+                }
+            }
+            cw0[0] = cw1[0]; cw1[0] = nw[0]; cw0[1] = cw1[1]; cw1[1] = nw[1];
+        }
     }
-    const uint32_t LUTLO = lut_lo(c), LUTHI = lut_hi(c);
+    const uint32_t LUTLO = launder(lut_lo(c)), LUTHI = launder(lut_hi(c));
     const uint32_t NEG_OE_DEL = pack2(-c.oe_del, -c.oe_del), NEG_OE_INS = pack2(-c.oe_ins, -c.oe_ins);
     const uint32_t NEG_E_DEL = pack2(-c.e_del, -c.e_del), NEG_E_INS = pack2(-c.e_ins, -c.e_ins);
     const uint32_t LONGER = ks[0].qlen > ks[1].qlen ? 0x0000ffffu : 0xffff0000u;
+
+    /* target bases: aligned words one word (4 rows) ahead, predicated in-place refill (bsw_core.cuh) */
+    uint32_t wcur[2], wnxt[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        wcur[p] = wnxt[p] = 0u;
+        if (ks[p].act) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(ref + ks[p].idr);
+            const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+            wcur[p] = wp[0]; wnxt[p] = wp[1];
+        }
+    }
+
+/* one local-SW cell of both lanes (A.2) */
+#define KSW_CELL(WV, Q, H, EN)                                                        \
+    {                                                                                 \
+        const uint32_t ve_ = st_e(WV);                                                \
+        const uint32_t s_ = p_perm(LUTLO, LUTHI, p_xsel(Q, T));                       \
+        H = p_max3_relu(p_add(hd, s_), ve_, f);                                       \
+        EN = p_addmax_relu(H, NEG_OE_DEL, p_add(ve_, NEG_E_DEL));                     \
+        f = p_addmax_relu(H, NEG_OE_INS, p_add(f, NEG_E_INS));                        \
+        hd = st_h2(WV, ve_);                                                          \
+    }
 
     int i = 0;
     while (ks[0].act | ks[1].act) {
         uint32_t tb[2];
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
-            uint32_t t = ks[p].act ? ref[ks[p].idr + i] : 0u;
-            tb[p] = t > 4u ? 4u : t;
+            tb[p] = 0u;
+            if (ks[p].act) {
+                const uintptr_t adr = reinterpret_cast<uintptr_t>(ref + ks[p].idr) + (uintptr_t)i;
+                const uint32_t t = (wcur[p] >> (8 * (int)(adr & 3))) & 0xffu;
+                tb[p] = t > 4u ? 4u : t;
+                rot_ld_if(wcur[p], wnxt[p], reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3) + 2, (adr & 3) == 3);
+            }
         }
         const uint32_t T = tb[0] * 0x0011u | tb[1] * 0x1100u;
         const uint32_t ACT = (ks[0].act ? 0x0000ffffu : 0u) | (ks[1].act ? 0xffff0000u : 0u);
         uint32_t f = 0, hd = 0, key = 0;
-        uint32_t jv = 0x00ff00ffu;                    /* 255 - j per lane */
         int j = 0;
-        if (ACT == 0xffffffffu) {
-#pragma unroll 4
-            for (; j < qmin; ++j) {
-                const uint32_t wv = he[j * S];
-                const uint32_t ve = st_e(wv);
-                uint32_t q_ = qs[j * S];
-                uint32_t x_ = p_xsel(q_, T);
-                uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-                uint32_t h_ = p_max3_relu(p_add(hd, s_), ve, f);
-                uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(ve, NEG_E_DEL));
-                f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS));
-                hd = st_h(wv);
-                he[j * S] = st_pack(h_, en);
-                key = p_maxu(key, (h_ << 8) + jv);
-                jv -= 0x00010001u;
+        if (ACT == 0xffffffffu && qmin >= 4) {
+            /* both lanes live: unmasked groups of four columns, next group's loads issued first.
+             * key = max over (h << 8 | 255 - j): row maximum and its FIRST column. */
+            const int n4 = qmin & ~3;
+            const uint32_t c0 = 0x00ff00ffu, c1 = 0x00fe00feu, c2 = 0x00fd00fdu, c3 = 0x00fc00fcu;
+            uint32_t v0 = he[0], v1 = he[S], v2 = he[2 * S], v3 = he[3 * S];
+            uint32_t q0 = qs[0], q1 = qs[S], q2 = qs[2 * S], q3 = qs[3 * S];
+#define KSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                     \
+            {                                                                         \
+                uint32_t ha, hb, hc, hd4, ea, eb, ec, ed;                             \
+                KSW_CELL(V0, Q0, ha, ea) he[(j + 0) * S] = st_pack(ha, ea);           \
+                KSW_CELL(V1, Q1, hb, eb) he[(j + 1) * S] = st_pack(hb, eb);           \
+                KSW_CELL(V2, Q2, hc, ec) he[(j + 2) * S] = st_pack(hc, ec);           \
+                KSW_CELL(V3, Q3, hd4, ed) he[(j + 3) * S] = st_pack(hd4, ed);         \
+                const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd4 << 8) + c3); \
+                key = p_maxu(key, g - (uint32_t)j * 0x00010001u);                     \
             }
+            while (j + 8 <= n4) {
+                const uint32_t w0 = he[(j + 4) * S], w1 = he[(j + 5) * S], w2 = he[(j + 6) * S], w3 = he[(j + 7) * S];
+                const uint32_t r0 = qs[(j + 4) * S], r1 = qs[(j + 5) * S], r2 = qs[(j + 6) * S], r3 = qs[(j + 7) * S];
+                KSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
+                v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
+                j += 4;
+            }
+            KSW_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
+            j += 4;
+#undef KSW_GROUP
         }
+        uint32_t jv = 0x00ff00ffu - (uint32_t)j * 0x00010001u;      /* 255 - j per lane */
         /* one lane finished, or the tail of the longer query: masked cells */
         for (; j < qmax; ++j) {
             const uint32_t MK = ACT & (j < qmin ? 0xffffffffu : LONGER);
