@@ -325,6 +325,12 @@ def main():
         peak_instr = bswb200.measure_dpx_peak(local_rank, 2)          # thread-level DPX instr/s, live
         peak_gcups = peak_instr * 2 / OPS_PER_CELL / 1e9
         ach = cells_step / (kernel_ms_step * 1e-3) / 1e9 if kernel_ms_step > 0 else 0.0
+        traffic = None                      # DRAM bytes per launch of the dominant kernel, from the committed ncu pass
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_launches_summary.json")) as f:
+                traffic = json.load(f)["bsw_packed_kernel<false>"]["dram_bytes_per_launch"]
+        except Exception:
+            pass
         line = {
             "metric": "bsw_gcups", "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -341,7 +347,9 @@ def main():
                     "api": "bsw_getScores8/bsw_getScores16 on pinned host SeqPair/sequence buffers"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "dpx-int", "achieved": ach, "peak": peak_gcups, "unit": "GCUPS",
-                         "frac": ach / peak_gcups if peak_gcups else None, "traffic": None,
+                         "frac": ach / peak_gcups if peak_gcups else None, "traffic": traffic,
+                         "traffic_note": "dram__bytes_read+write per bsw_packed_kernel launch (one launch per query-length bin), "
+                                         "ncu pass profiles/r01_launches_bench_steps1.csv; algorithmic ~0.055 B/cell",
                          "kernel": "bsw_packed_kernel", "kernel_ms_per_step": kernel_ms_step,
                          "ops_per_cell": OPS_PER_CELL,
                          "peak_source": "measured live: issue rate of independent VIMNMX3/VIADDMNMX.S16x2 streams "

@@ -122,7 +122,8 @@ void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBuf
  * Same computation on buffers that already live in the HBM of the handle's
  * first device; asynchronous on `stream` (a cudaStream_t, 0 = default stream).
  * Used by bench.py for the inputs-resident number and by pipelines that keep
- * read batches on the GPU.  refBytes/qerBytes are the buffer extents. */
+ * read batches on the GPU.  The sequence buffers must be readable for 16 bytes
+ * past the last base any pair names (the kernels fetch bases as aligned words). */
 void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                        const uint8_t *d_seqBufQer, int32_t numPairs, int32_t w, void *stream);
 void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
