@@ -156,12 +156,13 @@ void core_init(Core &k, int mode)
     for (DevCtx &x : k.ctx) {
         CK(cudaSetDevice(x.dev));
         if (max_smem > x.smem_optin) die("device shared memory too small for the packed kernels");
-        CK(cudaFuncSetAttribute(bsw_packed_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(bsw_packed_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CK(cudaFuncSetAttribute(bsw_packed_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        CK(cudaFuncSetAttribute(bsw_packed_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        CK(cudaFuncSetAttribute(kswv_packed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        const void *fns[] = { (const void *)bsw_packed_kernel<false, false>, (const void *)bsw_packed_kernel<false, true>,
+                              (const void *)bsw_packed_kernel<true, false>, (const void *)bsw_packed_kernel<true, true>,
+                              (const void *)kswv_packed_kernel<false>, (const void *)kswv_packed_kernel<true> };
+        for (const void *fn : fns) {
+            CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+            CK(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        }
     }
 }
 
@@ -265,12 +266,11 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
         const int NE = qb * 16, grid = (cnt + 63) / 64;
         cudaStream_t bs = x.bin_stream[qb];
         CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
-        if (k.count_cells)
-            bsw_packed_kernel<true><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
-                                                                              NE, k.c, w, (unsigned long long *)x.cells.p);
-        else
-            bsw_packed_kernel<false><<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
-                                                                               NE, k.c, w, (unsigned long long *)x.cells.p);
+        /* template flags: exact cell counting; symmetric gap sums (one packed add less per cell) */
+        auto kern = k.count_cells ? (k.c.oe_del == k.c.oe_ins ? bsw_packed_kernel<true, true> : bsw_packed_kernel<true, false>)
+                                  : (k.c.oe_del == k.c.oe_ins ? bsw_packed_kernel<false, true> : bsw_packed_kernel<false, false>);
+        kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+                                                        NE, k.c, w, (unsigned long long *)x.cells.p);
         CK(cudaGetLastError());
         CK(cudaEventRecord(x.bin_ev[qb], bs));
         CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
@@ -317,7 +317,9 @@ void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, con
             const int NE = qb * 16, grid = (cnt + 63) / 64;
             cudaStream_t bs = x.bin_stream[qb];
             CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
-            kswv_packed_kernel<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
+            /* SYM=false on purpose: sharing h - oe puts a third op on kswv's f -> h -> f chain (measured 3 % slower) */
+            auto kern = kswv_packed_kernel<false>;
+            kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
                                                                           k.c, is8, phase, (uint16_t *)sl.rowmax.p, stride,
                                                                           (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());

@@ -178,6 +178,9 @@ BSW_HD uint32_t st_h2(uint32_t w, uint32_t e) { return w - e * 256u; }
 BSW_HD uint32_t st_h(uint32_t w) { return w & 0x00ff00ffu; }
 BSW_HD uint32_t st_pack(uint32_t h, uint32_t e) { return e * 256u + h; }
 
+/* SYM: o_del + e_del == o_ins + e_ins (bwa-mem's default): M - oe is computed once for both gap
+ * directions, e' = max(e - e_del, M - oe, 0), f' = max(f - e_ins, M - oe, 0): one packed add less. */
+template <bool SYM>
 BSW_HD void bsw_cell(const RowCtx &r, uint32_t w, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
 {
     const uint32_t e = st_e(w), hs = st_h2(w, e);
@@ -185,13 +188,19 @@ BSW_HD void bsw_cell(const RowCtx &r, uint32_t w, uint32_t q, uint32_t &f, uint3
     const uint32_t s = p_perm(r.LUTLO, r.LUTHI, x);
     const uint32_t M = p_addmin(hs, s, hs * r.GATE);
     h = p_max3(M, e, f);
-    en = p_addmax_relu(M, r.NOD, p_add(e, r.NED));
-    f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
+    if (SYM) {
+        const uint32_t u = p_add(M, r.NOD);
+        en = p_addmax_relu(e, r.NED, u);
+        f = p_addmax_relu(f, r.NEI, u);
+    } else {
+        en = p_addmax_relu(M, r.NOD, p_add(e, r.NED));
+        f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
+    }
 }
 
 /* up to four cells with a bound and the f-cut check: used for the group that holds the cut column
  * and for the final partial group of a sweep (everything else runs the unchecked BSW_GROUP) */
-template <int S>
+template <int S, bool SYM>
 BSW_HD void bsw_group_generic(const RowCtx &r, uint32_t *hp, int k, int cnt, int kcut, uint32_t keepf, uint32_t keeph,
                               uint32_t v0, uint32_t v1, uint32_t v2, uint32_t v3,
                               uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3, uint32_t cbase,
@@ -203,7 +212,7 @@ BSW_HD void bsw_group_generic(const RowCtx &r, uint32_t *hp, int k, int cnt, int
         if (c < cnt) {
             if (k + c == kcut) { h1save = h1; f &= keepf; h1 &= keeph; }
             uint32_t h, en;
-            bsw_cell(r, vv[c], qq[c], f, h, en);
+            bsw_cell<SYM>(r, vv[c], qq[c], f, h, en);
             hp[(k + c) * S] = st_pack(h1, en);
             h1 = h;
             key = p_maxu(key, (h << 8) + cbase + (uint32_t)(k + c) * 0x00010001u);
@@ -220,7 +229,7 @@ BSW_HD void bsw_group_generic(const RowCtx &r, uint32_t *hp, int k, int cnt, int
  * f &= keepf and h1 &= keeph -- the exact right-trim cut of the lane that ends first, after which
  * that lane sweeps on over zero-state entries.
  */
-template <int S>
+template <int S, bool SYM>
 BSW_HD void bsw_sweep_cut(const RowCtx &r, uint32_t *he, const uint16_t *qs, int j0, int j1,
                           int jcut, uint32_t keepf, uint32_t keeph,
                           uint32_t &f, uint32_t &h1, uint32_t &key, uint32_t &h1save)
@@ -241,10 +250,10 @@ BSW_HD void bsw_sweep_cut(const RowCtx &r, uint32_t *he, const uint16_t *qs, int
 #define BSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                              \
             {                                                                                  \
                 uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                       \
-                bsw_cell(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);             \
-                bsw_cell(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);             \
-                bsw_cell(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);             \
-                bsw_cell(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);             \
+                bsw_cell<SYM>(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);             \
+                bsw_cell<SYM>(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);             \
+                bsw_cell<SYM>(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);             \
+                bsw_cell<SYM>(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);             \
                 h1 = hd;                                                                       \
                 const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
                 key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                              \
@@ -267,7 +276,7 @@ BSW_HD void bsw_sweep_cut(const RowCtx &r, uint32_t *he, const uint16_t *qs, int
             const uint32_t v1 = cnt > 1 ? hp[(k + 1) * S] : 0u, q1 = cnt > 1 ? qp[(k + 1) * S] : 0u;
             const uint32_t v2 = cnt > 2 ? hp[(k + 2) * S] : 0u, q2 = cnt > 2 ? qp[(k + 2) * S] : 0u;
             const uint32_t v3 = cnt > 3 ? hp[(k + 3) * S] : 0u, q3 = cnt > 3 ? qp[(k + 3) * S] : 0u;
-            bsw_group_generic<S>(r, hp, k, cnt, kcut, keepf, keeph, v0, v1, v2, v3, q0, q1, q2, q3, c0, f, h1, key, h1save);
+            bsw_group_generic<S, SYM>(r, hp, k, cnt, kcut, keepf, keeph, v0, v1, v2, v3, q0, q1, q2, q3, c0, f, h1, key, h1save);
             k += cnt;
         }
         if (k >= n) break;
@@ -291,7 +300,7 @@ BSW_HD void bsw_sweep_cut(const RowCtx &r, uint32_t *he, const uint16_t *qs, int
  *  - a lane that has terminated is zeroed once, after which it computes zeros for free.
  * COUNT additionally tracks the exact `beg` to report the oracle's DP-cell count.
  */
-template <int S, bool COUNT>
+template <int S, bool COUNT, bool SYM>
 BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                               const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                               uint32_t *he, uint16_t *qs, PairOut &oa, PairOut &ob)
@@ -452,7 +461,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                                 ((j_ >= sp[1] && j_ < ep[1]) ? 0xffff0000u : 0u);       \
             const uint32_t v = he[j_ * S];                                              \
             uint32_t h_, en, fn = f;                                                    \
-            bsw_cell(r, v, qs[j_ * S], fn, h_, en);                                     \
+            bsw_cell<SYM>(r, v, qs[j_ * S], fn, h_, en);                                     \
             he[j_ * S] = st_pack(h1 & MK, en & MK) | (v & ~MK);                         \
             f = fn & MK;                                                                \
             h1 = (h_ & MK) | (h1 & ~MK);                                                \
@@ -472,12 +481,12 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                 /* common case: one sweep, the short lane's f chain cut at its exact end */
                 const int jcut = e1 < e2 ? e1 : -1;
                 if (jcut >= 0) cut = sh;
-                bsw_sweep_cut<S>(r, he, qs, hs, e2, jcut, keep, e1 == sh_qlen ? keep : 0xffffffffu, f, h1, key, h1s);
+                bsw_sweep_cut<S, SYM>(r, he, qs, hs, e2, jcut, keep, e1 == sh_qlen ? keep : 0xffffffffu, f, h1, key, h1s);
             } else {
                 int j = ls;
                 const int head_end = mn(hs, e2);
                 for (; j < head_end; ++j) BSW_CELL_MASKED(j)
-                if (hs < e1) { bsw_sweep_cut<S>(r, he, qs, hs, e1, -1, 0u, 0u, f, h1, key, h1s); j = e1; }
+                if (hs < e1) { bsw_sweep_cut<S, SYM>(r, he, qs, hs, e1, -1, 0u, 0u, f, h1, key, h1s); j = e1; }
                 if (j < hs) j = hs;
                 if (j < e2) {
                     if (lazy && j >= e1) {
@@ -485,7 +494,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
                         f &= keep;
                         if (e1 == sh_qlen) h1 &= keep;              /* entry qlen is never read: keep it zero */
                         uint32_t dummy = 0;
-                        bsw_sweep_cut<S>(r, he, qs, j, e2, -1, 0u, 0u, f, h1, key, dummy);
+                        bsw_sweep_cut<S, SYM>(r, he, qs, j, e2, -1, 0u, 0u, f, h1, key, dummy);
                     } else {
                         for (; j < e2; ++j) BSW_CELL_MASKED(j)
                     }
@@ -494,7 +503,7 @@ BSW_HD void bsw_packed_thread(const Const &c, int w_in, const PairIn &A, const P
             h1cut = half_s(h1s, sh);
         } else {
             /* the other lane is dead and zeroed */
-            bsw_sweep_cut<S>(r, he, qs, ps[0].act ? sp[0] : sp[1], ps[0].act ? ep[0] : ep[1], -1, 0u, 0u, f, h1, key, h1s);
+            bsw_sweep_cut<S, SYM>(r, he, qs, ps[0].act ? sp[0] : sp[1], ps[0].act ? ep[0] : ep[1], -1, 0u, 0u, f, h1, key, h1s);
         }
 #undef BSW_CELL_MASKED
 

@@ -90,7 +90,7 @@ __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pa
 }
 
 /* ------------------------------------------------------------------ 4a. BSW packed */
-template <bool COUNT>
+template <bool COUNT, bool SYM>
 __global__ void __launch_bounds__(32)
 bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
@@ -107,7 +107,7 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
     if (pa >= 0) {
         PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
         PairOut oa, ob;
-        bsw_packed_thread<32, COUNT>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        bsw_packed_thread<32, COUNT, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
         int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
         o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
         my_cells += (unsigned long long)oa.cells;
@@ -157,6 +157,7 @@ __device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const b
 }
 
 /* ------------------------------------------------------------------ 4b. kswv packed */
+template <bool SYM>
 __global__ void __launch_bounds__(32)
 kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                    const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
@@ -174,7 +175,7 @@ kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__res
     if (pa >= 0) {
         PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
         KswOut oa, ob;
-        kswv_packed_thread<32>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
+        kswv_packed_thread<32, SYM>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
         kswv_store(aln, pairs, pa, oa, phase);
         my_cells += (unsigned long long)oa.cells;
         if (pb >= 0) { kswv_store(aln, pairs, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }

@@ -58,7 +58,7 @@ struct KState {
  * he[j*S] = row state word (st_pack: H(i-1, j) low byte, E(i, j) high byte of each lane), qs[j*S] = selector,
  * rm[i*RS] = imaxA | imaxB << 8 (this thread's slot of the row-max scratch).
  */
-template <int S>
+template <int S, bool SYM>
 BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const PairIn &B,
                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                                uint32_t *he, uint16_t *qs, uint16_t *rm, long long RS,
@@ -138,8 +138,14 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
         const uint32_t ve_ = st_e(WV);                                                \
         const uint32_t s_ = p_perm(LUTLO, LUTHI, p_xsel(Q, T));                       \
         H = p_max3_relu(p_add(hd, s_), ve_, f);                                       \
-        EN = p_addmax_relu(H, NEG_OE_DEL, p_add(ve_, NEG_E_DEL));                     \
-        f = p_addmax_relu(H, NEG_OE_INS, p_add(f, NEG_E_INS));                        \
+        if (SYM) {   /* equal gap-open+extend sums: h - oe shared by e' and f' */     \
+            const uint32_t u_ = p_add(H, NEG_OE_DEL);                                 \
+            EN = p_addmax_relu(ve_, NEG_E_DEL, u_);                                   \
+            f = p_addmax_relu(f, NEG_E_INS, u_);                                      \
+        } else {                                                                      \
+            EN = p_addmax_relu(H, NEG_OE_DEL, p_add(ve_, NEG_E_DEL));                 \
+            f = p_addmax_relu(H, NEG_OE_INS, p_add(f, NEG_E_INS));                    \
+        }                                                                             \
         hd = st_h2(WV, ve_);                                                          \
     }
 

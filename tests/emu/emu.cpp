@@ -42,8 +42,11 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         else B = { 0, 0, 0, 0, 0, 0 };
         int qm = A.len2 > B.len2 ? A.len2 : B.len2;
         std::vector<uint32_t> he(qm + 8); std::vector<uint16_t> qs(qm + 8);
-        if (count_cells) bsw_packed_thread<1, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-        else bsw_packed_thread<1, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+        const bool sym = c.oe_del == c.oe_ins;
+        if (count_cells) { if (sym) bsw_packed_thread<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+                           else bsw_packed_thread<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+        else { if (sym) bsw_packed_thread<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+               else bsw_packed_thread<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
     }
@@ -80,7 +83,8 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         else B = { 0, 0, 0, 0, 0, 0 };
         int qm = A.len2 > B.len2 ? A.len2 : B.len2, tm = A.len1 > B.len1 ? A.len1 : B.len1;
         std::vector<uint32_t> he(qm + 2); std::vector<uint16_t> qs(qm + 2), rm(tm + 2);
-        kswv_packed_thread<1>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
+        if (c.oe_del == c.oe_ins) kswv_packed_thread<1, true>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
+        else kswv_packed_thread<1, false>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
         kput(aln, pairs[ia], ia, oa, phase); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { kput(aln, pairs[ib], ib, ob, phase); if (cells_out) cells_out[ib] = ob.cells; }
     }
