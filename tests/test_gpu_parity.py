@@ -290,3 +290,35 @@ def test_properties_at_scale(ora, sw, bsw):
     P0, r0, q0 = d0["right"]
     g = P0.copy(); sw.getScores16(g, r0, q0, len(g), 1, 100)
     assert (g["score"] == g["h0"] + g["len2"]).all() and (g["qle"] == g["len2"]).all() and (g["gscore"] == g["score"]).all()
+
+
+def test_contract_violation_exits_like_the_reference(bsw):
+    """Reference convention (R:docs-archive/WEEK1_WRAPPER_COMPLETE.md:239-242): fprintf + exit(EXIT_FAILURE).
+    getScores8 with a 200-base pair, and h0 <= 0, must terminate the process with a message -- checked in a child."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import sys
+        sys.path[:0] = %r
+        import numpy as np, bswb200
+        sw = bswb200.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        p = np.zeros(1, bswb200.SEQPAIR); p['len1'] = %d; p['len2'] = 50; p['h0'] = %d
+        buf = np.zeros(400, np.uint8)
+        sw.getScores8(p, buf, buf, 1, 1, 100)
+        print('survived')
+    """)
+    paths = [p for p in sys.path if p.endswith(("bwa-mem2-arm_b200", "oracle", "tests"))]
+    for len1, h0 in ((200, 10), (60, 0)):
+        r = subprocess.run([sys.executable, "-c", code % (paths, len1, h0)], capture_output=True, text=True, timeout=120)
+        assert r.returncode != 0 and "survived" not in r.stdout
+        assert "violate the call contract" in r.stderr
+
+
+def test_small_and_repeated_calls(ora, sw):
+    """Many small calls on one handle (the host pipeline's real pattern: a few thousand pairs per call),
+    buffers reused, results independent of call history."""
+    prm = ora.make_params()
+    for k in range(12):
+        P, r, q = ora.gen_random(257 + 97 * k, 1, 127, 1, 127, h0min=1, h0max=100, sim=0.9, p_n=0.002, seed=500 + k)
+        o = P.copy(); ora.bsw_batch(o, r, q, prm, 100, 4)
+        g = P.copy(); sw.getScores8(g, r, q, len(g), 1, 100)
+        _assert_same(o, g)
