@@ -50,7 +50,7 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
-#define BSW_NSLOT 3
+#define BSW_NSLOT 4
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -82,6 +82,7 @@ struct Core {
     int timing = 0;
     int count_cells = 0;
     int chunk_pairs = 1 << 19;
+    int ahead = 2;
     int mode = MODE_BSW;
 };
 
@@ -151,6 +152,7 @@ void core_init(Core &k, int mode)
     }
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
+    k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
     const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
     for (DevCtx &x : k.ctx) {
@@ -204,7 +206,8 @@ Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_
 }
 
 /* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
-void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check,
+                  long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62)
 {
     x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
     x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
@@ -215,7 +218,7 @@ void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStr
     Plan *d_plan = (Plan *)x.plan.p;
     CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));
     const int max_elems = BSW_NBINS * 16;
-    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, n, k.c, k.mode, max_elems, tier8_check,
+    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, n, k.c, k.mode, max_elems, tier8_check, rlo, rhi, qlo, qhi,
                                                  (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
     CK(cudaGetLastError());
     CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
@@ -362,6 +365,23 @@ void extents(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long lo
     if (qhi <= qlo) { qlo = 0; qhi = 0; }
 }
 
+/* Estimate of the same ranges from every 32nd pair plus the first and last one.  bwa-mem2 fills its sequence
+ * arenas in pair order, so the estimate is normally exact; prep_kernel checks every pair against it on the
+ * device (Plan::oob_pairs) and the chunk is redone with the exact scan if any pair falls outside.  This keeps
+ * the calling host thread from reading all 56-byte records (0.56 GB per 10M pairs) before it can start a copy. */
+void extents_sampled(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long long &rhi, long long &qlo, long long &qhi)
+{
+    rlo = qlo = (long long)1 << 62; rhi = qhi = 0;
+    auto take = [&](int i) {
+        long long a = p[i].idr, b = a + std::max(p[i].len1, 0), c = p[i].idq, d = c + std::max(p[i].len2, 0);
+        rlo = std::min(rlo, a); rhi = std::max(rhi, b); qlo = std::min(qlo, c); qhi = std::max(qhi, d);
+    };
+    for (int i = first; i < first + cnt; i += 32) take(i);
+    for (int i = std::max(first, first + cnt - 32); i < first + cnt; ++i) take(i);
+    if (rhi <= rlo) { rlo = 0; rhi = 0; }
+    if (qhi <= qlo) { qlo = 0; qhi = 0; }
+}
+
 /* ---- BSW host-pointer call: chunked, pipelined, sharded ---------------------------------------
  * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
  * devices.  Each chunk uploads only the byte ranges of the sequence buffers its pairs touch, so the
@@ -385,6 +405,18 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
     const int chunk = std::max(1024, k.chunk_pairs);
     const int nchunks = (n + chunk - 1) / chunk;
     struct Job { int first, cnt; long long rlo, qlo; DevCtx *x; Slot *sl; };
+    auto upload = [&](Job &j, bool exact) {
+        long long rhi, qhi;
+        if (exact) extents(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
+        else extents_sampled(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
+        Slot &sl = *j.sl;
+        sl.ref.reserve((size_t)(rhi - j.rlo) + 64);
+        sl.qer.reserve((size_t)(qhi - j.qlo) + 64);
+        if (rhi > j.rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + j.rlo, (size_t)(rhi - j.rlo), cudaMemcpyHostToDevice, sl.stream));
+        if (qhi > j.qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + j.qlo, (size_t)(qhi - j.qlo), cudaMemcpyHostToDevice, sl.stream));
+        k.st.h2d_bytes += (rhi - j.rlo) + (qhi - j.qlo);
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, j.cnt, sl.stream, tier8_check, j.rlo, rhi, j.qlo, qhi);
+    };
     std::vector<Job> jobs(nchunks);
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
     auto stage_a = [&](int ci) {
@@ -392,18 +424,12 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
         j.x = &k.ctx[ci % nd]; j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
         slot_retire(k, *j.x, *j.sl);              /* its previous chunk must have landed */
-        long long rhi, qhi;
-        extents(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
         Slot &sl = *j.sl;
         CK(cudaSetDevice(j.x->dev));
         sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
-        sl.ref.reserve((size_t)(rhi - j.rlo) + 64);
-        sl.qer.reserve((size_t)(qhi - j.qlo) + 64);
         CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
-        if (rhi > j.rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + j.rlo, (size_t)(rhi - j.rlo), cudaMemcpyHostToDevice, sl.stream));
-        if (qhi > j.qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + j.qlo, (size_t)(qhi - j.qlo), cudaMemcpyHostToDevice, sl.stream));
-        k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - j.rlo) + (qhi - j.qlo);
-        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, j.cnt, sl.stream, tier8_check);
+        k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);
+        upload(j, false);
         sl.busy = true;
     };
     /* stage B: wait for the histogram, launch the DP kernels, download the results */
@@ -412,6 +438,11 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         Slot &sl = *j.sl;
         CK(cudaSetDevice(j.x->dev));
         const Plan *pl = plan_wait(sl, sl.stream);
+        if (pl->oob_pairs) {                      /* the sampled ranges missed a pair: redo with the exact scan */
+            upload(j, true);
+            pl = plan_wait(sl, sl.stream);
+            if (pl->oob_pairs) die("internal: exact extents still miss a pair");
+        }
         /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
         launch_bsw_dp(k, *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - j.rlo,
                       (const uint8_t *)sl.qer.p - j.qlo, j.cnt, w, sl.stream);
@@ -420,7 +451,7 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         k.st.d2h_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);
     };
     /* chunk c+nd is uploading while chunk c waits for its histogram: the copy engine never idles */
-    const int ahead = nd;
+    const int ahead = nd * std::max(1, std::min(BSW_NSLOT - 2, k.ahead));   /* chunks uploading ahead of the one waiting */
     for (int ci = 0; ci < std::min(ahead, nchunks); ++ci) stage_a(ci);
     for (int ci = 0; ci < nchunks; ++ci) {
         if (ci + ahead < nchunks) stage_a(ci + ahead);

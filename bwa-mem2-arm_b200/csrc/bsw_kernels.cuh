@@ -32,13 +32,14 @@ struct Plan {
     int max_len1;                  /* over all pairs                      */
     int max_len2_general;
     int bad_pairs;                 /* contract violations seen by prep    */
+    int oob_pairs;                 /* pairs whose bases fall outside the uploaded byte ranges */
 };
 
 enum { MODE_BSW = 0, MODE_KSWV = 1 };
 
 /* ------------------------------------------------------------------ 1. prep */
 __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Const c, int mode,
-                            int max_elems, int tier8_check,
+                            int max_elems, int tier8_check, long long rlo, long long rhi, long long qlo, long long qhi,
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, Plan *plan)
 {
     __shared__ int s_hist[BSW_NBINS + 2];
@@ -68,6 +69,10 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
         bool bad = len1 < 0 || len2 < 0 || (mode == MODE_BSW && h0 <= 0);
         if (tier8_check && (len1 >= BSW_MAX_SEQ_LEN8 || len2 >= BSW_MAX_SEQ_LEN8)) bad = true;
         if (bad) atomicAdd(&s_misc[3], 1);
+        /* the host estimates the byte ranges to upload from a sample of the pairs; verify them all here */
+        const long long ir = pairs[i].idr, iq = pairs[i].idq;
+        if (!bad && ((len1 > 0 && (ir < rlo || ir + len1 > rhi)) || (len2 > 0 && (iq < qlo || iq + len2 > qhi))))
+            atomicAdd(&plan->oob_pairs, 1);
         keys[i] = key; idx[i] = (uint32_t)i;
     }
     __syncthreads();
