@@ -149,28 +149,134 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
         hd = st_h2(WV, ve_);                                                          \
     }
 
-    int i = 0;
-    while (ks[0].act | ks[1].act) {
+    /* one local-SW cell with unpacked inputs (trailing row of a two-row pass): HD = H(i, j-1), E = E(i+1, j) */
+#define KSW_CELL_HE(TSEL, HD, E, Q, FF, H, EN)                                        \
+    {                                                                                 \
+        const uint32_t s_ = p_perm(LUTLO, LUTHI, p_xsel(Q, TSEL));                    \
+        H = p_max3_relu(p_add(HD, s_), E, FF);                                        \
+        EN = p_addmax_relu(H, NEG_OE_DEL, p_add(E, NEG_E_DEL));                       \
+        FF = p_addmax_relu(H, NEG_OE_INS, p_add(FF, NEG_E_INS));                      \
+    }
+
+    /* target base selector of both lanes for row `row` (advances the word queues) */
+    auto fetch_T = [&](int row) -> uint32_t {
         uint32_t tb[2];
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             tb[p] = 0u;
             if (ks[p].act) {
-                const uintptr_t adr = reinterpret_cast<uintptr_t>(ref + ks[p].idr) + (uintptr_t)i;
+                const uintptr_t adr = reinterpret_cast<uintptr_t>(ref + ks[p].idr) + (uintptr_t)row;
                 const uint32_t t = (wcur[p] >> (8 * (int)(adr & 3))) & 0xffu;
                 tb[p] = t > 4u ? 4u : t;
                 rot_ld_if(wcur[p], wnxt[p], reinterpret_cast<const uint32_t *>(adr & ~(uintptr_t)3) + 2, (adr & 3) == 3);
             }
         }
-        const uint32_t T = tb[0] * 0x0011u | tb[1] * 0x1100u;
+        return tb[0] * 0x0011u | tb[1] * 0x1100u;
+    };
+
+    /* columns [j, qmax) of row `row` with masks (one lane finished, the tail of the longer query, or the
+     * columns past the last full group), then the row's bookkeeping (A.2) */
+    auto finish_row = [&](int row, uint32_t T, int j, uint32_t f, uint32_t hd, uint32_t key) {
         const uint32_t ACT = (ks[0].act ? 0x0000ffffu : 0u) | (ks[1].act ? 0xffff0000u : 0u);
+        uint32_t jv = 0x00ff00ffu - (uint32_t)j * 0x00010001u;      /* 255 - j per lane */
+        for (; j < qmax; ++j) {
+            const uint32_t MK = ACT & (j < qmin ? 0xffffffffu : LONGER);
+            const uint32_t wv = he[j * S];
+            const uint32_t ve = st_e(wv);
+            uint32_t q_ = qs[j * S];
+            uint32_t x_ = p_xsel(q_, T);
+            uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
+            uint32_t h_ = p_max3_relu(p_add(hd, s_), ve, f) & MK;
+            uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(ve, NEG_E_DEL)) & MK;
+            f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS)) & MK;
+            hd = st_h(wv) & MK;
+            he[j * S] = st_pack(h_, en);
+            key = p_maxu(key, ((h_ << 8) + jv) & MK);
+            jv -= 0x00010001u;
+        }
+        {
+            const int ia = ks[0].act ? (int)((key >> 8) & 0xff) : 0;
+            const int ib = ks[1].act ? (int)(key >> 24) : 0;
+            rm[(long long)row * RS] = (uint16_t)(ia | (ib << 8));
+        }
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            KState &s = ks[p];
+            if (!s.act) continue;
+            const int kp = half_u(key, p);
+            const int imax = s.qlen > 0 ? (kp >> 8) : 0;
+            s.rows = row + 1;
+            if (imax > s.gmax) {
+                s.gmax = imax; s.te = row; s.qe = 255 - (kp & 0xff);
+                if ((is8 && s.gmax + shift >= 255) || s.gmax >= s.endsc) { s.act = 0; continue; }
+            }
+            if (row + 1 >= s.tlen) s.act = 0;
+        }
+    };
+
+    const uint32_t c0 = 0x00ff00ffu, c1 = 0x00fe00feu, c2 = 0x00fd00fdu, c3 = 0x00fc00fcu;
+    const int n4 = qmin & ~3;
+    int i = 0;
+    while (ks[0].act | ks[1].act) {
+        const bool both = ks[0].act && ks[1].act;
+        const uint32_t T = fetch_T(i);
         uint32_t f = 0, hd = 0, key = 0;
         int j = 0;
-        if (ACT == 0xffffffffu && qmin >= 4) {
+        if (both && n4 >= 8 && i + 1 < ks[0].tlen && i + 1 < ks[1].tlen) {
+            /* ---- two rows per pass: the leading row i runs one group of four columns ahead and hands
+             * H(i, .), E(i+1, .) to the trailing row i+1 in registers: per column one state load, one
+             * selector load and one state store serve two rows, and two f chains are in flight.  A lane
+             * that stops at row i (score threshold / 8-bit overflow) simply has its row i+1 ignored. */
+            const uint32_t T2 = fetch_T(i + 1);
+            const int G = n4 >> 2;
+            uint32_t fT = 0, keyT = 0, h1T = 0;            /* trailing chain; h1T = H(i, 4g-1) */
+            uint32_t q0 = qs[0], q1 = qs[S], q2 = qs[2 * S], q3 = qs[3 * S];
+            uint32_t ha, hb, hc, hd4, ea, eb, ec, ed;
+            {
+                const uint32_t v0 = he[0], v1 = he[S], v2 = he[2 * S], v3 = he[3 * S];
+                KSW_CELL(v0, q0, ha, ea) KSW_CELL(v1, q1, hb, eb) KSW_CELL(v2, q2, hc, ec) KSW_CELL(v3, q3, hd4, ed)
+                key = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd4 << 8) + c3);
+            }
+            uint32_t w0 = he[4 * S], w1 = he[5 * S], w2 = he[6 * S], w3 = he[7 * S];
+            uint32_t r0 = qs[4 * S], r1 = qs[5 * S], r2 = qs[6 * S], r3 = qs[7 * S];
+            for (int g = 0; g + 1 < G; ++g) {
+                const int kl = 4 * g + 4, kt = 4 * g;
+                uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, y0 = 0, y1 = 0, y2 = 0, y3 = 0;
+                if (g + 2 < G) {                           /* loads of leading group g+2 */
+                    x0 = he[(kl + 4) * S]; x1 = he[(kl + 5) * S]; x2 = he[(kl + 6) * S]; x3 = he[(kl + 7) * S];
+                    y0 = qs[(kl + 4) * S]; y1 = qs[(kl + 5) * S]; y2 = qs[(kl + 6) * S]; y3 = qs[(kl + 7) * S];
+                }
+                uint32_t na, nb, nc, nd, fa, fb, fc, fd;
+                KSW_CELL(w0, r0, na, fa) KSW_CELL(w1, r1, nb, fb) KSW_CELL(w2, r2, nc, fc) KSW_CELL(w3, r3, nd, fd)
+                key = p_maxu(key, p_maxu(p_max3u((na << 8) + c0, (nb << 8) + c1, (nc << 8) + c2), (nd << 8) + c3) - (uint32_t)kl * 0x00010001u);
+                uint32_t ta, tb_, tc, td, ua, ub, uc, ud;
+                KSW_CELL_HE(T2, h1T, ea, q0, fT, ta, ua) he[(kt + 0) * S] = st_pack(ta, ua);
+                KSW_CELL_HE(T2, ha, eb, q1, fT, tb_, ub) he[(kt + 1) * S] = st_pack(tb_, ub);
+                KSW_CELL_HE(T2, hb, ec, q2, fT, tc, uc)  he[(kt + 2) * S] = st_pack(tc, uc);
+                KSW_CELL_HE(T2, hc, ed, q3, fT, td, ud)  he[(kt + 3) * S] = st_pack(td, ud);
+                keyT = p_maxu(keyT, p_maxu(p_max3u((ta << 8) + c0, (tb_ << 8) + c1, (tc << 8) + c2), (td << 8) + c3) - (uint32_t)kt * 0x00010001u);
+                h1T = hd4; ha = na; hb = nb; hc = nc; hd4 = nd; ea = fa; eb = fb; ec = fc; ed = fd;
+                q0 = r0; q1 = r1; q2 = r2; q3 = r3;
+                w0 = x0; w1 = x1; w2 = x2; w3 = x3; r0 = y0; r1 = y1; r2 = y2; r3 = y3;
+            }
+            {   /* trailing group G-1 */
+                const int kt = n4 - 4;
+                uint32_t ta, tb_, tc, td, ua, ub, uc, ud;
+                KSW_CELL_HE(T2, h1T, ea, q0, fT, ta, ua) he[(kt + 0) * S] = st_pack(ta, ua);
+                KSW_CELL_HE(T2, ha, eb, q1, fT, tb_, ub) he[(kt + 1) * S] = st_pack(tb_, ub);
+                KSW_CELL_HE(T2, hb, ec, q2, fT, tc, uc)  he[(kt + 2) * S] = st_pack(tc, uc);
+                KSW_CELL_HE(T2, hc, ed, q3, fT, td, ud)  he[(kt + 3) * S] = st_pack(td, ud);
+                keyT = p_maxu(keyT, p_maxu(p_max3u((ta << 8) + c0, (tb_ << 8) + c1, (tc << 8) + c2), (td << 8) + c3) - (uint32_t)kt * 0x00010001u);
+            }
+            /* columns past the last full group: row i first (its outputs feed row i+1), then row i+1 */
+            finish_row(i, T, n4, f, hd, key);
+            finish_row(i + 1, T2, n4, fT, hd4, keyT);
+            i += 2;
+            continue;
+        }
+        if (both && qmin >= 4) {
             /* both lanes live: unmasked groups of four columns, next group's loads issued first.
              * key = max over (h << 8 | 255 - j): row maximum and its FIRST column. */
-            const int n4 = qmin & ~3;
-            const uint32_t c0 = 0x00ff00ffu, c1 = 0x00fe00feu, c2 = 0x00fd00fdu, c3 = 0x00fc00fcu;
             uint32_t v0 = he[0], v1 = he[S], v2 = he[2 * S], v3 = he[3 * S];
             uint32_t q0 = qs[0], q1 = qs[S], q2 = qs[2 * S], q3 = qs[3 * S];
 #define KSW_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                     \
@@ -194,41 +300,7 @@ BSW_HD void kswv_packed_thread(const Const &c, int is8, const PairIn &A, const P
             j += 4;
 #undef KSW_GROUP
         }
-        uint32_t jv = 0x00ff00ffu - (uint32_t)j * 0x00010001u;      /* 255 - j per lane */
-        /* one lane finished, or the tail of the longer query: masked cells */
-        for (; j < qmax; ++j) {
-            const uint32_t MK = ACT & (j < qmin ? 0xffffffffu : LONGER);
-            const uint32_t wv = he[j * S];
-            const uint32_t ve = st_e(wv);
-            uint32_t q_ = qs[j * S];
-            uint32_t x_ = p_xsel(q_, T);
-            uint32_t s_ = p_perm(LUTLO, LUTHI, x_);
-            uint32_t h_ = p_max3_relu(p_add(hd, s_), ve, f) & MK;
-            uint32_t en = p_addmax_relu(h_, NEG_OE_DEL, p_add(ve, NEG_E_DEL)) & MK;
-            f = p_addmax_relu(h_, NEG_OE_INS, p_add(f, NEG_E_INS)) & MK;
-            hd = st_h(wv) & MK;
-            he[j * S] = st_pack(h_, en);
-            key = p_maxu(key, ((h_ << 8) + jv) & MK);
-            jv -= 0x00010001u;
-        }
-        {
-            const int ia = ks[0].act ? (int)((key >> 8) & 0xff) : 0;
-            const int ib = ks[1].act ? (int)(key >> 24) : 0;
-            rm[(long long)i * RS] = (uint16_t)(ia | (ib << 8));
-        }
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            KState &s = ks[p];
-            if (!s.act) continue;
-            const int kp = half_u(key, p);
-            const int imax = s.qlen > 0 ? (kp >> 8) : 0;
-            s.rows = i + 1;
-            if (imax > s.gmax) {
-                s.gmax = imax; s.te = i; s.qe = 255 - (kp & 0xff);
-                if ((is8 && s.gmax + shift >= 255) || s.gmax >= s.endsc) { s.act = 0; continue; }
-            }
-            if (i + 1 >= s.tlen) s.act = 0;
-        }
+        finish_row(i, T, j, f, hd, key);
         ++i;
     }
 
