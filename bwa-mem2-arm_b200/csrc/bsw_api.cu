@@ -462,10 +462,23 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
 }
 
 /* ---- kswv host-pointer call: one slice per device (slot 0), synchronous -------------------------- */
+void host_call_kswv_part(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
+                         int n, int is8, int phase);
+
+/* bounded device scratch: the row-maximum scratch is (max len1) x (pairs) x 2 B, so large calls go in parts of
+ * BSW_CUDA_KSWV_PART pairs (phase 0 indexes aln by position, phase 1 by regid) */
 void host_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
                     int n, int is8, int phase)
 {
     k.st.calls++;
+    const int part = std::max(1024, env_int("BSW_CUDA_KSWV_PART", 1 << 21));
+    for (int off = 0; off < n; off += part)
+        host_call_kswv_part(k, pairs + off, ref, qer, phase == 0 ? aln + off : aln, std::min(part, n - off), is8, phase);
+}
+
+void host_call_kswv_part(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
+                         int n, int is8, int phase)
+{
     if (n <= 0) return;
     if (!pairs || !ref || !qer || !aln) die("null buffer passed to kswv getScores");
     const int nd = (int)k.ctx.size();

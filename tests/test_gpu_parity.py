@@ -322,3 +322,49 @@ def test_small_and_repeated_calls(ora, sw):
         o = P.copy(); ora.bsw_batch(o, r, q, prm, 100, 4)
         g = P.copy(); sw.getScores8(g, r, q, len(g), 1, 100)
         _assert_same(o, g)
+
+
+def test_concurrent_handles_from_host_threads(ora, bsw):
+    """The boundary is called concurrently from every worker thread of the host pipeline, each with its own
+    object (SURVEY.md 8b "Threading"): four threads, four handles, same device, different batches."""
+    import threading
+    prm = ora.make_params()
+    jobs = []
+    for k in range(4):
+        d = ora.gen_bsw(6000, seed=0x700 + k)
+        P, r, q = d["left"]
+        o = P.copy(); ora.bsw_batch(o, r, q, prm, 100, 4)
+        jobs.append((P, r, q, o))
+    out = [None] * 4
+
+    def work(k):
+        P, r, q, _ = jobs[k]
+        sw = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        g = None
+        for _ in range(3):                       # repeated calls, as a worker does per task
+            g = P.copy(); sw.getScores16(g, r, q, len(g), 1, 100)
+        sw.close()
+        out[k] = g
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    for t in th: t.start()
+    for t in th: t.join()
+    for k in range(4):
+        _assert_same(jobs[k][3], out[k])
+
+
+def test_kswv_call_in_parts(ora, bsw, monkeypatch):
+    """Large kswv calls are served in parts (bounded row-maximum scratch): same answers, phase 0 and 1."""
+    monkeypatch.setenv("BSW_CUDA_KSWV_PART", "3000")
+    prm = ora.make_params()
+    K, kr, kq = ora.gen_kswv(10000, seed=0x77)
+    ao = np.zeros(len(K), ora.KSWR); ag = np.zeros(len(K), bsw.KSWR)
+    ora.kswv_batch(K, kr, kq, ao, prm, 1, 0, 8)
+    ks2 = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    ks2.getScores8(K, kr, kq, ag, len(K), 1, 0)
+    assert (ao == ag).all()
+    p1, r1, q1 = ora.kswv_phase1_inputs(K, kr, kq, ao)
+    ora.kswv_batch(p1, r1, q1, ao, prm, 1, 1, 8)
+    ks2.getScores8(p1, r1, q1, ag, len(p1), 1, 1)
+    ks2.close()
+    assert (ao == ag).all()
