@@ -5,8 +5,8 @@
  * kswv::getScores8/16 (bwa-mem2 src/bandedSWA.cpp, src/kswv.cpp; call sites in
  * mem_chain2aln_across_reads_V2 / mem_sam_pe_batch, SURVEY.md sections 3, 8b).
  * One handle per calling host thread (as the reference constructs one object
- * per worker); a handle owns, per device, a stream, grow-only device scratch
- * and a pinned mailbox.  No CPU fallback: any CUDA failure is fatal, as in the
+ * per worker); a handle owns, per device, four chunk slots (stream, grow-only
+ * device scratch, pinned mailbox) and one priority stream per query-length bin.  No CPU fallback: any CUDA failure is fatal, as in the
  * reference (fprintf + exit).
  */
 #include <cstdio>
@@ -56,13 +56,11 @@ struct Slot {
     cudaEvent_t done = nullptr;
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
     Plan *h_plan = nullptr;          /* pinned mailbox */
-    /* host-side bookkeeping of the chunk in flight */
-    int first = 0, cnt = 0; bool busy = false;
+    bool busy = false;               /* a chunk is in flight on this slot */
 };
 
 struct DevCtx {
     int dev = 0;
-    cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     /* one stream per query-length bin: the bins' kernels run concurrently, so one bin's tail wave
      * overlaps the next bin's blocks (fork/join on events around them) */
@@ -127,7 +125,6 @@ void core_init(Core &k, int mode)
         DevCtx &x = k.ctx[i];
         x.dev = devs[i];
         CK(cudaSetDevice(x.dev));
-        CK(cudaStreamCreateWithFlags(&x.stream, cudaStreamNonBlocking));
         CK(cudaEventCreate(&x.ev0)); CK(cudaEventCreate(&x.ev1));
         {
             int lo = 0, hi = 0;                       /* numerically lowest = highest priority */
@@ -172,7 +169,6 @@ void core_destroy(Core &k)
 {
     for (DevCtx &x : k.ctx) {
         cudaSetDevice(x.dev);
-        cudaStreamSynchronize(x.stream);
         for (Slot &sl : x.slot) {
             if (sl.stream) cudaStreamSynchronize(sl.stream);
             sl.pairs.release(); sl.ref.release(); sl.qer.release(); sl.aln.release();
@@ -186,7 +182,6 @@ void core_destroy(Core &k)
         cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
         if (x.fork_ev) cudaEventDestroy(x.fork_ev);
         for (int qb = 1; qb <= BSW_NBINS; ++qb) { if (x.bin_stream[qb]) cudaStreamDestroy(x.bin_stream[qb]); if (x.bin_ev[qb]) cudaEventDestroy(x.bin_ev[qb]); }
-        cudaStreamDestroy(x.stream);
     }
     k.ctx.clear();
 }
