@@ -107,11 +107,14 @@ BSW_HD int mx(int a, int b) { return a > b ? a : b; }
  * one unsigned 16-bit lane. */
 #define BSW_PACKED_MAX_SCORE 255
 #define BSW_PACKED_MAX_QLEN  255
+/* the BSW sweep runs up to 3 columns past the query end (bsw_core2.cuh): column indices must still fit 8 bits */
+#define BSW_PACKED_MAX_QLEN_BSW 252
+#define BSW_SWEEP_SLACK 4
 
 BSW_HD bool packed_eligible(const Const &c, int len1, int len2, int h0)
 {
     if (len1 < 0 || len2 < 0 || h0 <= 0) return false;
-    if (len2 > BSW_PACKED_MAX_QLEN) return false;
+    if (len2 > BSW_PACKED_MAX_QLEN_BSW) return false;
     long long bound = (long long)h0 + (long long)mn(len1, len2) * c.a;
     if (c.a > 120 || c.b > 120) return false;
     return bound <= BSW_PACKED_MAX_SCORE;

@@ -19,6 +19,7 @@
 #include <stdint.h>
 #include "../../include/bsw_cuda.h"
 #include "bsw_core.cuh"
+#include "bsw_core2.cuh"
 #include "kswv_core.cuh"
 
 namespace bswk {
@@ -51,7 +52,8 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
     if (i < n) {
         const int len1 = pairs[i].len1, len2 = pairs[i].len2, h0 = pairs[i].h0;
         bool ok = (mode == MODE_BSW) ? packed_eligible(c, len1, len2, h0) : kswv_packed_eligible(c, len1, len2);
-        const int qb = (len2 + 1 + 15) >> 4;
+        /* columns a thread needs: len2 + 1 (kswv), len2 + 4 (BSW: the sweep's slack, bsw_core2.cuh) */
+        const int qb = (len2 + (mode == MODE_BSW ? BSW_SWEEP_SLACK : 1) + 15) >> 4;
         if (ok && qb * 16 > max_elems) ok = false;
         uint32_t key = 0;
         if (ok) {
@@ -112,7 +114,8 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
     if (pa >= 0) {
         PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
         PairOut oa, ob;
-        bsw_packed_thread<32, COUNT, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        if (COUNT) bsw_packed_thread<32, true, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        else bsw_packed_thread2<32, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
         int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
         o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
         my_cells += (unsigned long long)oa.cells;

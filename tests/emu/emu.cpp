@@ -6,6 +6,7 @@
 #include <cstring>
 #include <cstdint>
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core.cuh"
+#include "../../bwa-mem2-arm_b200/csrc/bsw_core2.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/kswv_core.cuh"
 #include "../../include/bsw_cuda.h"
 
@@ -45,8 +46,8 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         const bool sym = c.oe_del == c.oe_ins;
         if (count_cells) { if (sym) bsw_packed_thread<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
                            else bsw_packed_thread<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
-        else { if (sym) bsw_packed_thread<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-               else bsw_packed_thread<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+        else { if (sym) bsw_packed_thread2<1, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+               else bsw_packed_thread2<1, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
     }

@@ -20,7 +20,8 @@ for l in txt[start + 1:]:
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
     if m:
         ins.append((m.group(2).strip(), cur))
-out = subprocess.run(f"ncu -i {rep} --page source --csv", shell=True, capture_output=True, text=True).stdout
+skip = os.environ.get("NCU_SKIP", "0")
+out = subprocess.run(f"ncu -i {rep} --launch-skip {skip} --launch-count 1 --page source --csv", shell=True, capture_output=True, text=True).stdout
 rows = list(csv.reader(out.split("\n")))
 hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
 hdr = rows[hi]; data = [r for r in rows[hi + 1:] if len(r) == len(hdr) and r[0] != "Address"][:len(ins)]
