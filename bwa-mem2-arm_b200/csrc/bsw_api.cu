@@ -155,8 +155,9 @@ void core_init(Core &k, int mode)
     for (DevCtx &x : k.ctx) {
         CK(cudaSetDevice(x.dev));
         if (max_smem > x.smem_optin) die("device shared memory too small for the packed kernels");
-        const void *fns[] = { (const void *)bsw_packed_kernel<false, false>, (const void *)bsw_packed_kernel<false, true>,
-                              (const void *)bsw_packed_kernel<true, false>, (const void *)bsw_packed_kernel<true, true>,
+        const void *fns[] = { (const void *)bsw_packed_kernel<false, false, false>, (const void *)bsw_packed_kernel<false, true, false>,
+                              (const void *)bsw_packed_kernel<false, false, true>, (const void *)bsw_packed_kernel<false, true, true>,
+                              (const void *)bsw_packed_kernel<true, false, false>, (const void *)bsw_packed_kernel<true, true, false>,
                               (const void *)kswv_packed_kernel<false>, (const void *)kswv_packed_kernel<true> };
         for (const void *fn : fns) {
             CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
@@ -201,23 +202,23 @@ Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_
 }
 
 /* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
-void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check,
+void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_qer, int n, cudaStream_t s, int tier8_check,
                   long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62)
 {
     x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
     x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
     size_t tmp_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp_bytes, (uint32_t *)nullptr, (uint32_t *)nullptr,
-                                                 (uint32_t *)nullptr, (uint32_t *)nullptr, n, 0, 25, s));
+                                                 (uint32_t *)nullptr, (uint32_t *)nullptr, n, 0, BSW_KEY_BITS, s));
     x.cubtmp.reserve(tmp_bytes);
     Plan *d_plan = (Plan *)x.plan.p;
     CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));
     const int max_elems = BSW_NBINS * 16;
-    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, n, k.c, k.mode, max_elems, tier8_check, rlo, rhi, qlo, qhi,
+    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, d_qer, n, k.c, k.mode, max_elems, tier8_check, rlo, rhi, qlo, qhi,
                                                  (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
     CK(cudaGetLastError());
     CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
-                                                 (uint32_t *)x.idx_a.p, (uint32_t *)x.idx_b.p, n, 0, 25, s));
+                                                 (uint32_t *)x.idx_a.p, (uint32_t *)x.idx_b.p, n, 0, BSW_KEY_BITS, s));
     CK(cudaMemcpyAsync(x.h_plan, d_plan, sizeof(Plan), cudaMemcpyDeviceToHost, s));
     k.st.kernel_launches += 1 + 8;    /* prep + the sort's internal launches (upper bound of cub's onesweep path) */
 }
@@ -234,9 +235,9 @@ const Plan *plan_wait(Slot &x, cudaStream_t s)
     return x.h_plan;
 }
 
-const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, int n, cudaStream_t s, int tier8_check)
+const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_qer, int n, cudaStream_t s, int tier8_check)
 {
-    plan_enqueue(k, x, d_pairs, n, s, tier8_check);
+    plan_enqueue(k, x, d_pairs, d_qer, n, s, tier8_check);
     return plan_wait(x, s);
 }
 
@@ -247,7 +248,7 @@ void launch_bsw(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint
                 int n, int w, cudaStream_t s, int tier8_check)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, n, s, tier8_check);
+    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, tier8_check);
     launch_bsw_dp(k, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
 }
 
@@ -258,23 +259,33 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     CK(cudaEventRecord(x.fork_ev, s));
-    for (int qb = BSW_NBINS; qb >= 1; --qb) {            /* longest queries first */
-        const int cnt = pl->hist[qb];
-        if (cnt <= 0) continue;
-        const int NE = qb * 16, grid = (cnt + 63) / 64;
-        cudaStream_t bs = x.bin_stream[qb];
-        CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
-        /* template flags: exact cell counting; symmetric gap sums (one packed add less per cell) */
-        auto kern = k.count_cells ? (k.c.oe_del == k.c.oe_ins ? bsw_packed_kernel<true, true> : bsw_packed_kernel<true, false>)
-                                  : (k.c.oe_del == k.c.oe_ins ? bsw_packed_kernel<false, true> : bsw_packed_kernel<false, false>);
-        kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
-                                                        NE, k.c, w, (unsigned long long *)x.cells.p);
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(x.bin_ev[qb], bs));
-        CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
-        k.st.kernel_launches++;
-        n_packed += cnt;
-    }
+    unsigned used = 0;
+    /* sorted order: pairs whose query holds an N first (key bit 25), then the others; each longest query first */
+    for (int pass = 0; pass < 2; ++pass)
+        for (int qb = BSW_NBINS; qb >= 1; --qb) {
+            const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
+            if (cnt <= 0) continue;
+            const int NE = qb * 16, grid = (cnt + 63) / 64;
+            cudaStream_t bs = x.bin_stream[qb];
+            if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+            used |= 1u << qb;
+            /* template flags: exact cell counting (first-generation row loop); symmetric gap sums (one packed add less
+             * per cell); general score table for queries with an N */
+            const bool sym = k.c.oe_del == k.c.oe_ins;
+            auto kern = k.count_cells ? (sym ? bsw_packed_kernel<true, true, false> : bsw_packed_kernel<true, false, false>)
+                      : pass == 0     ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
+                                      : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
+            kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
+                                                            NE, k.c, w, (unsigned long long *)x.cells.p);
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+            n_packed += cnt;
+        }
+    for (int qb = BSW_NBINS; qb >= 1; --qb)
+        if (used & (1u << qb)) {
+            CK(cudaEventRecord(x.bin_ev[qb], x.bin_stream[qb]));
+            CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
+        }
     if (pl->n_general > 0) {
         /* bounded scratch: at most ~1 GiB of eh rows per launch */
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2);
@@ -299,7 +310,7 @@ void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, con
                  bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, n, s, 0);
+    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, 0);
     const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
@@ -410,7 +421,7 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         if (rhi > j.rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + j.rlo, (size_t)(rhi - j.rlo), cudaMemcpyHostToDevice, sl.stream));
         if (qhi > j.qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + j.qlo, (size_t)(qhi - j.qlo), cudaMemcpyHostToDevice, sl.stream));
         k.st.h2d_bytes += (rhi - j.rlo) + (qhi - j.qlo);
-        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, j.cnt, sl.stream, tier8_check, j.rlo, rhi, j.qlo, qhi);
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - j.qlo, j.cnt, sl.stream, tier8_check, j.rlo, rhi, j.qlo, qhi);
     };
     std::vector<Job> jobs(nchunks);
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */

@@ -42,14 +42,52 @@ static inline uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) { s &= 31; retu
 static inline uint32_t ldg32(const uint32_t *p) { return *p; }
 #endif
 
+/* Row context of the second-generation kernel.  QN = false (no N / invalid base in either query, decided by
+ * prep_kernel): the substitution score of both lanes is ONE PRMT into a per-row byte table, LA = scores of lane
+ * A's target base against query bases 0..3, LB = the same for lane B; the stored selector picks byte q (and its
+ * sign).  QN = true: the general form of bsw_core.cuh (LOP3 index + PRMT into the constant 8-entry table). */
+struct RowCtx2 : RowCtx { uint32_t LA, LB; };
+
+template <bool SYM, bool QN>
+BSW_HD void bsw_cell2(const RowCtx2 &r, uint32_t w, uint32_t q, uint32_t &f, uint32_t &h, uint32_t &en)
+{
+    const uint32_t e = st_e(w), hs = st_h2(w, e);
+    const uint32_t s = QN ? p_perm(r.LUTLO, r.LUTHI, p_xsel(q, r.T)) : p_perm(r.LA, r.LB, q);
+    const uint32_t M = p_addmin(hs, s, hs * r.GATE);
+    h = p_max3(M, e, f);
+    if (SYM) {
+        const uint32_t u = p_add(M, r.NOD);
+        en = p_addmax_relu(e, r.NED, u);
+        f = p_addmax_relu(f, r.NEI, u);
+    } else {
+        en = p_addmax_relu(M, r.NOD, p_add(e, r.NED));
+        f = p_addmax_relu(M, r.NOI, p_add(f, r.NEI));
+    }
+}
+
+/* selector of query column bases (qa, qb), both already clamped to 0..4 */
+template <bool QN>
+BSW_HD uint16_t bsw_selector(uint32_t qa, uint32_t qb)
+{
+    if (QN) return (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+    qa &= 3u; qb &= 3u;
+    return (uint16_t)(((12u | qb) << 12) | ((4u | qb) << 8) | ((8u | qa) << 4) | qa);
+}
+
+/* per-row score table of one lane (QN = false): byte q = score(t, q) for q = 0..3; t8 = 8 * target base (32 = N) */
+BSW_HD uint32_t bsw_lutrow(uint32_t mis, uint32_t x, uint32_t amb, uint32_t t8)
+{
+    return t8 >= 32u ? amb : (mis ^ shl_clamp(x, (int)t8));
+}
+
 /* one unchecked group of four columns (both lanes): cells, state stores, row-max key */
 #define BSW2_GROUP(V0, V1, V2, V3, Q0, Q1, Q2, Q3)                                                 \
     {                                                                                              \
         uint32_t ha, hb, hc, hd, ea, eb, ec, ed;                                                   \
-        bsw_cell<SYM>(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);                    \
-        bsw_cell<SYM>(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);                    \
-        bsw_cell<SYM>(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);                    \
-        bsw_cell<SYM>(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);                    \
+        bsw_cell2<SYM, QN>(r, V0, Q0, f, ha, ea); hp[(k + 0) * S] = st_pack(h1, ea);                    \
+        bsw_cell2<SYM, QN>(r, V1, Q1, f, hb, eb); hp[(k + 1) * S] = st_pack(ha, eb);                    \
+        bsw_cell2<SYM, QN>(r, V2, Q2, f, hc, ec); hp[(k + 2) * S] = st_pack(hb, ec);                    \
+        bsw_cell2<SYM, QN>(r, V3, Q3, f, hd, ed); hp[(k + 3) * S] = st_pack(hc, ed);                    \
         h1 = hd;                                                                                   \
         const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3); \
         key = p_maxu(key, g + (uint32_t)k * 0x00010001u);                                          \
@@ -65,7 +103,7 @@ static inline uint32_t ldg32(const uint32_t *p) { return *p; }
         h1 &= ~(cap & QF);                                                                         \
         f &= ~cap;                                                                                 \
         uint32_t h_, e_;                                                                           \
-        bsw_cell<SYM>(r, V, Q, f, h_, e_);                                                         \
+        bsw_cell2<SYM, QN>(r, V, Q, f, h_, e_);                                                         \
         hp[(k + (C)) * S] = st_pack(h1, e_);                                                       \
         h1 = h_;                                                                                   \
         gk[C] = (h_ << 8);                                                                         \
@@ -78,8 +116,8 @@ static inline uint32_t ldg32(const uint32_t *p) { return *p; }
  * computes zeros from its cut on.  QF: lane mask of the lanes whose end == qlen.
  * Out: h1save = per lane the h of its last in-range cell; key = max over (h << 8 | j).
  */
-template <int S, bool SYM>
-BSW_HD void bsw_sweep2(const RowCtx &r, uint32_t *he, const uint16_t *qs, int j0, int cA, int cB, uint32_t QF,
+template <int S, bool SYM, bool QN>
+BSW_HD void bsw_sweep2(const RowCtx2 &r, uint32_t *he, const uint16_t *qs, int j0, int cA, int cB, uint32_t QF,
                        uint32_t &f, uint32_t &h1, uint32_t &key, uint32_t &h1save)
 {
     uint32_t *hp = he + j0 * S;
@@ -136,15 +174,22 @@ BSW_HD void twin_init(TWin &t, const uint8_t *ref, int idr, int tlen, bool act)
 BSW_HD uint32_t twin_refill(TWin &t, int r)
 {
     const uint32_t win = funnel_r(t.lo, t.hi, t.sh);
+#if defined(__CUDA_ARCH__)
+    /* rotate and load IN PLACE: written as `hi = *p` the compiler loads into a temporary and moves it, and the move
+     * waits for the load right here (5 % of the kernel time in profile s1) instead of four rows later */
+    asm volatile("{ .reg .pred q; setp.lt.s32 q, %3, %4; mov.b32 %0, %1; mov.b32 %1, 0; @q ld.global.nc.u32 %1, [%2]; }"
+                 : "+r"(t.lo), "+r"(t.hi) : "l"(t.wp + r + 2), "r"(r + 2), "r"(t.nwords));
+#else
     t.lo = t.hi;
     t.hi = (r + 2 < t.nwords) ? ldg32(t.wp + r + 2) : 0u;
+#endif
     return p_minu4(win, 0x04040404u);
 }
 
 /*
  * One thread, two pairs (see bsw_core.cuh for the layout of he / qs and the exactness notes).
  */
-template <int S, bool SYM>
+template <int S, bool SYM, bool QN>
 BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                                uint32_t *he, uint16_t *qs, PairOut &oa, PairOut &ob)
@@ -208,7 +253,7 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
                     uint32_t qa = (j < qlen[0]) ? ((by[0] >> (8 * u)) & 0xffu) : 0u;
                     uint32_t qb = (j < qlen[1]) ? ((by[1] >> (8 * u)) & 0xffu) : 0u;
                     qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
-                    qs[j * S] = (uint16_t)(((8u | qb) << 12) | (qb << 8) | ((8u | qa) << 4) | qa);
+                    qs[j * S] = bsw_selector<QN>(qa, qb);
                 }
             }
             cw0[0] = cw1[0]; cw1[0] = nw[0]; cw0[1] = cw1[1]; cw1[1] = nw[1];
@@ -222,8 +267,10 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
         if (clean[1]) he[mn(qlen[1], wb[1] + 1) * S] &= 0x0000ffffu;
     }
 
-    RowCtx r;
+    RowCtx2 r;
     r.LUTLO = launder(lut_lo(c)); r.LUTHI = launder(lut_hi(c));
+    r.LA = r.LB = 0;
+    const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
     r.NOD = pack2(-c.oe_del, -c.oe_del); r.NOI = pack2(-c.oe_ins, -c.oe_ins);
     r.NED = pack2(-c.e_del, -c.e_del);   r.NEI = pack2(-c.e_ins, -c.e_ins);
     r.GATE = (uint32_t)(c.a + 1);
@@ -245,7 +292,8 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
     while (act) {
         /* ---------------- row prologue ---------------- */
         if ((i & 3) == 0) { winA = twin_refill(tw[0], i >> 2); winB = twin_refill(tw[1], i >> 2); }
-        r.T = (winA & 0xffu) * 0x0011u | (winB & 0xffu) * 0x1100u;
+        if (QN) r.T = (winA & 0xffu) * 0x0011u | (winB & 0xffu) * 0x1100u;
+        else { r.LA = bsw_lutrow(MISW, XW, AMBW, (winA & 0xffu) * 8u); r.LB = bsw_lutrow(MISW, XW, AMBW, (winB & 0xffu) * 8u); }
         winA >>= 8; winB >>= 8;
         hcol = p_addmax_relu(hcol, r.NED, 0u);
 
@@ -277,15 +325,16 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
             if (!act) break;
         }
         const int both = act == 3;
-        const int lv = (act & 1) ? 0 : 1;                          /* a live lane */
+        const bool la = (act & 1) != 0;                            /* lane A is live (else lane B is); selects, not array
+                                                                    * indexing by a run-time lane (that put st[]/clean[] in local memory) */
         uint32_t f = 0, key = 0, h1save = 0;
-        const bool fast = (both ? (clean[0] & clean[1] & (st[0] == st[1])) : clean[lv]) != 0;
+        const bool fast = (both ? (clean[0] & clean[1] & (st[0] == st[1])) : (la ? clean[0] : clean[1])) != 0;
         if (fast) {
-            const int j0 = st[lv];
+            const int j0 = la ? st[0] : st[1];
             const int cA = (act & 1) ? end[0] : end[1], cB = (act & 2) ? end[1] : end[0];   /* a dead lane mirrors the live one */
             const uint32_t QF = (end[0] == qlen[0] ? 0x0000ffffu : 0u) | (end[1] == qlen[1] ? 0xffff0000u : 0u);
             uint32_t h1 = j0 == 0 ? hcol : 0u;
-            bsw_sweep2<S, SYM>(r, he, qs, j0, cA, cB, QF, f, h1, key, h1save);
+            bsw_sweep2<S, SYM, QN>(r, he, qs, j0, cA, cB, QF, f, h1, key, h1save);
         } else {
             /* generic masked row: each lane exactly over its own [st, end); entries outside are left untouched */
             int sp[2], ep[2];
@@ -297,7 +346,7 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
                 const uint32_t MK = ((j >= sp[0] && j < ep[0]) ? 0x0000ffffu : 0u) | ((j >= sp[1] && j < ep[1]) ? 0xffff0000u : 0u);
                 const uint32_t v = he[j * S];
                 uint32_t h_, en, fn = f;
-                bsw_cell<SYM>(r, v, qs[j * S], fn, h_, en);
+                bsw_cell2<SYM, QN>(r, v, qs[j * S], fn, h_, en);
                 he[j * S] = st_pack(h1 & MK, en & MK) | (v & ~MK);
                 f = fn & MK;
                 h1 = (h_ & MK) | (h1 & ~MK);

@@ -28,7 +28,8 @@ namespace bswk {
 #define BSW_WARP_ELEM_BYTES 192 /* per element per warp: 32 x (state word + uint16 selector) */
 
 struct Plan {
-    int hist[BSW_NBINS + 2];       /* [qb] = packed-admissible pairs with ceil((len2+1)/16) == qb */
+    int hist[BSW_NBINS + 2];       /* [qb] = packed-admissible pairs whose rows need qb x 16 columns */
+    int hist_n[BSW_NBINS + 2];     /* BSW: the subset of them whose query holds an N / invalid base (sorted first; counted here, not in hist) */
     int n_general;                 /* pairs routed to the general kernel */
     int max_len1;                  /* over all pairs                      */
     int max_len2_general;
@@ -39,13 +40,31 @@ struct Plan {
 enum { MODE_BSW = 0, MODE_KSWV = 1 };
 
 /* ------------------------------------------------------------------ 1. prep */
-__global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Const c, int mode,
+/* does the query hold a base > 3?  Aligned word reads; stays inside the words that hold the query's bytes */
+__device__ __forceinline__ bool query_has_n(const uint8_t *__restrict__ qer, long long idq, int len2)
+{
+    const uintptr_t a = reinterpret_cast<uintptr_t>(qer + idq);
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+    const int off = (int)(a & 3), nbytes = off + len2, nw = (nbytes + 3) >> 2;
+    uint32_t acc = 0;
+    for (int k = 0; k < nw; ++k) {
+        uint32_t w = __ldg(wp + k);
+        if (k == 0) w &= 0xffffffffu << (8 * off);
+        if (k == nw - 1 && (nbytes & 3)) w &= 0xffffffffu >> (8 * (4 - (nbytes & 3)));
+        acc |= w;
+    }
+    return (acc & 0xfcfcfcfcu) != 0;
+}
+
+#define BSW_KEY_BITS 26         /* (has-N flag) << 25 | (len2 + 1) << 16 | (len1 / 2) << 8 | h0 */
+
+__global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ qer, int n, Const c, int mode,
                             int max_elems, int tier8_check, long long rlo, long long rhi, long long qlo, long long qhi,
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, Plan *plan)
 {
-    __shared__ int s_hist[BSW_NBINS + 2];
+    __shared__ int s_hist[2 * (BSW_NBINS + 2)];
     __shared__ int s_misc[4];
-    if (threadIdx.x < BSW_NBINS + 2) s_hist[threadIdx.x] = 0;
+    if (threadIdx.x < 2 * (BSW_NBINS + 2)) s_hist[threadIdx.x] = 0;
     if (threadIdx.x < 4) s_misc[threadIdx.x] = 0;
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,7 +81,12 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
             const uint32_t l1 = (uint32_t)(len1 >> 1) > 255u ? 255u : (uint32_t)(len1 >> 1);
             const uint32_t hh = mode == MODE_BSW ? ((uint32_t)h0 > 255u ? 255u : (uint32_t)h0) : 0u;
             key = ((uint32_t)(len2 + 1) << 16) | (l1 << 8) | hh;
-            atomicAdd(&s_hist[qb], 1);
+            /* BSW: queries with an N go to the kernel variant with the general score table (bsw_core2.cuh, QN).  Only
+             * pairs inside the uploaded byte ranges are read here (the others make the host redo the chunk). */
+            const long long iq0 = pairs[i].idq;
+            const bool qn = mode == MODE_BSW && len2 > 0 && iq0 >= qlo && iq0 + len2 <= qhi && query_has_n(qer, iq0, len2);
+            if (qn) key |= 1u << 25;
+            atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
         } else {
             atomicAdd(&s_misc[0], 1);
             atomicMax(&s_misc[2], len2);
@@ -78,7 +102,8 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, Cons
         keys[i] = key; idx[i] = (uint32_t)i;
     }
     __syncthreads();
-    if (threadIdx.x < BSW_NBINS + 2 && s_hist[threadIdx.x]) atomicAdd(&plan->hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (threadIdx.x < 2 * (BSW_NBINS + 2) && s_hist[threadIdx.x])      /* hist and hist_n are adjacent in Plan */
+        atomicAdd(&plan->hist[threadIdx.x], s_hist[threadIdx.x]);
     if (threadIdx.x == 0) {
         if (s_misc[0]) atomicAdd(&plan->n_general, s_misc[0]);
         atomicMax(&plan->max_len1, s_misc[1]);
@@ -97,7 +122,7 @@ __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pa
 }
 
 /* ------------------------------------------------------------------ 4a. BSW packed */
-template <bool COUNT, bool SYM>
+template <bool COUNT, bool SYM, bool QN>
 __global__ void __launch_bounds__(32)
 bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
@@ -115,7 +140,7 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
         PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
         PairOut oa, ob;
         if (COUNT) bsw_packed_thread<32, true, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
-        else bsw_packed_thread2<32, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        else bsw_packed_thread2<32, SYM, QN>(c, w, A, B, ref, qer, he, qs, oa, ob);
         int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
         o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
         my_cells += (unsigned long long)oa.cells;

@@ -31,6 +31,8 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
             int a, int b, int ambig, int w, int force_general, long long *cells_out)
 {
     const bool count_cells = cells_out != nullptr;
+    const bool force_qn = (force_general & 2) != 0;   // bit 1: run every thread through the general-selector variant
+    force_general &= 1;
     Const c = mk(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig);
     std::vector<int> el, ge;
     for (int i = 0; i < n; ++i)
@@ -46,8 +48,17 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         const bool sym = c.oe_del == c.oe_ins;
         if (count_cells) { if (sym) bsw_packed_thread<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
                            else bsw_packed_thread<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
-        else { if (sym) bsw_packed_thread2<1, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-               else bsw_packed_thread2<1, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+        else {
+            // the library's prep_kernel routes pairs whose query holds an N (or an invalid base) to the QN = true variant
+            bool qn = false;
+            for (int j = 0; j < A.len2; ++j) qn |= qer[A.idq + j] > 3;
+            for (int j = 0; ib >= 0 && j < B.len2; ++j) qn |= qer[B.idq + j] > 3;
+            if (force_qn) qn = true;
+            if (sym) { if (qn) bsw_packed_thread2<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+                       else bsw_packed_thread2<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+            else { if (qn) bsw_packed_thread2<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
+                   else bsw_packed_thread2<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+        }
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
     }

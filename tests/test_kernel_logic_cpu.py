@@ -13,7 +13,7 @@ def _check_bsw(ora, pairs, ref, qer, **kw):
     prm = ora.make_params(**{k: v for k, v in kw.items() if k != "w"})
     o = pairs.copy()
     _, oc = ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4, True)
-    for fg, count in ((0, True), (0, False), (1, True)):
+    for fg, count in ((0, True), (0, False), (1, True), (2, False)):      # 2: packed path, general (N-capable) selectors
         e, ec, _ = emu.bsw(pairs, ref, qer, force_general=fg, count=count, **kw)
         bad = common.diff_fields(o, e, common.BSW_FIELDS)
         if count:
