@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbswcuda.so")
+LIB_PATH = os.environ.get("BSW_CUDA_LIB") or os.path.join(_HERE, "libbswcuda.so")   # override: A/B builds (tools/ab.sh)
 
 SEQPAIR = np.dtype([(n, "<i4") for n in (
     "idr", "idq", "id", "len1", "len2", "h0", "seqid", "regid",

@@ -42,6 +42,21 @@ static inline uint32_t funnel_r(uint32_t lo, uint32_t hi, int s) { s &= 31; retu
 static inline uint32_t ldg32(const uint32_t *p) { return *p; }
 #endif
 
+/* 4-byte asynchronous global -> shared copy (LDGSTS) and the wait for all of this thread's copies */
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void stage32(uint32_t *dst, const uint32_t *src)
+#if defined(BSW2_STAGE_LDST)
+{ *dst = __ldg(src); }
+__device__ __forceinline__ void stage_wait() {}
+#else
+{ asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory"); }
+__device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+#endif
+#else
+static inline void stage32(uint32_t *dst, const uint32_t *src) { *dst = *src; }
+static inline void stage_wait() {}
+#endif
+
 /* Row context of the second-generation kernel.  QN = false (no N / invalid base in either query, decided by
  * prep_kernel): the substitution score of both lanes is ONE PRMT into a per-row byte table, LA = scores of lane
  * A's target base against query bases 0..3, LB = the same for lane B; the stored selector picks byte q (and its
@@ -129,11 +144,19 @@ BSW_HD void bsw_sweep2(const RowCtx2 &r, uint32_t *he, const uint16_t *qs, int j
     uint32_t v0 = hp[0], v1 = hp[S], v2 = hp[2 * S], v3 = hp[3 * S];
     uint32_t q0 = qp[0], q1 = qp[S], q2 = qp[2 * S], q3 = qp[3 * S];
     for (;;) {
-        while (k < kend) {      /* unchecked groups; the next group (at least the cut group) is loaded ahead */
-            const uint32_t w0 = hp[(k + 4) * S], w1 = hp[(k + 5) * S], w2 = hp[(k + 6) * S], w3 = hp[(k + 7) * S];
-            const uint32_t r0 = qp[(k + 4) * S], r1 = qp[(k + 5) * S], r2 = qp[(k + 6) * S], r3 = qp[(k + 7) * S];
-            BSW2_GROUP(v0, v1, v2, v3, q0, q1, q2, q3)
-            v0 = w0; v1 = w1; v2 = w2; v3 = w3; q0 = r0; q1 = r1; q2 = r2; q3 = r3;
+        /* unchecked groups.  Each state word / selector register is reloaded with the next group's column (at the
+         * latest the cut group's) right after the cell that consumed it: prefetch about one group ahead, in place,
+         * with no second register set and no moves (a two-groups-per-iteration unroll was measured slower: the
+         * remainder group runs once per row for the whole warp as soon as one thread has an odd group count) */
+        while (k < kend) {
+            uint32_t ha, hb, hc, hd, ea, eb, ec, ed;
+            bsw_cell2<SYM, QN>(r, v0, q0, f, ha, ea); v0 = hp[(k + 4) * S]; q0 = qp[(k + 4) * S]; hp[(k + 0) * S] = st_pack(h1, ea);
+            bsw_cell2<SYM, QN>(r, v1, q1, f, hb, eb); v1 = hp[(k + 5) * S]; q1 = qp[(k + 5) * S]; hp[(k + 1) * S] = st_pack(ha, eb);
+            bsw_cell2<SYM, QN>(r, v2, q2, f, hc, ec); v2 = hp[(k + 6) * S]; q2 = qp[(k + 6) * S]; hp[(k + 2) * S] = st_pack(hb, ec);
+            bsw_cell2<SYM, QN>(r, v3, q3, f, hd, ed); v3 = hp[(k + 7) * S]; q3 = qp[(k + 7) * S]; hp[(k + 3) * S] = st_pack(hc, ed);
+            h1 = hd;
+            const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3);
+            key = p_maxu(key, g + (uint32_t)k * 0x00010001u);
             k += 4;
         }
         {   /* cut group */
@@ -210,53 +233,58 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
         clean[p] = 1;
     }
 
-    /* ---- first row of H (A.1), E = 0, query selectors; columns qmax+1 .. qmax+3 zeroed (sweep slack) ---- */
+    RowCtx2 r;
+    r.LUTLO = launder(lut_lo(c)); r.LUTHI = launder(lut_hi(c));
+    r.LA = r.LB = 0;
+    const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
+    r.NOD = pack2(-c.oe_del, -c.oe_del); r.NOI = pack2(-c.oe_ins, -c.oe_ins);
+    r.NED = pack2(-c.e_del, -c.e_del);   r.NEI = pack2(-c.e_ins, -c.e_ins);
+    r.GATE = (uint32_t)(c.a + 1);
+    r.T = 0;
+
+    /* ---- query selectors and first row of H (A.1), E = 0; columns qmax+1 .. qmax+3 zeroed (sweep slack) ---- */
     {
         const int qmax = mx(qlen[0], qlen[1]);
-        int hp0 = 0, hp1 = 0, lastnz0 = 0, lastnz1 = 0;
-        const uint32_t *wq[2]; int shq[2]; uint32_t cw0[2], cw1[2];
+        /* (1) the raw query words of both lanes are staged in the (still unused) state rows -- lane A's words in
+         *     he[0 .. nwA), lane B's behind them -- by asynchronous copies issued back to back: one memory round
+         *     trip instead of one per four columns (the dependent word loads were 7 % of the kernel time, profile s2) */
+        const uint32_t *wq[2]; int shq[2], nwq[2];
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             const PairIn &x = *in[p];
             const uintptr_t aq = reinterpret_cast<uintptr_t>(qer + (x.valid ? x.idq : 0));
             wq[p] = reinterpret_cast<const uint32_t *>(aq & ~(uintptr_t)3);
             shq[p] = (int)(aq & 3) * 8;
-            cw0[p] = cw1[p] = 0u;
-            if (x.valid && x.len2 > 0) { cw0[p] = ldg32(wq[p]); cw1[p] = ldg32(wq[p] + 1); }
+            nwq[p] = qlen[p] > 0 ? (int)(((aq & 3) + (uintptr_t)qlen[p] + 3) >> 2) : 0;
         }
+        for (int g = 0; g < nwq[0]; ++g) stage32(he + g * S, wq[0] + g);
+        for (int g = 0; g < nwq[1]; ++g) stage32(he + (nwq[0] + g) * S, wq[1] + g);
+        stage_wait();
+        /* (2) selectors; a word index past a lane's staged words reads other staged / unused words: masked by j < qlen */
         for (int j0 = 0; j0 <= qmax + 3; j0 += 4) {
-            uint32_t nw[2], by[2];
-#pragma unroll
-            for (int p = 0; p < 2; ++p) {
-                const PairIn &x = *in[p];
-                nw[p] = (x.valid && j0 + 4 < x.len2) ? ldg32(wq[p] + (j0 >> 2) + 2) : 0u;
-                by[p] = funnel_r(cw0[p], cw1[p], shq[p]);
-            }
+            const int g = j0 >> 2;
+            const uint32_t by0 = funnel_r(he[g * S], he[(g + 1) * S], shq[0]);
+            const uint32_t by1 = funnel_r(he[(nwq[0] + g) * S], he[(nwq[0] + g + 1) * S], shq[1]);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int j = j0 + u;
-                if (j <= qmax + 3) {
-                    int hv[2];
-#pragma unroll
-                    for (int p = 0; p < 2; ++p) {
-                        int prev = p ? hp1 : hp0, v;
-                        if (j > qlen[p]) v = 0;
-                        else if (j == 0) v = h0[p];
-                        else if (j == 1) v = h0[p] > c.oe_ins ? h0[p] - c.oe_ins : 0;
-                        else v = prev > c.e_ins ? prev - c.e_ins : 0;
-                        hv[p] = v;
-                    }
-                    hp0 = hv[0]; hp1 = hv[1];
-                    if (hv[0]) lastnz0 = j;
-                    if (hv[1]) lastnz1 = j;
-                    he[j * S] = pack2(hv[0], hv[1]);
-                    uint32_t qa = (j < qlen[0]) ? ((by[0] >> (8 * u)) & 0xffu) : 0u;
-                    uint32_t qb = (j < qlen[1]) ? ((by[1] >> (8 * u)) & 0xffu) : 0u;
-                    qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
-                    qs[j * S] = bsw_selector<QN>(qa, qb);
-                }
+                uint32_t qa = (j < qlen[0]) ? ((by0 >> (8 * u)) & 0xffu) : 0u;
+                uint32_t qb = (j < qlen[1]) ? ((by1 >> (8 * u)) & 0xffu) : 0u;
+                qa = qa > 4u ? 4u : qa; qb = qb > 4u ? 4u : qb;
+                if (j <= qmax + 3) qs[j * S] = bsw_selector<QN>(qa, qb);
             }
-            cw0[0] = cw1[0]; cw1[0] = nw[0]; cw0[1] = cw1[1]; cw1[1] = nw[1];
+        }
+        /* (3) H(-1, j): h0, relu(h0 - oe_ins), then relu(previous - e_ins); zero right of the lane's query */
+        int lastnz0 = 0, lastnz1 = 0;
+        uint32_t V = pack2(h0[0], h0[1]);
+        he[0] = V;
+        V = p_addmax_relu(V, r.NOI, 0u);
+        for (int j = 1; j <= qmax + 3; ++j) {
+            V &= (j <= qlen[0] ? 0x0000ffffu : 0u) | (j <= qlen[1] ? 0xffff0000u : 0u);
+            he[j * S] = V;
+            lastnz0 = (V & 0x0000ffffu) ? j : lastnz0;
+            lastnz1 = (V & 0xffff0000u) ? j : lastnz1;
+            V = p_addmax_relu(V, r.NEI, 0u);
         }
         /* clean: every non-zero initial entry is inside row 0's range [0, min(qlen, w+1)] */
         clean[0] = lastnz0 <= mn(qlen[0], wb[0] + 1);
@@ -267,14 +295,6 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
         if (clean[1]) he[mn(qlen[1], wb[1] + 1) * S] &= 0x0000ffffu;
     }
 
-    RowCtx2 r;
-    r.LUTLO = launder(lut_lo(c)); r.LUTHI = launder(lut_hi(c));
-    r.LA = r.LB = 0;
-    const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
-    r.NOD = pack2(-c.oe_del, -c.oe_del); r.NOI = pack2(-c.oe_ins, -c.oe_ins);
-    r.NED = pack2(-c.e_del, -c.e_del);   r.NEI = pack2(-c.e_ins, -c.e_ins);
-    r.GATE = (uint32_t)(c.a + 1);
-    r.T = 0;
     const int BIG = 0x3fffffff;
 
     TWin tw[2];
