@@ -155,8 +155,9 @@ BSW_HD void bsw_sweep2(const RowCtx2 &r, uint32_t *he, const uint16_t *qs, int j
             bsw_cell2<SYM, QN>(r, v2, q2, f, hc, ec); v2 = hp[(k + 6) * S]; q2 = qp[(k + 6) * S]; hp[(k + 2) * S] = st_pack(hb, ec);
             bsw_cell2<SYM, QN>(r, v3, q3, f, hd, ed); v3 = hp[(k + 7) * S]; q3 = qp[(k + 7) * S]; hp[(k + 3) * S] = st_pack(hc, ed);
             h1 = hd;
-            const uint32_t g = p_maxu(p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2), (hd << 8) + c3);
-            key = p_maxu(key, g + (uint32_t)k * 0x00010001u);
+            /* two 3-input maxima instead of max3 + max + max: the column offset of the group is added on the FMA pipe */
+            const uint32_t kk = (uint32_t)k * 0x00010001u;
+            key = p_max3u(key, p_max3u((ha << 8) + c0, (hb << 8) + c1, (hc << 8) + c2) + kk, (hd << 8) + (c3 + kk));
             k += 4;
         }
         {   /* cut group */

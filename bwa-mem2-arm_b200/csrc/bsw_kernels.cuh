@@ -122,8 +122,11 @@ __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pa
 }
 
 /* ------------------------------------------------------------------ 4a. BSW packed */
+#ifndef BSW_MINBLOCKS
+#define BSW_MINBLOCKS 1
+#endif
 template <bool COUNT, bool SYM, bool QN>
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32, BSW_MINBLOCKS)
 bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
                   int first, int bin_end, int NE, Const c, int w, unsigned long long *cells)

@@ -32,7 +32,9 @@ ix = {h: i for i, h in enumerate(hdr)}
 stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 agg = collections.OrderedDict()
 for k, r in enumerate(data):
-    a = agg.setdefault(ins[k][2], [0, 0, 0, collections.Counter(), set(), ins[k][3], 0])
+    a = agg.setdefault(ins[k][2], [0, 0, 0, collections.Counter(), set(), ins[k][3], 0, 0])
+    opc = ins[k][0].split()[1] if ins[k][0].startswith("@") else ins[k][0].split()[0]
+    if re.match(r"(PRMT|LOP3|VIADD|VIMNMX|VIADDMNMX|ISETP|SEL|SHF|IADD3|IABS|FSETP|LEA|PLOP3|VABSDIFF|SGXT|BMSK|FLO|POPC|I2F|F2I)", opc) and not opc.startswith("IMAD"): a[7] += 1
     a[0] += 1; a[1] += int(r[ix["Instructions Executed"]]); a[2] += int(r[ix["# Samples"]]); a[4].add(ins[k][1])
     a[6] += int(r[ix["Thread Instructions Executed"]]) if "Thread Instructions Executed" in ix else 0
     for h in stalls:
@@ -40,8 +42,8 @@ for k, r in enumerate(data):
 ti = sum(v[1] for v in agg.values()); ts = sum(v[2] for v in agg.values())
 print(f"warp instructions {ti}, samples {ts}")
 thr = float(os.environ.get("MIN_PCT", "0.4"))
-for b, (n, e, s_, st, lines, addr, te) in agg.items():
+for b, (n, e, s_, st, lines, addr, te, nalu) in agg.items():
     if s_ / ts * 100 < thr: continue
     ls = sorted(x for x in lines if x)
     tops = ",".join(f"{n_}:{c}" for n_, c in st.most_common(3))
-    print(f"{addr:6x} {b:12s} n={n:4d} exec/inst={e/n:12.0f} {e/ti*100:5.1f}% inst {s_/ts*100:5.1f}% time lanes={te/max(e,1):4.1f} lines {ls[0] if ls else 0}-{ls[-1] if ls else 0} [{tops}]")
+    print(f"{addr:6x} {b:12s} n={n:4d} alu={nalu:3d} exec/inst={e/n:12.0f} {e/ti*100:5.1f}% inst {s_/ts*100:5.1f}% time lanes={te/max(e,1):4.1f} lines {ls[0] if ls else 0}-{ls[-1] if ls else 0} [{tops}]")
