@@ -216,7 +216,7 @@ BSW_HD uint32_t twin_refill(TWin &t, int r)
 template <int S, bool SYM, bool QN>
 BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                               uint32_t *he, uint16_t *qs, PairOut &oa, PairOut &ob)
+                               uint32_t *he, uint16_t *qs, const uint32_t *lut5, PairOut &oa, PairOut &ob)
 {
     const PairIn *in[2] = { &A, &B };
     int qlen[2], tlen[2], h0[2], wb[2], end[2], smax[2], max_i[2], max_j[2], max_ie[2], gscore[2], max_off[2], clean[2];
@@ -314,7 +314,14 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
         /* ---------------- row prologue ---------------- */
         if ((i & 3) == 0) { winA = twin_refill(tw[0], i >> 2); winB = twin_refill(tw[1], i >> 2); }
         if (QN) r.T = (winA & 0xffu) * 0x0011u | (winB & 0xffu) * 0x1100u;
+#if defined(BSW2_LUTSMEM)
+        else {      /* per-row score tables of the two lanes: one shared-memory load each (lut5[t]) */
+            r.LA = lut5[winA & 0xffu]; r.LB = lut5[winB & 0xffu];
+        }
+#else
         else { r.LA = bsw_lutrow(MISW, XW, AMBW, (winA & 0xffu) * 8u); r.LB = bsw_lutrow(MISW, XW, AMBW, (winB & 0xffu) * 8u); }
+        (void)lut5;
+#endif
         winA >>= 8; winB >>= 8;
         hcol = p_addmax_relu(hcol, r.NED, 0u);
 
@@ -323,8 +330,13 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             lb[p] = mx(i - wb[p], 0);
+#if defined(BSW2_T25)
+            end[p] = mn(end[p], i + wb[p] + 1);                 /* end <= qlen always holds (set that way below) */
+            st[p] = mx(t, i - wb[p]);
+#else
             end[p] = mn(mn(end[p], i + wb[p] + 1), qlen[p]);
             st[p] = mx(t, lb[p]);
+#endif
             if (((act >> p) & 1) && st[p] >= end[p]) empty |= 1 << p;
         }
         if (empty) {
@@ -402,7 +414,14 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
             int off = mj - i; off = off < 0 ? -off : off;
             const int di = i - max_i[p], dj = mj - max_j[p];
             const int pen = di > dj ? (di - dj) * c.e_del : (dj - di) * c.e_ins;
+#if defined(BSW2_ZPRE)
+            /* z-drop needs max - m > zdrop at least (the gap term only subtracts): then the lane takes the rare branch, which
+             * repeats this row's exact test */
+            const bool zpre = !upd && c.zdrop > 0 && smax[p] - m > c.zdrop;
+            const bool zd = zpre && smax[p] - m - pen > c.zdrop;
+#else
             const bool zd = !upd && c.zdrop > 0 && smax[p] - m - pen > c.zdrop;
+#endif
             const bool stop = (m == 0) | zd | (i + 1 >= tlen[p]);
             max_off[p] = (upd && off > max_off[p]) ? off : max_off[p];
             smax[p] = upd ? m : smax[p]; max_i[p] = upd ? i : max_i[p]; max_j[p] = upd ? mj : max_j[p];

@@ -24,6 +24,9 @@
 
 namespace bswk {
 
+#define MISW_OF(c) (((uint32_t)(-(c).b) & 0xffu) * 0x01010101u)
+#define XW_OF(c) (((uint32_t)(c).a ^ (uint32_t)(-(c).b)) & 0xffu)
+
 #define BSW_NBINS 16            /* bins of 16 elements: up to 256 elements per thread */
 #define BSW_WARP_ELEM_BYTES 192 /* per element per warp: 32 x (state word + uint16 selector) */
 
@@ -138,12 +141,16 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
     const int slot = first + blockIdx.x * 64 + lane * 2;
     const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
     const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
+    /* per-row score tables by target base: byte q of lut_tbl[t] = score(t, q) */
+    __shared__ uint32_t lut_tbl[8];
+    if (lane < 5) lut_tbl[lane] = bsw_lutrow(MISW_OF(c), XW_OF(c), lut_hi(c), lane * 8u);
+    __syncwarp();
     unsigned long long my_cells = 0;
     if (pa >= 0) {
         PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
         PairOut oa, ob;
         if (COUNT) bsw_packed_thread<32, true, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
-        else bsw_packed_thread2<32, SYM, QN>(c, w, A, B, ref, qer, he, qs, oa, ob);
+        else bsw_packed_thread2<32, SYM, QN>(c, w, A, B, ref, qer, he, qs, lut_tbl, oa, ob);
         int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
         o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
         my_cells += (unsigned long long)oa.cells;

@@ -50,14 +50,15 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
                            else bsw_packed_thread<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
         else {
             // the library's prep_kernel routes pairs whose query holds an N (or an invalid base) to the QN = true variant
+            uint32_t lut5[5]; for (int t = 0; t < 5; ++t) lut5[t] = bsw_lutrow(((uint32_t)(-c.b) & 0xffu) * 0x01010101u, ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu, lut_hi(c), t * 8u);
             bool qn = false;
             for (int j = 0; j < A.len2; ++j) qn |= qer[A.idq + j] > 3;
             for (int j = 0; ib >= 0 && j < B.len2; ++j) qn |= qer[B.idq + j] > 3;
             if (force_qn) qn = true;
-            if (sym) { if (qn) bsw_packed_thread2<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-                       else bsw_packed_thread2<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
-            else { if (qn) bsw_packed_thread2<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-                   else bsw_packed_thread2<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
+            if (sym) { if (qn) bsw_packed_thread2<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob);
+                       else bsw_packed_thread2<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob); }
+            else { if (qn) bsw_packed_thread2<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob);
+                   else bsw_packed_thread2<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob); }
         }
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }

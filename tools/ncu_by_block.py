@@ -5,7 +5,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rep = sys.argv[1]
 prefix = sys.argv[2] if len(sys.argv) > 2 else "_ZN4bswk17bsw_packed_kernelILb0ELb1"
 tmp = tempfile.mkdtemp()
-subprocess.run(f"cd {tmp} && cuobjdump -xelf all {ROOT}/bwa-mem2-arm_b200/libbswcuda.so > /dev/null && nvdisasm -g -c *.cubin > dis.txt", shell=True, check=True)
+subprocess.run(f"cd {tmp} && cuobjdump -xelf all {os.environ.get("BSW_CUDA_LIB") or ROOT + "/bwa-mem2-arm_b200/libbswcuda.so"} > /dev/null && nvdisasm -g -c *.cubin > dis.txt", shell=True, check=True)
 txt = open(os.path.join(tmp, "dis.txt")).read().split("\n")
 start = [i for i, l in enumerate(txt) if l.startswith(".text." + prefix)][0]
 ins, cur, blk, nblk = [], None, "entry", 0
@@ -45,5 +45,5 @@ thr = float(os.environ.get("MIN_PCT", "0.4"))
 for b, (n, e, s_, st, lines, addr, te, nalu) in agg.items():
     if s_ / ts * 100 < thr: continue
     ls = sorted(x for x in lines if x)
-    tops = ",".join(f"{n_}:{c}" for n_, c in st.most_common(3))
+    tops = ",".join(f"{n_}:{c}" for n_, c in st.most_common(7))
     print(f"{addr:6x} {b:12s} n={n:4d} alu={nalu:3d} exec/inst={e/n:12.0f} {e/ti*100:5.1f}% inst {s_/ts*100:5.1f}% time lanes={te/max(e,1):4.1f} lines {ls[0] if ls else 0}-{ls[-1] if ls else 0} [{tops}]")
