@@ -271,6 +271,32 @@ def test_device_resident_api(ora, sw, bsw):
     _assert_same(o, g)
 
 
+def test_device_resident_calls_overlap_on_streams(ora, sw, bsw):
+    """Device-resident calls issued on different caller streams overlap inside the library (slot ring of
+    bsw_dev_getScores): more calls in flight than slots, no host sync in between, then a host-pointer call
+    straight after -- every call's results equal the oracle's."""
+    import torch
+    streams = [torch.cuda.Stream(priority=-1) for _ in range(3)]
+    jobs = []
+    for i in range(7):                                   # > BSW_NSLOT calls, different sizes and seeds
+        (L, lr, lq), _ = common.bsw_c1(1500 + 700 * i, seed=100 + i)
+        o, _ = _oracle_bsw(ora, L, lr, lq)
+        dp = torch.from_numpy(L.view(np.uint8).copy()).cuda()
+        jobs.append((o, dp, torch.from_numpy(lr).cuda(), torch.from_numpy(lq).cuda(), len(L)))
+    torch.cuda.synchronize()
+    for rep in range(2):                                 # second round: the calls rewrite the same arrays in place
+        for i, (o, dp, dr, dq, n) in enumerate(jobs):
+            sw.dev_getScores(dp, dr, dq, n, 100, streams[i % len(streams)].cuda_stream)
+    (L, lr, lq), _ = common.bsw_c1(3000, seed=7)         # host-pointer call while the device calls are in flight
+    oh, _ = _oracle_bsw(ora, L, lr, lq)
+    gh = L.copy()
+    sw.getScores16(gh, lr, lq, len(gh), 1, 100)
+    _assert_same(oh, gh)
+    torch.cuda.synchronize()
+    for o, dp, _, _, _ in jobs:
+        _assert_same(o, dp.cpu().numpy().view(bsw.SEQPAIR))
+
+
 def test_properties_at_scale(ora, sw, bsw):
     """Size-independent properties on 1M C2-shaped pairs: idempotence, order independence
     (results do not depend on where a pair sits in the batch), all-match closed form."""
