@@ -246,7 +246,7 @@ def main():
     # the reference's worker threads.  They are issued round-robin on `args.streams` caller streams: calls on different
     # streams overlap inside the library (slot ring of bsw_dev_getScores), so the next call's prep / sort / DP blocks
     # fill the SMs while the previous call's last warps drain.  --streams 1 = strictly serial calls.
-    side = [torch.cuda.Stream(priority=-1) for _ in range(max(1, args.streams))]
+    side = [torch.cuda.Stream(priority=int(os.environ.get("BENCH_STREAM_PRIO", "-1"))) for _ in range(max(1, args.streams))]
 
     def one_step_resident(serial=False):
         for i, (c, dp) in enumerate(zip(calls, dev_pairs)):
