@@ -51,6 +51,7 @@ struct DevBuf {
 };
 
 #define BSW_NSLOT 4
+#define BSW_NLEVELS 6
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -67,6 +68,12 @@ struct DevCtx {
     /* one stream per query-length bin: the bins' kernels run concurrently, so one bin's tail wave
      * overlaps the next bin's blocks (fork/join on events around them) */
     cudaStream_t bin_stream[BSW_NBINS + 1] = {};
+    /* BSW: one stream per (priority level, bin).  The levels a call's non-empty bins get are decided per call from its
+     * histogram (assign_levels): with fixed per-bin priorities a call used only three of the device's levels, and inside
+     * one level the SHORTER bins win every freed shared-memory fragment, so the longest bin of a level ran last and its
+     * long-lived warps made the call's tail (bin trace: NE=96 ending at 6.08 ms of a 6.08 ms call, NE=80 at 4.5 ms). */
+    cudaStream_t lvl_stream[BSW_NLEVELS][BSW_NBINS + 1] = {};
+    int nlevels = 1;
     cudaEvent_t fork_ev = nullptr, bin_ev[BSW_NBINS + 1] = {};
     int sm_count = 0, smem_optin = 0;
     DevBuf cells;
@@ -138,6 +145,11 @@ void core_init(Core &k, int mode)
                 CK(cudaStreamCreateWithPriority(&x.bin_stream[qb], cudaStreamNonBlocking, pr));
                 CK(cudaEventCreateWithFlags(&x.bin_ev[qb], cudaEventDisableTiming));
             }
+            x.nlevels = std::max(1, std::min(BSW_NLEVELS, lo - hi + 1));
+            if (mode == MODE_BSW)
+                for (int l = 0; l < x.nlevels; ++l)
+                    for (int qb = 1; qb <= BSW_NBINS; ++qb)
+                        CK(cudaStreamCreateWithPriority(&x.lvl_stream[l][qb], cudaStreamNonBlocking, hi + l));
         }
         CK(cudaDeviceGetAttribute(&x.sm_count, cudaDevAttrMultiProcessorCount, x.dev));
         CK(cudaDeviceGetAttribute(&x.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, x.dev));
@@ -188,6 +200,8 @@ void core_destroy(Core &k)
         cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
         if (x.fork_ev) cudaEventDestroy(x.fork_ev);
         for (int qb = 1; qb <= BSW_NBINS; ++qb) { if (x.bin_stream[qb]) cudaStreamDestroy(x.bin_stream[qb]); if (x.bin_ev[qb]) cudaEventDestroy(x.bin_ev[qb]); }
+        for (int l = 0; l < BSW_NLEVELS; ++l)
+            for (int qb = 1; qb <= BSW_NBINS; ++qb) if (x.lvl_stream[l][qb]) cudaStreamDestroy(x.lvl_stream[l][qb]);
     }
     k.ctx.clear();
 }
@@ -257,9 +271,33 @@ void launch_bsw(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint
     launch_bsw_dp(k, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
 }
 
+/* Priority level (0 = highest) of every non-empty bin of a call: longest queries first, one level per bin while the
+ * device has levels left; otherwise neighbouring bins at the two ends of the list share a level, the pair with the
+ * smaller estimated work (pairs x columns^2) first. */
+static void assign_levels(const Plan *pl, int nlev, int level_of[BSW_NBINS + 1])
+{
+    std::vector<int> last;              /* index (into `bins`) of the last bin of each group */
+    std::vector<double> gw;
+    std::vector<int> bins;
+    for (int qb = BSW_NBINS; qb >= 1; --qb) {
+        level_of[qb] = 0;
+        const double cnt = (double)std::max(0, pl->hist[qb]) + (double)std::max(0, pl->hist_n[qb]);
+        if (cnt > 0) { bins.push_back(qb); last.push_back((int)bins.size() - 1); gw.push_back(cnt * qb * qb); }
+    }
+    while ((int)gw.size() > nlev) {
+        const size_t m = gw.size();
+        if (gw[0] + gw[1] <= gw[m - 2] + gw[m - 1]) { gw[0] += gw[1]; last[0] = last[1]; gw.erase(gw.begin() + 1); last.erase(last.begin() + 1); }
+        else { gw[m - 2] += gw[m - 1]; last[m - 2] = last[m - 1]; gw.pop_back(); last.pop_back(); }
+    }
+    for (size_t g = 0, b = 0; g < gw.size(); ++g)
+        for (; (int)b <= last[g]; ++b) level_of[bins[b]] = (int)g;
+}
+
 void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
                    const uint8_t *d_qer, int n, int w, cudaStream_t s)
 {
+    int level_of[BSW_NBINS + 1];
+    assign_levels(pl, x.nlevels, level_of);
     const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
@@ -271,7 +309,7 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
             const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
             if (cnt <= 0) continue;
             const int NE = qb * 16, grid = (cnt + 63) / 64;
-            cudaStream_t bs = x.bin_stream[qb];
+            cudaStream_t bs = x.lvl_stream[level_of[qb]][qb];
             if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             used |= 1u << qb;
             /* template flags: exact cell counting (first-generation row loop); symmetric gap sums (one packed add less
@@ -286,9 +324,13 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
             k.st.kernel_launches++;
             n_packed += cnt;
         }
+    cudaEvent_t trace_ev[BSW_NBINS + 1] = {};
+    const bool trace = k.timing && env_int("BSW_CUDA_BIN_TRACE", 0);      /* debug: when does each bin's last block retire? */
     for (int qb = BSW_NBINS; qb >= 1; --qb)
         if (used & (1u << qb)) {
-            CK(cudaEventRecord(x.bin_ev[qb], x.bin_stream[qb]));
+            cudaStream_t bs = x.lvl_stream[level_of[qb]][qb];
+            if (trace) { CK(cudaEventCreate(&trace_ev[qb])); CK(cudaEventRecord(trace_ev[qb], bs)); }
+            CK(cudaEventRecord(x.bin_ev[qb], bs));
             CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
         }
     if (pl->n_general > 0) {
@@ -307,6 +349,16 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
     if (k.timing) {
         CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
         float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
+        if (trace) {
+            fprintf(stderr, "[bsw-b200] bin trace: call of %d pairs, DP window %.3f ms; last block of bin (columns: ms, pairs):", n, ms);
+            for (int qb = BSW_NBINS; qb >= 1; --qb)
+                if (trace_ev[qb]) {
+                    float t = 0; CK(cudaEventElapsedTime(&t, x.ev0, trace_ev[qb]));
+                    fprintf(stderr, " %d: %.3f, %d;", qb * 16, t, pl->hist[qb] + pl->hist_n[qb]);
+                    cudaEventDestroy(trace_ev[qb]);
+                }
+            fprintf(stderr, "\n");
+        }
     }
     k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
 }
