@@ -663,10 +663,11 @@ void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_
  * that calls issued on DIFFERENT caller streams overlap: the next call's prep / sort / DP blocks fill the SMs while the
  * previous call's last warps drain (bench step of four 2.5M-pair calls: 18.54 ms on one stream, 18.16 ms on four).
  * Calls on one stream stay ordered by that stream.  A slot is reused only after the call that last used it has finished (stream-side wait). */
-static Slot &dev_slot(DevCtx &x, cudaStream_t s)
+static Slot &dev_slot(DevCtx &x, cudaStream_t s, bool rotate)
 {
-    Slot &sl = x.slot[x.dev_rr];
-    x.dev_rr = (x.dev_rr + 1) % BSW_NSLOT;
+    /* kswv keeps to one slot: its row-maxima scratch is ~1 GB per million pairs, and a slot's buffers grow on first use */
+    Slot &sl = x.slot[rotate ? x.dev_rr : 0];
+    if (rotate) x.dev_rr = (x.dev_rr + 1) % BSW_NSLOT;
     if (sl.dev_used) CK(cudaStreamWaitEvent(s, sl.dev_done, 0));
     sl.dev_used = true;
     return sl;
@@ -678,7 +679,7 @@ void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_se
     DevCtx &x = h->k.ctx[0];
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
-    Slot &sl = dev_slot(x, (cudaStream_t)stream);
+    Slot &sl = dev_slot(x, (cudaStream_t)stream, true);
     launch_bsw(h->k, x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
 }
@@ -716,7 +717,7 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
     DevCtx &x = h->k.ctx[0];
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
-    Slot &sl = dev_slot(x, (cudaStream_t)stream);
+    Slot &sl = dev_slot(x, (cudaStream_t)stream, false);
     launch_kswv(h->k, x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase, (cudaStream_t)stream);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
 }
