@@ -52,6 +52,13 @@ public:
                                 int nthreads, int32_t w)
     { bsw_scalarBandedSWAWrapper(h_, seqPairArray, seqBufRef, seqBufQer, numPairs, nthreads, w); }
 
+    /* device-resident pairs: the whole caller protocol of the extension step (left attempts with band retry, right h0
+     * chained from the left score by regid, right attempts) in one submission; see bsw_dev_extendChained */
+    void extendChainedResident(SeqPair *d_left, const uint8_t *d_leftRef, const uint8_t *d_leftQer, int32_t numLeft,
+                               SeqPair *d_right, const uint8_t *d_rightRef, const uint8_t *d_rightQer, int32_t numRight,
+                               int32_t w, int32_t maxBandTry, void *stream)
+    { bsw_dev_extendChained(h_, d_left, d_leftRef, d_leftQer, numLeft, d_right, d_rightRef, d_rightQer, numRight, w, maxBandTry, stream); }
+
     int64_t getTicks() { return 0; }          /* the reference's rdtsc counter; device time is in bsw_get_stats */
     bsw_t *handle() { return h_; }
 

@@ -26,7 +26,7 @@ KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "kswv_dev_getScores", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -72,6 +72,8 @@ def lib():
         f.argtypes = [vp, vp, vp, vp, vp, i32, C.c_uint16, C.c_int]
     L.bsw_dev_getScores.restype = None
     L.bsw_dev_getScores.argtypes = [vp, vp, vp, vp, i32, i32, vp]
+    L.bsw_dev_extendChained.restype = None
+    L.bsw_dev_extendChained.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp]
     L.kswv_dev_getScores.restype = None
     L.kswv_dev_getScores.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, C.c_int, vp]
     L.bsw_host_alloc.restype = vp
@@ -149,6 +151,13 @@ class BandedPairWiseSW:
     def dev_getScores(self, d_pairs, d_ref, d_qer, numPairs, w=100, stream=0):
         """Device-resident variant: arguments are device pointers / CUDA tensors."""
         self._L.bsw_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), numPairs, w, C.c_void_p(stream))
+
+    def dev_extendChained(self, d_left, d_lref, d_lqer, numLeft, d_right, d_rref, d_rqer, numRight, w=100, maxBandTry=2,
+                          stream=0):
+        """Caller protocol on resident pairs in one submission: left attempts with band retry,
+        right h0 = left score by regid, right attempts."""
+        self._L.bsw_dev_extendChained(self._h, _ptr(d_left), _ptr(d_lref), _ptr(d_lqer), numLeft, _ptr(d_right), _ptr(d_rref),
+                                      _ptr(d_rqer), numRight, w, maxBandTry, C.c_void_p(stream))
 
     def stats(self):
         s = Stats()

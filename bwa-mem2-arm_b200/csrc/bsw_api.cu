@@ -56,6 +56,8 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
+    DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
+    int *h_count = nullptr;                       /* pinned mailbox of the retry count */
     Plan *h_plan = nullptr;          /* pinned mailbox */
     bool busy = false;               /* a chunk is in flight on this slot */
     cudaEvent_t dev_done = nullptr;  /* end of the last device-resident call that used this slot's scratch */
@@ -158,6 +160,7 @@ void core_init(Core &k, int mode)
             CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&sl.dev_done, cudaEventDisableTiming));
             CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
+            CK(cudaHostAlloc((void **)&sl.h_count, sizeof(int), cudaHostAllocDefault));
             sl.plan.reserve(sizeof(Plan));
         }
         x.cells.reserve(sizeof(unsigned long long));
@@ -191,6 +194,8 @@ void core_destroy(Core &k)
             sl.pairs.release(); sl.ref.release(); sl.qer.release(); sl.aln.release();
             sl.keys_a.release(); sl.keys_b.release(); sl.idx_a.release(); sl.idx_b.release();
             sl.cubtmp.release(); sl.plan.release(); sl.scratch.release(); sl.rowmax.release();
+            sl.px_prev.release(); sl.px_list.release(); sl.px_sub.release(); sl.px_count.release();
+            if (sl.h_count) cudaFreeHost(sl.h_count);
             if (sl.h_plan) cudaFreeHost(sl.h_plan);
             if (sl.done) cudaEventDestroy(sl.done);
             if (sl.dev_done) cudaEventDestroy(sl.dev_done);
@@ -682,6 +687,62 @@ void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_se
     Slot &sl = dev_slot(x, (cudaStream_t)stream, true);
     launch_bsw(h->k, x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
+}
+
+/* One side (left or right extensions) of the caller protocol on resident pairs: attempt 0 with band w on all pairs,
+ * then up to maxBandTry-1 retries with the band doubled, each on the pairs the upstream rule selects (score changed by
+ * the attempt and max_off >= 3/4 of the attempt's band), moved to a dense sub-array and back.  One 4-byte read-back per
+ * retry (the count) on top of the histogram read-back of every BSW launch. */
+static void dev_extend_side(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                            int n, int w, int max_try, cudaStream_t s)
+{
+    if (n <= 0) return;
+    const int T = 256, G = (n + T - 1) / T;
+    sl.px_prev.reserve((size_t)n * sizeof(int));
+    sl.px_list.reserve((size_t)n * sizeof(int));
+    sl.px_count.reserve(sizeof(int));
+    bswk::proto_save_score_kernel<<<G, T, 0, s>>>(d_pairs, n, (int *)sl.px_prev.p);
+    launch_bsw(k, x, sl, d_pairs, d_ref, d_qer, n, w, s, 0);
+    for (int attempt = 1; attempt < max_try; ++attempt) {
+        const int w_prev = w << (attempt - 1), w_now = w << attempt;
+        CK(cudaMemsetAsync(sl.px_count.p, 0, sizeof(int), s));
+        bswk::proto_select_retry_kernel<<<G, T, 0, s>>>(d_pairs, (const int *)sl.px_prev.p, n, (w_prev >> 1) + (w_prev >> 2),
+                                                        (int *)sl.px_list.p, (int *)sl.px_count.p);
+        CK(cudaMemcpyAsync(sl.h_count, sl.px_count.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        if (attempt + 1 < max_try) bswk::proto_save_score_kernel<<<G, T, 0, s>>>(d_pairs, n, (int *)sl.px_prev.p);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(s));
+        const int m = *sl.h_count;
+        k.st.kernel_launches += 2;
+        if (m <= 0) break;
+        sl.px_sub.reserve((size_t)m * sizeof(bsw_seqpair_t));
+        const int Gm = (m + T - 1) / T;
+        bswk::proto_gather_kernel<<<Gm, T, 0, s>>>(d_pairs, (const int *)sl.px_list.p, m, (bsw_seqpair_t *)sl.px_sub.p);
+        launch_bsw(k, x, sl, (bsw_seqpair_t *)sl.px_sub.p, d_ref, d_qer, m, w_now, s, 0);
+        bswk::proto_scatter_kernel<<<Gm, T, 0, s>>>((const bsw_seqpair_t *)sl.px_sub.p, (const int *)sl.px_list.p, m, d_pairs);
+        CK(cudaGetLastError());
+        k.st.kernel_launches += 2;
+    }
+}
+
+void bsw_dev_extendChained(bsw_t *h, bsw_seqpair_t *d_left, const uint8_t *d_leftRef, const uint8_t *d_leftQer, int32_t numLeft,
+                           bsw_seqpair_t *d_right, const uint8_t *d_rightRef, const uint8_t *d_rightQer, int32_t numRight,
+                           int32_t w, int32_t maxBandTry, void *stream)
+{
+    DevCtx &x = h->k.ctx[0];
+    CK(cudaSetDevice(x.dev));
+    cudaStream_t s = (cudaStream_t)stream;
+    h->k.st.calls++;
+    Slot &sl = dev_slot(x, s, true);
+    const int tries = maxBandTry < 1 ? 1 : maxBandTry;
+    dev_extend_side(h->k, x, sl, d_left, d_leftRef, d_leftQer, numLeft, w, tries, s);
+    if (numRight > 0) {
+        bswk::proto_chain_h0_kernel<<<(numRight + 255) / 256, 256, 0, s>>>(d_left, numLeft, d_right, numRight);
+        CK(cudaGetLastError());
+        h->k.st.kernel_launches++;
+        dev_extend_side(h->k, x, sl, d_right, d_rightRef, d_rightQer, numRight, w, tries, s);
+    }
+    CK(cudaEventRecord(sl.dev_done, s));
 }
 
 kswv_t *kswv_create(int o_del, int e_del, int o_ins, int e_ins, int8_t w_match, int8_t w_mismatch,

@@ -278,4 +278,53 @@ __global__ void dpx_peak_kernel(uint32_t *out, int iters, uint32_t seed)
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
 }
 
+/* ------------------------------------------------------------------ caller protocol on the device
+ * The bookkeeping mem_chain2aln_across_reads_V2 does on the host between its BSW calls (row a9), as kernels over the
+ * resident SeqPair array: remember the scores before an attempt, pick the pairs that need the wider band, move them to
+ * / from a dense sub-array, and hand every right extension the score of its read's left extension as h0. */
+__global__ void proto_save_score_kernel(const bsw_seqpair_t *__restrict__ pairs, int n, int *__restrict__ prev)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) prev[i] = pairs[i].score;
+}
+
+/* retry rule: score != score before the attempt && max_off >= (w >> 1) + (w >> 2), w = band of the attempt just done */
+__global__ void proto_select_retry_kernel(const bsw_seqpair_t *__restrict__ pairs, const int *__restrict__ prev, int n,
+                                          int thr, int *__restrict__ list, int *__restrict__ count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool pick = i < n && pairs[i].score != prev[i] && pairs[i].max_off >= thr;
+    const unsigned m = __ballot_sync(0xffffffffu, pick);
+    if (!m) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == __ffs(m) - 1) base = atomicAdd(count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (pick) list[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+
+__global__ void proto_gather_kernel(const bsw_seqpair_t *__restrict__ pairs, const int *__restrict__ list, int m,
+                                    bsw_seqpair_t *__restrict__ sub)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) sub[j] = pairs[list[j]];
+}
+
+__global__ void proto_scatter_kernel(const bsw_seqpair_t *__restrict__ sub, const int *__restrict__ list, int m,
+                                     bsw_seqpair_t *__restrict__ pairs)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) pairs[list[j]] = sub[j];
+}
+
+/* right h0 = score of the left extension the pair's regid names (regid < 0: the pair keeps its h0) */
+__global__ void proto_chain_h0_kernel(const bsw_seqpair_t *__restrict__ left, int n_left, bsw_seqpair_t *__restrict__ right,
+                                      int n_right)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_right) return;
+    const int r = right[i].regid;
+    if (r >= 0 && r < n_left) right[i].h0 = left[r].score;
+}
+
 } /* namespace bswk */

@@ -123,9 +123,34 @@ void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBuf
  * first device; asynchronous on `stream` (a cudaStream_t, 0 = default stream).
  * Used by bench.py for the inputs-resident number and by pipelines that keep
  * read batches on the GPU.  The sequence buffers must be readable for 16 bytes
- * past the last base any pair names (the kernels fetch bases as aligned words). */
+ * past the last base any pair names (the kernels fetch bases as aligned words).
+ * The call blocks the host only for its 200-byte histogram; the DP kernels are
+ * left in flight.  Calls issued on one stream are ordered by that stream; BSW
+ * calls issued on DIFFERENT streams (from one host thread per handle) overlap on
+ * the device -- each takes the next of the handle's four scratch slots, and a
+ * slot is reused only after the call that last used it has finished.  Results
+ * of a call are visible to work queued on its stream after the call returns. */
 void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                        const uint8_t *d_seqBufQer, int32_t numPairs, int32_t w, void *stream);
+
+/* Caller protocol of the extension step on resident pairs, one submission
+ * (replaces the host loop around bswLeft/bswRight in
+ * mem_chain2aln_across_reads_V2, bwamem.cpp ~L2200-2900, anchor BUG_REPORT.md:28):
+ *   left:  attempt 0 with band w on all numLeft pairs; then, for attempt = 1 ..
+ *          maxBandTry-1 (upstream MAX_BAND_TRY = 2), the pairs whose score changed
+ *          in the previous attempt and whose max_off >= (w' >> 1) + (w' >> 2)
+ *          (w' = that attempt's band) are re-extended from scratch with band
+ *          w << attempt;
+ *   chain: d_right[i].h0 = d_left[d_right[i].regid].score  (regid < 0: h0 kept);
+ *   right: the same attempts on the numRight pairs.
+ * Both tiers (8/16-bit) share one arithmetic here, so there is no tier routing.
+ * Results in place, as bsw_dev_getScores; the host blocks for one histogram per
+ * BSW launch and one 4-byte count per retry; returns with the last kernels queued
+ * on `stream`. */
+void bsw_dev_extendChained(bsw_t *h, bsw_seqpair_t *d_left, const uint8_t *d_leftRef, const uint8_t *d_leftQer,
+                           int32_t numLeft, bsw_seqpair_t *d_right, const uint8_t *d_rightRef,
+                           const uint8_t *d_rightQer, int32_t numRight, int32_t w, int32_t maxBandTry, void *stream);
+
 void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                         const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs,
                         int is8, int phase, void *stream);

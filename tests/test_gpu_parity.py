@@ -297,6 +297,50 @@ def test_device_resident_calls_overlap_on_streams(ora, sw, bsw):
         _assert_same(o, dp.cpu().numpy().view(bsw.SEQPAIR))
 
 
+def _oracle_protocol_side(ora, pairs, ref, qer, w, tries):
+    """Host statement of the caller protocol of one side on the oracle."""
+    prm = ora.make_params()
+    out = pairs.copy()
+    for attempt in range(tries):
+        wa = w << attempt
+        if attempt == 0:
+            todo = np.arange(len(out))
+        else:
+            wp = w << (attempt - 1)
+            todo = np.nonzero((out["score"] != prev) & (out["max_off"] >= (wp >> 1) + (wp >> 2)))[0]
+            if len(todo) == 0:
+                break
+        prev = out["score"].copy()
+        sub = out[todo].copy()
+        ora.bsw_batch(sub, ref, qer, prm, wa, 8)
+        out[todo] = sub
+    return out, (0 if attempt == 0 else len(todo))
+
+
+@pytest.mark.parametrize("w,div,tries", [(100, 0.01, 2), (4, 0.05, 2), (2, 0.08, 2), (2, 0.08, 3), (3, 0.08, 1)])
+def test_device_side_caller_protocol(ora, sw, bsw, w, div, tries):
+    """bsw_dev_extendChained: left attempts with band retry, right h0 chained from the left score by
+    regid, right attempts -- one submission on resident pairs == the host protocol on the oracle."""
+    import torch
+    d = ora.gen_bsw(6000, seed=0xF1, div=div)
+    L, lr, lq = d["left"]; R, rr, rq = d["right"]
+    Lo, nl = _oracle_protocol_side(ora, L, lr, lq, w, tries)
+    Rin = R.copy(); ora.chain_h0(Lo, Rin)
+    Ro, nr = _oracle_protocol_side(ora, Rin, rr, rq, w, tries)
+    if w <= 2 and tries > 1:
+        assert nl > 0 and nr > 0                       # the retry path is really exercised
+    dev = lambda a: torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).cuda()
+    dL, dR = dev(L), dev(R)
+    sw.dev_extendChained(dL, dev(lr), dev(lq), len(L), dR, dev(rr), dev(rq), len(R), w, tries,
+                         torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    _assert_same(Lo, dL.cpu().numpy().view(bsw.SEQPAIR))
+    Rg = dR.cpu().numpy().view(bsw.SEQPAIR)
+    assert (Rg["h0"] == Rin["h0"]).all()
+    Ro["h0"] = Rin["h0"]
+    _assert_same(Ro, Rg)
+
+
 def test_properties_at_scale(ora, sw, bsw):
     """Size-independent properties on 1M C2-shaped pairs: idempotence, order independence
     (results do not depend on where a pair sits in the batch), all-match closed form."""
