@@ -15,6 +15,10 @@
 #include <vector>
 #include <string>
 #include <algorithm>
+#include <thread>
+#include <mutex>
+#include <condition_variable>
+#include <functional>
 #include <cub/device/device_radix_sort.cuh>
 #include "bsw_kernels.cuh"
 
@@ -50,6 +54,61 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+/* grow-only pinned host buffer (staging of the gathered sequences) */
+struct PinBuf {
+    void *p = nullptr; size_t cap = 0;
+    void reserve(size_t bytes)
+    {
+        if (bytes <= cap) return;
+        if (p) CK(cudaFreeHost(p));
+        size_t want = bytes + bytes / 4 + 256;
+        CK(cudaHostAlloc(&p, want, cudaHostAllocPortable)); cap = want;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+/* helper threads of one handle for the host-side gather (the reference's getScores has a numThreads argument too) */
+struct Pool {
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv, cv_done;
+    std::function<void(int)> job;
+    int gen = 0, pending = 0;
+    bool stop = false;
+    int size() const { return (int)th.size() + 1; }
+    void start(int nthreads)
+    {
+        for (int t = 1; t < nthreads; ++t)
+            th.emplace_back([this, t] {
+                int seen = 0;
+                std::unique_lock<std::mutex> lk(m);
+                for (;;) {
+                    cv.wait(lk, [&] { return stop || gen != seen; });
+                    if (stop) return;
+                    seen = gen;
+                    lk.unlock(); job(t); lk.lock();
+                    if (--pending == 0) cv_done.notify_one();
+                }
+            });
+    }
+    void run(const std::function<void(int)> &fn)     /* fn(t) for t = 0 .. size()-1; t = 0 on the calling thread */
+    {
+        if (th.empty()) { fn(0); return; }
+        { std::lock_guard<std::mutex> lk(m); job = fn; pending = (int)th.size(); ++gen; }
+        cv.notify_all();
+        fn(0);
+        std::unique_lock<std::mutex> lk(m);
+        cv_done.wait(lk, [&] { return pending == 0; });
+    }
+    void shutdown()
+    {
+        { std::lock_guard<std::mutex> lk(m); stop = true; }
+        cv.notify_all();
+        for (auto &t : th) t.join();
+        th.clear();
+    }
+};
+
 #define BSW_NSLOT 4
 #define BSW_NLEVELS 6
 struct Slot {
@@ -58,6 +117,8 @@ struct Slot {
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
     DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
     int *h_count = nullptr;                       /* pinned mailbox of the retry count */
+    PinBuf st_ref, st_qer, st_off;                /* gathered sequences + their offsets (host-pointer BSW calls) */
+    DevBuf off;
     Plan *h_plan = nullptr;          /* pinned mailbox */
     bool busy = false;               /* a chunk is in flight on this slot */
     cudaEvent_t dev_done = nullptr;  /* end of the last device-resident call that used this slot's scratch */
@@ -94,6 +155,11 @@ struct Core {
     int chunk_pairs = 1 << 19;
     int ahead = 2;
     int mode = MODE_BSW;
+    /* host-pointer BSW calls: gather the bases the chunk's pairs name into pinned staging with `gather` host threads and
+     * upload those, instead of the [min, max) byte range of the caller's buffers (which holds the other tier's bases
+     * too: bwa-mem2 passes ONE sequence arena to getScores8 and getScores16).  0 = range upload. */
+    int gather = 0;
+    Pool *pool = nullptr;
 };
 
 int env_int(const char *name, int dflt)
@@ -169,6 +235,7 @@ void core_init(Core &k, int mode)
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
+    k.gather = env_int("BSW_CUDA_GATHER_THREADS", 0);
     /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
     const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
     for (DevCtx &x : k.ctx) {
@@ -187,6 +254,7 @@ void core_init(Core &k, int mode)
 
 void core_destroy(Core &k)
 {
+    if (k.pool) { k.pool->shutdown(); delete k.pool; k.pool = nullptr; }
     for (DevCtx &x : k.ctx) {
         cudaSetDevice(x.dev);
         for (Slot &sl : x.slot) {
@@ -194,6 +262,7 @@ void core_destroy(Core &k)
             sl.pairs.release(); sl.ref.release(); sl.qer.release(); sl.aln.release();
             sl.keys_a.release(); sl.keys_b.release(); sl.idx_a.release(); sl.idx_b.release();
             sl.cubtmp.release(); sl.plan.release(); sl.scratch.release(); sl.rowmax.release();
+            sl.st_ref.release(); sl.st_qer.release(); sl.st_off.release(); sl.off.release();
             sl.px_prev.release(); sl.px_list.release(); sl.px_sub.release(); sl.px_count.release();
             if (sl.h_count) cudaFreeHost(sl.h_count);
             if (sl.h_plan) cudaFreeHost(sl.h_plan);
@@ -486,6 +555,51 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         k.st.h2d_bytes += (rhi - j.rlo) + (qhi - j.qlo);
         plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - j.qlo, j.cnt, sl.stream, tier8_check, j.rlo, rhi, j.qlo, qhi);
     };
+    /* gathered upload: (1) every helper thread sums the lengths of its share of the chunk's pairs, (2) exclusive prefix
+     * over the shares, (3) every thread copies its pairs' bases to their place in the pinned staging buffers and notes
+     * the new offsets; then pairs, offsets and the two dense buffers go up, and swap_offsets_kernel points the device
+     * copy of the records at the dense buffers */
+    auto upload_gathered = [&](Job &j) {
+        Slot &sl = *j.sl;
+        if (!k.pool) { k.pool = new Pool(); k.pool->start(std::max(1, k.gather)); }
+        const int T = k.pool->size();
+        std::vector<long long> sr(T + 1, 0), sq(T + 1, 0);
+        auto share = [&](int t, int &b, int &e) { b = j.first + (int)((long long)j.cnt * t / T); e = j.first + (int)((long long)j.cnt * (t + 1) / T); };
+        k.pool->run([&](int t) {
+            int b, e; share(t, b, e);
+            long long r = 0, q = 0;
+            for (int i = b; i < e; ++i) { r += std::max(pairs[i].len1, 0); q += std::max(pairs[i].len2, 0); }
+            sr[t + 1] = r; sq[t + 1] = q;
+        });
+        for (int t = 0; t < T; ++t) { sr[t + 1] += sr[t]; sq[t + 1] += sq[t]; }
+        const long long tot_r = sr[T], tot_q = sq[T];
+        if (tot_r >= ((long long)1 << 31) || tot_q >= ((long long)1 << 31)) die("chunk too large for 32-bit sequence offsets");
+        sl.st_ref.reserve((size_t)tot_r + 64); sl.st_qer.reserve((size_t)tot_q + 64); sl.st_off.reserve((size_t)j.cnt * sizeof(int2));
+        uint8_t *gr = (uint8_t *)sl.st_ref.p, *gq = (uint8_t *)sl.st_qer.p;
+        int2 *go = (int2 *)sl.st_off.p;
+        k.pool->run([&](int t) {
+            int b, e; share(t, b, e);
+            long long r = sr[t], q = sq[t];
+            for (int i = b; i < e; ++i) {
+                const int l1 = std::max(pairs[i].len1, 0), l2 = std::max(pairs[i].len2, 0);
+                memcpy(gr + r, ref + pairs[i].idr, (size_t)l1);
+                memcpy(gq + q, qer + pairs[i].idq, (size_t)l2);
+                go[i - j.first] = make_int2((int)r, (int)q);
+                r += l1; q += l2;
+            }
+        });
+        sl.ref.reserve((size_t)tot_r + 64); sl.qer.reserve((size_t)tot_q + 64); sl.off.reserve((size_t)j.cnt * sizeof(int2));
+        CK(cudaMemcpyAsync(sl.off.p, go, (size_t)j.cnt * sizeof(int2), cudaMemcpyHostToDevice, sl.stream));
+        if (tot_r > 0) CK(cudaMemcpyAsync(sl.ref.p, gr, (size_t)tot_r, cudaMemcpyHostToDevice, sl.stream));
+        if (tot_q > 0) CK(cudaMemcpyAsync(sl.qer.p, gq, (size_t)tot_q, cudaMemcpyHostToDevice, sl.stream));
+        k.st.h2d_bytes += tot_r + tot_q + (long long)j.cnt * (long long)sizeof(int2);
+        bswk::swap_offsets_kernel<<<(j.cnt + 255) / 256, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, (int2 *)sl.off.p, j.cnt);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+        j.rlo = 0; j.qlo = 0;
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p, j.cnt, sl.stream, tier8_check,
+                     0, std::max(tot_r, 1LL), 0, std::max(tot_q, 1LL));
+    };
     std::vector<Job> jobs(nchunks);
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
     auto stage_a = [&](int ci) {
@@ -498,7 +612,8 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
         CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
         k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);
-        upload(j, false);
+        if (k.gather > 0) upload_gathered(j);
+        else upload(j, false);
         sl.busy = true;
     };
     /* stage B: wait for the histogram, launch the DP kernels, download the results */
@@ -508,6 +623,7 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         CK(cudaSetDevice(j.x->dev));
         const Plan *pl = plan_wait(sl, sl.stream);
         if (pl->oob_pairs) {                      /* the sampled ranges missed a pair: redo with the exact scan */
+            if (k.gather > 0) die("internal: gathered offsets out of range");
             upload(j, true);
             pl = plan_wait(sl, sl.stream);
             if (pl->oob_pairs) die("internal: exact extents still miss a pair");
@@ -515,6 +631,11 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
         launch_bsw_dp(k, *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - j.rlo,
                       (const uint8_t *)sl.qer.p - j.qlo, j.cnt, w, sl.stream);
+        if (k.gather > 0) {                       /* the caller's idr / idq go back into the records before the download */
+            bswk::swap_offsets_kernel<<<(j.cnt + 255) / 256, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, (int2 *)sl.off.p, j.cnt);
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+        }
         CK(cudaMemcpyAsync(pairs + j.first, sl.pairs.p, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, sl.stream));
         CK(cudaEventRecord(sl.done, sl.stream));
         k.st.d2h_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);

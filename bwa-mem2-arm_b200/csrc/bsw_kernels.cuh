@@ -327,4 +327,16 @@ __global__ void proto_chain_h0_kernel(const bsw_seqpair_t *__restrict__ left, in
     if (r >= 0 && r < n_left) right[i].h0 = left[r].score;
 }
 
+
+/* host-pointer path with gathered sequences: exchanges (idr, idq) of the device copy of every pair with the offsets
+ * into the gathered buffers; a second run puts the caller's offsets back before the results are downloaded */
+__global__ void swap_offsets_kernel(bsw_seqpair_t *__restrict__ pairs, int2 *__restrict__ off, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int2 o = off[i];
+    off[i] = make_int2(pairs[i].idr, pairs[i].idq);
+    pairs[i].idr = o.x; pairs[i].idq = o.y;
+}
+
 } /* namespace bswk */

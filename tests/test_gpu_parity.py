@@ -341,6 +341,32 @@ def test_device_side_caller_protocol(ora, sw, bsw, w, div, tries):
     _assert_same(Ro, Rg)
 
 
+@pytest.mark.parametrize("threads", [1, 5])
+def test_gathered_upload_of_host_calls(ora, bsw, monkeypatch, threads):
+    """Host-pointer calls with BSW_CUDA_GATHER_THREADS: the bases the pairs name are gathered into pinned staging by
+    helper threads and uploaded densely (the two tier calls share ONE sequence arena, so a byte-range upload carries the
+    other tier's bases too).  Same results, caller's idr / idq untouched, fewer H2D bytes."""
+    (L, lr, lq), _ = common.bsw_c1(30000, seed=0x6A)
+    o, _ = _oracle_bsw(ora, L, lr, lq)
+    tiers = ora.classify(L)
+    res = {}
+    for mode in (0, threads):
+        monkeypatch.setenv("BSW_CUDA_GATHER_THREADS", str(mode))
+        monkeypatch.setenv("BSW_CUDA_CHUNK_PAIRS", "4096")
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        g = L.copy()
+        for tier, fn in ((0, h.getScores8), (1, h.getScores16)):
+            sel = np.nonzero(tiers == tier)[0]
+            part = np.ascontiguousarray(g[sel])
+            fn(part, lr, lq, len(part), 1, 100)
+            g[sel] = part
+        res[mode] = (g, h.stats()["h2d_bytes"])
+        h.close()
+    _assert_same(o, res[0][0])
+    _assert_same(o, res[threads][0])
+    assert res[threads][1] < res[0][1]
+
+
 def test_properties_at_scale(ora, sw, bsw):
     """Size-independent properties on 1M C2-shaped pairs: idempotence, order independence
     (results do not depend on where a pair sits in the batch), all-match closed form."""
