@@ -30,6 +30,8 @@ EXPORTS = (
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
+    "bsw_arena_begin", "bsw_arena_end", "bsw_ref_upload", "bsw_ref_free", "bsw_getScoresRef",
+    "bsw_set_direct_min", "kswv_set_direct_min", "bsw_engine_get_stats", "bsw_engine_reset_stats",
 )
 
 
@@ -37,6 +39,14 @@ class Stats(C.Structure):
     _fields_ = [("calls", C.c_int64), ("pairs", C.c_int64), ("pairs_packed", C.c_int64),
                 ("pairs_general", C.c_int64), ("cells", C.c_int64), ("kernel_launches", C.c_int64),
                 ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("kernel_ms", C.c_double)]
+
+    def asdict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_}
+
+
+class EngineStats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("batches", "pairs", "calls", "kernel_launches", "h2d_bytes", "d2h_bytes",
+                                          "max_batch_pairs")]
 
     def asdict(self):
         return {f: getattr(self, f) for f, _ in self._fields_}
@@ -85,6 +95,18 @@ def lib():
         f.argtypes = [vp]
     for f in (L.bsw_set_timing, L.kswv_set_timing, L.bsw_set_cell_counting):
         f.argtypes = [vp, C.c_int]
+    L.bsw_arena_begin.restype = None
+    L.bsw_arena_begin.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t]
+    L.bsw_arena_end.argtypes = [vp]
+    L.bsw_ref_upload.restype = vp
+    L.bsw_ref_upload.argtypes = [vp, C.c_int64]
+    L.bsw_ref_free.argtypes = [vp]
+    L.bsw_getScoresRef.restype = None
+    L.bsw_getScoresRef.argtypes = [vp, vp, vp, vp, vp, i32, i32]
+    for f in (L.bsw_set_direct_min, L.kswv_set_direct_min):
+        f.argtypes = [vp, C.c_int]
+    L.bsw_engine_get_stats.argtypes = [C.c_int, C.POINTER(EngineStats)]
+    L.bsw_engine_reset_stats.argtypes = [C.c_int]
     L.bsw_measure_dpx_peak.restype = C.c_double
     L.bsw_measure_dpx_peak.argtypes = [C.c_int, C.c_int]
     L.bsw_device_count.restype = C.c_int
@@ -159,6 +181,22 @@ class BandedPairWiseSW:
         self._L.bsw_dev_extendChained(self._h, _ptr(d_left), _ptr(d_lref), _ptr(d_lqer), numLeft, _ptr(d_right), _ptr(d_rref),
                                       _ptr(d_rqer), numRight, w, maxBandTry, C.c_void_p(stream))
 
+    def arena_begin(self, seqBufRef, seqBufQer):
+        """Declares the two sequence arenas of a batch (uploaded once; see bsw_arena_begin)."""
+        self._L.bsw_arena_begin(self._h, _ptr(seqBufRef), seqBufRef.nbytes, _ptr(seqBufQer), seqBufQer.nbytes)
+
+    def arena_end(self):
+        self._L.bsw_arena_end(self._h)
+
+    def getScoresRef(self, pairArray, ref, rpos, seqBufQer, numPairs=None, w=100):
+        """Targets from the resident reference `ref` (a Reference object) at doubled-strand positions `rpos` (int64)."""
+        n = len(pairArray) if numPairs is None else numPairs
+        assert rpos.dtype == np.int64
+        self._L.bsw_getScoresRef(self._h, _ptr(pairArray), ref._r, _ptr(rpos), _ptr(seqBufQer), n, w)
+
+    def set_direct_min(self, pairs):
+        self._L.bsw_set_direct_min(self._h, int(pairs))
+
     def stats(self):
         s = Stats()
         self._L.bsw_get_stats(self._h, C.byref(s))
@@ -217,6 +255,47 @@ class kswv:
 
     def set_timing(self, on=True):
         self._L.kswv_set_timing(self._h, int(on))
+
+    def set_direct_min(self, pairs):
+        self._L.kswv_set_direct_min(self._h, int(pairs))
+
+
+class Reference:
+    """2-bit packed reference resident on the GPU (bsw_ref_upload): `pac` in bwa's .pac layout, `l_pac` bases."""
+
+    def __init__(self, pac, l_pac):
+        self._L = lib()
+        pac = np.ascontiguousarray(pac, dtype=np.uint8)
+        self.l_pac = int(l_pac)
+        self._r = self._L.bsw_ref_upload(_ptr(pac), self.l_pac)
+
+    def close(self):
+        if getattr(self, "_r", None):
+            self._L.bsw_ref_free(self._r)
+            self._r = None
+
+    __del__ = close
+
+
+def pack_pac(bases):
+    """bases (uint8, values 0..3) -> bwa .pac bytes: base x in byte x >> 2, bits ((~x & 3) << 1)."""
+    b = np.asarray(bases, dtype=np.uint8)
+    n = len(b)
+    pad = (-n) % 4
+    if pad:
+        b = np.concatenate([b, np.zeros(pad, np.uint8)])
+    q = b.reshape(-1, 4)
+    return ((q[:, 0] << 6) | (q[:, 1] << 4) | (q[:, 2] << 2) | q[:, 3]).astype(np.uint8)
+
+
+def engine_stats(device=0):
+    s = EngineStats()
+    lib().bsw_engine_get_stats(device, C.byref(s))
+    return s.asdict()
+
+
+def engine_reset_stats(device=0):
+    lib().bsw_engine_reset_stats(device)
 
 
 def measure_dpx_peak(device=0, which=2):

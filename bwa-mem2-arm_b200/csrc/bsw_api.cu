@@ -4,169 +4,214 @@
  * Host side of the drop-in replacement for BandedPairWiseSW::getScores8/16 and
  * kswv::getScores8/16 (bwa-mem2 src/bandedSWA.cpp, src/kswv.cpp; call sites in
  * mem_chain2aln_across_reads_V2 / mem_sam_pe_batch, SURVEY.md sections 3, 8b).
- * One handle per calling host thread (as the reference constructs one object
- * per worker); a handle owns, per device, four chunk slots (stream, grow-only
- * device scratch, pinned mailbox) and one priority stream per query-length bin.  No CPU fallback: any CUDA failure is fatal, as in the
- * reference (fprintf + exit).
+ *
+ * A handle is cheap: scoring constants plus pointers.  Everything expensive is process-wide per device and
+ * built once (DevRt): the priority streams of the per-bin launches, a pool of per-call contexts (chunk slots with
+ * their streams, events, pinned mailboxes and grow-only scratch -- handed to a handle on its first large call and
+ * returned to the pool by bsw_destroy) and the staged-call engine (engine.cuh).  The reference constructs its
+ * BandedPairWiseSW / kswv objects per task and per worker thread; a handle that built
+ * its own 116 streams and 8 pinned allocations cost 0.57 s to create (profiles/r02_pcie_probe_1gpu.json).
+ *
+ * Three ways in:
+ *   host-pointer calls below BSW_CUDA_DIRECT_MIN pairs -> staged engine (merged with the other threads' calls);
+ *   larger host-pointer calls -> "direct": chunked DMA from the caller's buffers, pipelined over chunk slots;
+ *   bsw_dev_* / kswv_dev_* -> buffers already resident in HBM.
+ * No CPU fallback: any CUDA failure is fatal, as in the reference (fprintf + exit).
  */
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
 #include <vector>
 #include <string>
 #include <algorithm>
-#include <thread>
 #include <mutex>
-#include <condition_variable>
-#include <functional>
+#include <memory>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <thrust/iterator/transform_iterator.h>
+#include <thrust/iterator/counting_iterator.h>
+#include "host_common.cuh"
 #include "bsw_kernels.cuh"
+#include "engine.cuh"
 
 using namespace bswk;
-
-#define CK(call)                                                                              \
-    do {                                                                                      \
-        cudaError_t e_ = (call);                                                              \
-        if (e_ != cudaSuccess) {                                                              \
-            fprintf(stderr, "[bsw-b200] CUDA error %s at %s:%d: %s\n", cudaGetErrorName(e_),  \
-                    __FILE__, __LINE__, cudaGetErrorString(e_));                              \
-            exit(EXIT_FAILURE);                                                               \
-        }                                                                                     \
-    } while (0)
-
-static void die(const char *msg)
-{
-    fprintf(stderr, "[bsw-b200] fatal: %s\n", msg);
-    exit(EXIT_FAILURE);
-}
+using namespace bswh;
 
 namespace {
 
-struct DevBuf {
-    void *p = nullptr; size_t cap = 0;
-    void reserve(size_t bytes)
-    {
-        if (bytes <= cap) return;
-        if (p) CK(cudaFree(p));
-        size_t want = bytes + bytes / 4 + 256;
-        CK(cudaMalloc(&p, want)); cap = want;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-};
-
-/* grow-only pinned host buffer (staging of the gathered sequences) */
-struct PinBuf {
-    void *p = nullptr; size_t cap = 0;
-    void reserve(size_t bytes)
-    {
-        if (bytes <= cap) return;
-        if (p) CK(cudaFreeHost(p));
-        size_t want = bytes + bytes / 4 + 256;
-        CK(cudaHostAlloc(&p, want, cudaHostAllocPortable)); cap = want;
-    }
-    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
-};
-
-/* helper threads of one handle for the host-side gather (the reference's getScores has a numThreads argument too) */
-struct Pool {
-    std::vector<std::thread> th;
-    std::mutex m;
-    std::condition_variable cv, cv_done;
-    std::function<void(int)> job;
-    int gen = 0, pending = 0;
-    bool stop = false;
-    int size() const { return (int)th.size() + 1; }
-    void start(int nthreads)
-    {
-        for (int t = 1; t < nthreads; ++t)
-            th.emplace_back([this, t] {
-                int seen = 0;
-                std::unique_lock<std::mutex> lk(m);
-                for (;;) {
-                    cv.wait(lk, [&] { return stop || gen != seen; });
-                    if (stop) return;
-                    seen = gen;
-                    lk.unlock(); job(t); lk.lock();
-                    if (--pending == 0) cv_done.notify_one();
-                }
-            });
-    }
-    void run(const std::function<void(int)> &fn)     /* fn(t) for t = 0 .. size()-1; t = 0 on the calling thread */
-    {
-        if (th.empty()) { fn(0); return; }
-        { std::lock_guard<std::mutex> lk(m); job = fn; pending = (int)th.size(); ++gen; }
-        cv.notify_all();
-        fn(0);
-        std::unique_lock<std::mutex> lk(m);
-        cv_done.wait(lk, [&] { return pending == 0; });
-    }
-    void shutdown()
-    {
-        { std::lock_guard<std::mutex> lk(m); stop = true; }
-        cv.notify_all();
-        for (auto &t : th) t.join();
-        th.clear();
-    }
-};
-
 #define BSW_NSLOT 4
 #define BSW_NLEVELS 6
+
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
     DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
+    DevBuf rpos, toff, reftmp;                    /* reference-resident calls: positions, target offsets, expanded targets */
+    PinBuf h_res;                                 /* kswv phase 1: pinned landing area of a chunk's pass results */
     int *h_count = nullptr;                       /* pinned mailbox of the retry count */
-    PinBuf st_ref, st_qer, st_off;                /* gathered sequences + their offsets (host-pointer BSW calls) */
-    DevBuf off;
-    Plan *h_plan = nullptr;          /* pinned mailbox */
-    bool busy = false;               /* a chunk is in flight on this slot */
-    cudaEvent_t dev_done = nullptr;  /* end of the last device-resident call that used this slot's scratch */
+    Plan *h_plan = nullptr;                       /* pinned mailbox of the histogram */
+    bool busy = false;                            /* a chunk is in flight on this slot */
+    cudaEvent_t dev_done = nullptr;               /* end of the last device-resident call that used this slot's scratch */
     bool dev_used = false;
 };
 
+/* what one handle needs on one device while it makes large or resident calls; pooled per device */
 struct DevCtx {
     int dev = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    /* one stream per query-length bin: the bins' kernels run concurrently, so one bin's tail wave
-     * overlaps the next bin's blocks (fork/join on events around them) */
-    cudaStream_t bin_stream[BSW_NBINS + 1] = {};
-    /* BSW: one stream per (priority level, bin).  The levels a call's non-empty bins get are decided per call from its
-     * histogram (assign_levels): with fixed per-bin priorities a call used only three of the device's levels, and inside
-     * one level the SHORTER bins win every freed shared-memory fragment, so the longest bin of a level ran last and its
-     * long-lived warps made the call's tail (bin trace: NE=96 ending at 6.08 ms of a 6.08 ms call, NE=80 at 4.5 ms). */
-    cudaStream_t lvl_stream[BSW_NLEVELS][BSW_NBINS + 1] = {};
-    int nlevels = 1;
     cudaEvent_t fork_ev = nullptr, bin_ev[BSW_NBINS + 1] = {};
-    int sm_count = 0, smem_optin = 0;
     DevBuf cells;
     int dev_rr = 0;                  /* next slot of the device-resident calls (see dev_slot) */
-    /* in-flight chunk slots of the host-pointer path: while chunk c computes, chunk c+1 uploads and
-     * chunk c-1 downloads (one stream, one set of scratch buffers and one pinned mailbox per slot) */
     Slot slot[BSW_NSLOT];
+    /* sequence arenas declared with bsw_arena_begin: device copies + the event that marks them uploaded */
+    DevBuf arena_ref, arena_qer;
+    cudaStream_t arena_stream = nullptr;
+    cudaEvent_t arena_ev = nullptr;
 };
+
+/* resident 2-bit reference (bsw_ref_upload), one copy per device */
+struct RefCopy { int dev; uint8_t *d_pac; };
+
+} /* namespace */
+
+struct bsw_ref {
+    int64_t l_pac = 0;
+    std::vector<RefCopy> copies;
+    const uint8_t *on(int dev) const
+    {
+        for (const RefCopy &c : copies) if (c.dev == dev) return c.d_pac;
+        return nullptr;
+    }
+};
+
+namespace {
+
+/* process-wide, per device */
+struct DevRt {
+    int dev = 0;
+    int sm_count = 0, smem_optin = 0, nlevels = 1;
+    /* one stream per query-length bin (kswv) and per (priority level, bin) (BSW): the bins' kernels run concurrently,
+     * so one bin's tail wave overlaps the next bin's blocks (fork/join on events around them).  The levels a call's
+     * non-empty bins get are decided per call from its histogram (assign_levels). */
+    cudaStream_t bin_stream[BSW_NBINS + 1] = {};
+    cudaStream_t lvl_stream[BSW_NLEVELS][BSW_NBINS + 1] = {};
+    std::mutex mu;
+    std::vector<DevCtx *> free_ctx;
+    std::unique_ptr<Engine> engine;
+    std::once_flag engine_once;
+
+    Engine &eng()
+    {
+        std::call_once(engine_once, [this] { engine.reset(new Engine(dev)); });
+        return *engine;
+    }
+};
+
+std::mutex g_rt_mu;
+std::vector<DevRt *> g_rt;            /* index = CUDA device ordinal; entries live until process exit */
+
+void stop_engines()
+{
+    std::lock_guard<std::mutex> lk(g_rt_mu);
+    for (DevRt *r : g_rt) if (r && r->engine) r->engine->shutdown();
+}
+
+DevRt &devrt(int dev)
+{
+    std::lock_guard<std::mutex> lk(g_rt_mu);
+    if ((int)g_rt.size() <= dev) g_rt.resize(dev + 1, nullptr);
+    if (g_rt[dev]) return *g_rt[dev];
+    static bool hooked = false;
+    if (!hooked) { atexit(stop_engines); hooked = true; }
+    DevRt *r = new DevRt();
+    r->dev = dev;
+    CK(cudaSetDevice(dev));
+    CK(cudaDeviceGetAttribute(&r->sm_count, cudaDevAttrMultiProcessorCount, dev));
+    CK(cudaDeviceGetAttribute(&r->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    int lo = 0, hi = 0;                       /* numerically lowest = highest priority */
+    CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    r->nlevels = std::max(1, std::min(BSW_NLEVELS, lo - hi + 1));
+    for (int qb = 1; qb <= BSW_NBINS; ++qb) {
+        const int pr = hi + (BSW_NBINS - qb) * (lo - hi) / BSW_NBINS;   /* long queries first */
+        CK(cudaStreamCreateWithPriority(&r->bin_stream[qb], cudaStreamNonBlocking, pr));
+        for (int l = 0; l < r->nlevels; ++l)
+            CK(cudaStreamCreateWithPriority(&r->lvl_stream[l][qb], cudaStreamNonBlocking, hi + l));
+    }
+    /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
+    const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
+    if (max_smem > r->smem_optin) die("device shared memory too small for the packed kernels");
+    const void *fns[] = { (const void *)bsw_packed_kernel<false, false, false>, (const void *)bsw_packed_kernel<false, true, false>,
+                          (const void *)bsw_packed_kernel<false, false, true>, (const void *)bsw_packed_kernel<false, true, true>,
+                          (const void *)bsw_packed_kernel<true, false, true>, (const void *)bsw_packed_kernel<true, true, true>,
+                          (const void *)kswv_packed_kernel<false> };
+    for (const void *fn : fns) {
+        CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CK(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    }
+    g_rt[dev] = r;
+    return *r;
+}
+
+DevCtx *ctx_acquire(DevRt &rt)
+{
+    {
+        std::lock_guard<std::mutex> lk(rt.mu);
+        if (!rt.free_ctx.empty()) { DevCtx *x = rt.free_ctx.back(); rt.free_ctx.pop_back(); return x; }
+    }
+    DevCtx *x = new DevCtx();
+    x->dev = rt.dev;
+    CK(cudaSetDevice(rt.dev));
+    CK(cudaEventCreate(&x->ev0)); CK(cudaEventCreate(&x->ev1));
+    CK(cudaEventCreateWithFlags(&x->fork_ev, cudaEventDisableTiming));
+    for (int qb = 1; qb <= BSW_NBINS; ++qb) CK(cudaEventCreateWithFlags(&x->bin_ev[qb], cudaEventDisableTiming));
+    for (Slot &sl : x->slot) {
+        CK(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.dev_done, cudaEventDisableTiming));
+        CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
+        CK(cudaHostAlloc((void **)&sl.h_count, sizeof(int), cudaHostAllocDefault));
+        sl.plan.reserve(sizeof(Plan));
+    }
+    CK(cudaStreamCreateWithFlags(&x->arena_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&x->arena_ev, cudaEventDisableTiming));
+    x->cells.reserve(sizeof(unsigned long long));
+    CK(cudaMemset(x->cells.p, 0, sizeof(unsigned long long)));
+    return x;
+}
+
+/* back to the pool (buffers, streams and mailboxes are kept for the next handle); all of its work must be done */
+void ctx_release(DevRt &rt, DevCtx *x)
+{
+    CK(cudaSetDevice(rt.dev));
+    for (Slot &sl : x->slot) { CK(cudaStreamSynchronize(sl.stream)); sl.busy = false; sl.dev_used = false; }
+    CK(cudaStreamSynchronize(x->arena_stream));
+    CK(cudaMemset(x->cells.p, 0, sizeof(unsigned long long)));
+    x->dev_rr = 0;
+    std::lock_guard<std::mutex> lk(rt.mu);
+    rt.free_ctx.push_back(x);
+}
 
 struct Core {
     Const c;
-    std::vector<DevCtx> ctx;
+    std::vector<int> devs;
+    std::vector<DevCtx *> ctx;       /* per device of the handle; created on first large / resident call */
     bsw_stats_t st;
     int timing = 0;
     int count_cells = 0;
     int chunk_pairs = 1 << 19;
     int ahead = 2;
+    int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
     int mode = MODE_BSW;
-    /* host-pointer BSW calls: gather the bases the chunk's pairs name into pinned staging with `gather` host threads and
-     * upload those, instead of the [min, max) byte range of the caller's buffers (which holds the other tier's bases
-     * too: bwa-mem2 passes ONE sequence arena to getScores8 and getScores16).  0 = range upload. */
-    int gather = 0;
-    Pool *pool = nullptr;
-};
+    /* arenas declared with bsw_arena_begin */
+    const uint8_t *arena_ref_h = nullptr, *arena_qer_h = nullptr;
+    size_t arena_ref_n = 0, arena_qer_n = 0;
+    bool arena_on = false;
 
-int env_int(const char *name, int dflt)
-{
-    const char *s = getenv(name);
-    return (s && *s) ? atoi(s) : dflt;
-}
+    DevRt &rt(int i) { return devrt(devs[i]); }
+    DevCtx &cx(int i)
+    {
+        if (!ctx[i]) ctx[i] = ctx_acquire(rt(i));
+        return *ctx[i];
+    }
+};
 
 std::vector<int> pick_devices()
 {
@@ -197,92 +242,25 @@ void core_init(Core &k, int mode)
     k.mode = mode;
     memset(&k.st, 0, sizeof k.st);
     k.timing = env_int("BSW_CUDA_TIMING", 0);
-    std::vector<int> devs = pick_devices();
-    k.ctx.resize(devs.size());
-    for (size_t i = 0; i < devs.size(); ++i) {
-        DevCtx &x = k.ctx[i];
-        x.dev = devs[i];
-        CK(cudaSetDevice(x.dev));
-        CK(cudaEventCreate(&x.ev0)); CK(cudaEventCreate(&x.ev1));
-        {
-            int lo = 0, hi = 0;                       /* numerically lowest = highest priority */
-            CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-            CK(cudaEventCreateWithFlags(&x.fork_ev, cudaEventDisableTiming));
-            for (int qb = 1; qb <= BSW_NBINS; ++qb) {
-                int pr = hi + (BSW_NBINS - qb) * (lo - hi) / BSW_NBINS;   /* long queries first */
-                CK(cudaStreamCreateWithPriority(&x.bin_stream[qb], cudaStreamNonBlocking, pr));
-                CK(cudaEventCreateWithFlags(&x.bin_ev[qb], cudaEventDisableTiming));
-            }
-            x.nlevels = std::max(1, std::min(BSW_NLEVELS, lo - hi + 1));
-            if (mode == MODE_BSW)
-                for (int l = 0; l < x.nlevels; ++l)
-                    for (int qb = 1; qb <= BSW_NBINS; ++qb)
-                        CK(cudaStreamCreateWithPriority(&x.lvl_stream[l][qb], cudaStreamNonBlocking, hi + l));
-        }
-        CK(cudaDeviceGetAttribute(&x.sm_count, cudaDevAttrMultiProcessorCount, x.dev));
-        CK(cudaDeviceGetAttribute(&x.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, x.dev));
-        for (Slot &sl : x.slot) {
-            CK(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking));
-            CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
-            CK(cudaEventCreateWithFlags(&sl.dev_done, cudaEventDisableTiming));
-            CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
-            CK(cudaHostAlloc((void **)&sl.h_count, sizeof(int), cudaHostAllocDefault));
-            sl.plan.reserve(sizeof(Plan));
-        }
-        x.cells.reserve(sizeof(unsigned long long));
-        CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
-    }
+    k.devs = pick_devices();
+    k.ctx.assign(k.devs.size(), nullptr);
+    for (size_t i = 0; i < k.devs.size(); ++i) (void)devrt(k.devs[i]);       /* first handle on a device builds its runtime */
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
-    k.gather = env_int("BSW_CUDA_GATHER_THREADS", 0);
-    /* packed kernels: one warp per block, dynamic shared memory = NE x 192 B (NE <= 256) */
-    const int max_smem = BSW_NBINS * 16 * BSW_WARP_ELEM_BYTES;
-    for (DevCtx &x : k.ctx) {
-        CK(cudaSetDevice(x.dev));
-        if (max_smem > x.smem_optin) die("device shared memory too small for the packed kernels");
-        const void *fns[] = { (const void *)bsw_packed_kernel<false, false, false>, (const void *)bsw_packed_kernel<false, true, false>,
-                              (const void *)bsw_packed_kernel<false, false, true>, (const void *)bsw_packed_kernel<false, true, true>,
-                              (const void *)bsw_packed_kernel<true, false, false>, (const void *)bsw_packed_kernel<true, true, false>,
-                              (const void *)kswv_packed_kernel<false>, (const void *)kswv_packed_kernel<true> };
-        for (const void *fn : fns) {
-            CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-            CK(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        }
-    }
+    k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
 }
 
 void core_destroy(Core &k)
 {
-    if (k.pool) { k.pool->shutdown(); delete k.pool; k.pool = nullptr; }
-    for (DevCtx &x : k.ctx) {
-        cudaSetDevice(x.dev);
-        for (Slot &sl : x.slot) {
-            if (sl.stream) cudaStreamSynchronize(sl.stream);
-            sl.pairs.release(); sl.ref.release(); sl.qer.release(); sl.aln.release();
-            sl.keys_a.release(); sl.keys_b.release(); sl.idx_a.release(); sl.idx_b.release();
-            sl.cubtmp.release(); sl.plan.release(); sl.scratch.release(); sl.rowmax.release();
-            sl.st_ref.release(); sl.st_qer.release(); sl.st_off.release(); sl.off.release();
-            sl.px_prev.release(); sl.px_list.release(); sl.px_sub.release(); sl.px_count.release();
-            if (sl.h_count) cudaFreeHost(sl.h_count);
-            if (sl.h_plan) cudaFreeHost(sl.h_plan);
-            if (sl.done) cudaEventDestroy(sl.done);
-            if (sl.dev_done) cudaEventDestroy(sl.dev_done);
-            if (sl.stream) cudaStreamDestroy(sl.stream);
-        }
-        x.cells.release();
-        cudaEventDestroy(x.ev0); cudaEventDestroy(x.ev1);
-        if (x.fork_ev) cudaEventDestroy(x.fork_ev);
-        for (int qb = 1; qb <= BSW_NBINS; ++qb) { if (x.bin_stream[qb]) cudaStreamDestroy(x.bin_stream[qb]); if (x.bin_ev[qb]) cudaEventDestroy(x.bin_ev[qb]); }
-        for (int l = 0; l < BSW_NLEVELS; ++l)
-            for (int qb = 1; qb <= BSW_NBINS; ++qb) if (x.lvl_stream[l][qb]) cudaStreamDestroy(x.lvl_stream[l][qb]);
-    }
-    k.ctx.clear();
+    for (size_t i = 0; i < k.ctx.size(); ++i)
+        if (k.ctx[i]) { ctx_release(k.rt((int)i), k.ctx[i]); k.ctx[i] = nullptr; }
 }
 
 Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus, int w_match, int w_mismatch)
 {
     Const c;
+    memset(&c, 0, sizeof c);
     if (e_del <= 0 || e_ins <= 0) die("gap extension penalties must be positive");
     if (w_match <= 0) die("w_match must be positive");
     c.o_del = o_del; c.e_del = e_del; c.o_ins = o_ins; c.e_ins = e_ins;
@@ -294,9 +272,19 @@ Const make_const(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_
     return c;
 }
 
-/* stages 1-3 + plan read-back; returns the host copy of the plan (valid until the next call) */
+[[noreturn]] void die_contract(int bad)
+{
+    fprintf(stderr, "[bsw-b200] fatal: %d pair(s) violate the call contract (negative length, h0 <= 0, or "
+                    ">= %d bases in getScores8)\n", bad, BSW_MAX_SEQ_LEN8);
+    exit(EXIT_FAILURE);
+}
+
+/* ================================================================ large / resident calls: prep, sort, per-bin launches */
+
+/* stages 1-3 + plan read-back (asynchronous) */
 void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t *d_qer, int n, cudaStream_t s, int tier8_check,
-                  long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62)
+                  long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62,
+                  bool clear_plan = true)
 {
     x.keys_a.reserve((size_t)n * 4); x.keys_b.reserve((size_t)n * 4);
     x.idx_a.reserve((size_t)n * 4);  x.idx_b.reserve((size_t)n * 4);
@@ -305,7 +293,7 @@ void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t 
                                                  (uint32_t *)nullptr, (uint32_t *)nullptr, n, 0, BSW_KEY_BITS, s));
     x.cubtmp.reserve(tmp_bytes);
     Plan *d_plan = (Plan *)x.plan.p;
-    CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));
+    if (clear_plan) CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));     /* else: cleared before ref_expand_kernel reported into it */
     const int max_elems = BSW_NBINS * 16;
     prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, d_qer, n, k.c, k.mode, max_elems, tier8_check, rlo, rhi, qlo, qhi,
                                                  (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
@@ -320,11 +308,7 @@ void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t 
 const Plan *plan_wait(Slot &x, cudaStream_t s)
 {
     CK(cudaStreamSynchronize(s));
-    if (x.h_plan->bad_pairs) {
-        fprintf(stderr, "[bsw-b200] fatal: %d pair(s) violate the call contract (negative length, h0 <= 0, or "
-                        ">= %d bases in getScores8)\n", x.h_plan->bad_pairs, BSW_MAX_SEQ_LEN8);
-        exit(EXIT_FAILURE);
-    }
+    if (x.h_plan->bad_pairs) die_contract(x.h_plan->bad_pairs);
     return x.h_plan;
 }
 
@@ -334,21 +318,10 @@ const Plan *run_plan(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8
     return plan_wait(x, s);
 }
 
-void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
-                   const uint8_t *d_qer, int n, int w, cudaStream_t s);
-
-void launch_bsw(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
-                int n, int w, cudaStream_t s, int tier8_check)
-{
-    if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, tier8_check);
-    launch_bsw_dp(k, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
-}
-
 /* Priority level (0 = highest) of every non-empty bin of a call: longest queries first, one level per bin while the
  * device has levels left; otherwise neighbouring bins at the two ends of the list share a level, the pair with the
  * smaller estimated work (pairs x columns^2) first. */
-static void assign_levels(const Plan *pl, int nlev, int level_of[BSW_NBINS + 1])
+void assign_levels(const Plan *pl, int nlev, int level_of[BSW_NBINS + 1])
 {
     std::vector<int> last;              /* index (into `bins`) of the last bin of each group */
     std::vector<double> gw;
@@ -367,12 +340,13 @@ static void assign_levels(const Plan *pl, int nlev, int level_of[BSW_NBINS + 1])
         for (; (int)b <= last[g]; ++b) level_of[bins[b]] = (int)g;
 }
 
-void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
+void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
                    const uint8_t *d_qer, int n, int w, cudaStream_t s)
 {
     int level_of[BSW_NBINS + 1];
-    assign_levels(pl, x.nlevels, level_of);
+    assign_levels(pl, rt.nlevels, level_of);
     const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
+    const PairIO io = pairio_records(d_pairs);
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     CK(cudaEventRecord(x.fork_ev, s));
@@ -383,17 +357,17 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
             const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
             if (cnt <= 0) continue;
             const int NE = qb * 16, grid = (cnt + 63) / 64;
-            cudaStream_t bs = x.lvl_stream[level_of[qb]][qb];
+            cudaStream_t bs = rt.lvl_stream[level_of[qb]][qb];
             if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             used |= 1u << qb;
-            /* template flags: exact cell counting (first-generation row loop); symmetric gap sums (one packed add less
-             * per cell); general score table for queries with an N */
+            /* template flags: exact cell counting; symmetric gap sums (one packed add less per cell); general score
+             * table for queries with an N (the counting variant always uses it) */
             const bool sym = k.c.oe_del == k.c.oe_ins;
-            auto kern = k.count_cells ? (sym ? bsw_packed_kernel<true, true, false> : bsw_packed_kernel<true, false, false>)
+            auto kern = k.count_cells ? (sym ? bsw_packed_kernel<true, true, true> : bsw_packed_kernel<true, false, true>)
                       : pass == 0     ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
                                       : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
-            kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, sorted, n_packed, n_packed + cnt,
-                                                            NE, k.c, w, (unsigned long long *)x.cells.p);
+            kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(io, d_ref, d_qer, sorted, bintable_single(n_packed, cnt, NE),
+                                                            k.c, w, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
             n_packed += cnt;
@@ -402,7 +376,7 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
     const bool trace = k.timing && env_int("BSW_CUDA_BIN_TRACE", 0);      /* debug: when does each bin's last block retire? */
     for (int qb = BSW_NBINS; qb >= 1; --qb)
         if (used & (1u << qb)) {
-            cudaStream_t bs = x.lvl_stream[level_of[qb]][qb];
+            cudaStream_t bs = rt.lvl_stream[level_of[qb]][qb];
             if (trace) { CK(cudaEventCreate(&trace_ev[qb])); CK(cudaEventRecord(trace_ev[qb], bs)); }
             CK(cudaEventRecord(x.bin_ev[qb], bs));
             CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
@@ -414,7 +388,7 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
         sl.scratch.reserve((size_t)chunk * per_pair);
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, sorted, n_packed + first, cnt,
+            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, sorted, n_packed + first, cnt,
                                                               k.c, w, (int2 *)sl.scratch.p, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -437,35 +411,62 @@ void launch_bsw_dp(Core &k, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *
     k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
 }
 
-void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
-                 bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
+void launch_bsw(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                int n, int w, cudaStream_t s, int tier8_check)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, 0);
+    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, tier8_check);
+    launch_bsw_dp(k, rt, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
+}
+
+/* kswv row-maximum scratch (kswv_core.cuh): rows x packed pairs x 2 B, rows = longest target among the PACKED pairs.
+ * Launches are cut so that one launch's scratch stays below BSW_CUDA_ROWMAX_MB (default 2048 MB): sorted order is
+ * longest query first, so a part is a contiguous range of sorted slots inside one bin. */
+void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
+                    const uint8_t *d_qer, bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
+{
     const uint32_t *sorted = (const uint32_t *)sl.idx_b.p;
+    const PairIO io = pairio_records(d_pairs);
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     for (int qb = 1; qb <= BSW_NBINS; ++qb) n_packed += pl->hist[qb];
     if (n_packed > 0) {
-        const long long stride = n_packed;
-        sl.rowmax.reserve((size_t)std::max(1, pl->max_len1) * (size_t)stride * sizeof(uint16_t));
+        const size_t rows = (size_t)std::max(1, pl->max_len1_packed);
+        const size_t budget = (size_t)std::max(16, env_int("BSW_CUDA_ROWMAX_MB", 2048)) << 20;
+        /* slots per part, a multiple of 64 (one block = 64 slots) */
+        const size_t part = std::max<size_t>(64, (budget / (rows * sizeof(uint16_t))) & ~(size_t)63);
+        const long long stride = (long long)std::min<size_t>((size_t)n_packed, part);
+        sl.rowmax.reserve(rows * (size_t)stride * sizeof(uint16_t));
+        const bool one_part = (size_t)n_packed <= part;
         int first = 0;
-        CK(cudaEventRecord(x.fork_ev, s));
+        if (one_part) CK(cudaEventRecord(x.fork_ev, s));
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
             const int cnt = pl->hist[qb];
             if (cnt <= 0) continue;
-            const int NE = qb * 16, grid = (cnt + 63) / 64;
-            cudaStream_t bs = x.bin_stream[qb];
-            CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+            const int NE = qb * 16;
             /* SYM=false on purpose: sharing h - oe puts a third op on kswv's f -> h -> f chain (measured 3 % slower) */
             auto kern = kswv_packed_kernel<false>;
-            kern<<<grid, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(d_pairs, d_ref, d_qer, d_aln, sorted, first, first + cnt, NE,
+            if (one_part) {
+                cudaStream_t bs = rt.bin_stream[qb];
+                CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+                kern<<<(cnt + 63) / 64, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(io, d_ref, d_qer, d_aln, sorted, bintable_single(first, cnt, NE),
                                                                           k.c, is8, phase, (uint16_t *)sl.rowmax.p, stride,
                                                                           (unsigned long long *)x.cells.p);
-            CK(cudaGetLastError());
-            CK(cudaEventRecord(x.bin_ev[qb], bs));
-            CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
-            k.st.kernel_launches++;
+                CK(cudaGetLastError());
+                CK(cudaEventRecord(x.bin_ev[qb], bs));
+                CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
+                k.st.kernel_launches++;
+            } else {
+                /* budgeted: parts one after another on the call's stream, each indexing the scratch from its own first slot */
+                for (int off = 0; off < cnt; off += (int)part) {
+                    const int c2 = std::min<int>((int)part, cnt - off);
+                    kern<<<(c2 + 63) / 64, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(io, d_ref, d_qer, d_aln, sorted, bintable_single(first + off, c2, NE),
+                                                                            k.c, is8, phase, (uint16_t *)sl.rowmax.p - (first + off), stride,
+                                                                            (unsigned long long *)x.cells.p);
+                    CK(cudaGetLastError());
+                    k.st.kernel_launches++;
+                }
+            }
             first += cnt;
         }
     }
@@ -477,7 +478,7 @@ void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, con
         int *rm = (int *)((char *)sl.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(d_pairs, d_ref, d_qer, d_aln, sorted, n_packed + first, cnt,
+            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, d_aln, sorted, n_packed + first, cnt,
                                                                k.c, is8, phase, he, rm, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -488,6 +489,14 @@ void launch_kswv(Core &k, DevCtx &x, Slot &sl, const bsw_seqpair_t *d_pairs, con
         float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
     }
     k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
+}
+
+void launch_kswv(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                 bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
+{
+    if (n <= 0) return;
+    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, 0);
+    launch_kswv_dp(k, rt, x, sl, pl, d_pairs, d_ref, d_qer, d_aln, n, is8, phase, s);
 }
 
 /* byte extents [lo, hi) of the sequence buffers touched by pairs[first, first+cnt) */
@@ -506,114 +515,117 @@ void extents(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long lo
  * arenas in pair order, so the estimate is normally exact; prep_kernel checks every pair against it on the
  * device (Plan::oob_pairs) and the chunk is redone with the exact scan if any pair falls outside.  This keeps
  * the calling host thread from reading all 56-byte records (0.56 GB per 10M pairs) before it can start a copy. */
-void extents_sampled(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long long &rhi, long long &qlo, long long &qhi)
+void extents_sampled(const bsw_seqpair_t *p, int first, int cnt, long long &rlo, long long &rhi, long long &qlo, long long &qhi,
+                     long long *len1_sum32 = nullptr)
 {
     rlo = qlo = (long long)1 << 62; rhi = qhi = 0;
+    long long l1 = 0;
     auto take = [&](int i) {
         long long a = p[i].idr, b = a + std::max(p[i].len1, 0), c = p[i].idq, d = c + std::max(p[i].len2, 0);
         rlo = std::min(rlo, a); rhi = std::max(rhi, b); qlo = std::min(qlo, c); qhi = std::max(qhi, d);
     };
-    for (int i = first; i < first + cnt; i += 32) take(i);
+    for (int i = first; i < first + cnt; i += 32) { take(i); l1 += std::max(p[i].len1, 0) + 4; }
     for (int i = std::max(first, first + cnt - 32); i < first + cnt; ++i) take(i);
     if (rhi <= rlo) { rlo = 0; rhi = 0; }
     if (qhi <= qlo) { qlo = 0; qhi = 0; }
+    if (len1_sum32) *len1_sum32 = l1;
 }
 
-/* ---- BSW host-pointer call: chunked, pipelined, sharded ---------------------------------------
- * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
- * devices.  Each chunk uploads only the byte ranges of the sequence buffers its pairs touch, so the
- * H2D copy of chunk c+1 and the D2H copy of chunk c-1 overlap the kernels of chunk c (three slots per
- * device).  Results land directly in the caller's SeqPair array.  Synchronous on return. */
-void slot_retire(Core &k, DevCtx &x, Slot &sl)
+void slot_retire(DevCtx &x, Slot &sl)
 {
     if (sl.dev_used) { CK(cudaSetDevice(x.dev)); CK(cudaEventSynchronize(sl.dev_done)); sl.dev_used = false; }
     if (!sl.busy) return;
     CK(cudaSetDevice(x.dev));
     CK(cudaEventSynchronize(sl.done));
     sl.busy = false;
-    (void)k;
 }
 
-void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check)
+/* ---- direct BSW call: chunked, pipelined, sharded ---------------------------------------------
+ * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
+ * devices.  Each chunk uploads its 56-byte records and only the byte ranges of the sequence buffers its pairs
+ * touch (nothing when the buffers lie in a declared arena, bsw_arena_begin; no target bases at all when the
+ * targets come from the resident reference, `rpos` != nullptr), so the H2D copy of chunk c+1 and the D2H copy of
+ * chunk c-1 overlap the kernels of chunk c.  Results land directly in the caller's SeqPair array (whole-record
+ * DMA: a 24-of-56-byte strided copy reaches 1.5 GB/s up and 15 GB/s down against 55 GB/s for the contiguous
+ * records, profiles/r02_pcie_probe_1gpu.json).  Synchronous on return. */
+void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check,
+                     const bsw_ref *rref = nullptr, const int64_t *rpos = nullptr)
 {
-    k.st.calls++;
-    if (n <= 0) return;
-    if (!pairs || !ref || !qer) die("null buffer passed to getScores");
-    const int nd = (int)k.ctx.size();
+    const int nd = (int)k.devs.size();
     const int chunk = std::max(1024, k.chunk_pairs);
     const int nchunks = (n + chunk - 1) / chunk;
-    struct Job { int first, cnt; long long rlo, qlo; DevCtx *x; Slot *sl; };
+    struct Job { int first, cnt, di; long long rlo, qlo; const uint8_t *d_ref, *d_qer; DevCtx *x; Slot *sl; };
+    const bool in_arena_r = k.arena_on && !rref && ref >= k.arena_ref_h && ref < k.arena_ref_h + k.arena_ref_n;
+    const bool in_arena_q = k.arena_on && qer >= k.arena_qer_h && qer < k.arena_qer_h + k.arena_qer_n;
     auto upload = [&](Job &j, bool exact) {
-        long long rhi, qhi;
-        if (exact) extents(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
-        else extents_sampled(pairs, j.first, j.cnt, j.rlo, rhi, j.qlo, qhi);
+        long long rlo, rhi, qlo, qhi, l1s = 0;
+        if (exact) { extents(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi); for (int i = j.first; i < j.first + j.cnt; ++i) l1s += std::max(pairs[i].len1, 0) + 4; }
+        else extents_sampled(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi, &l1s);
         Slot &sl = *j.sl;
-        sl.ref.reserve((size_t)(rhi - j.rlo) + 64);
-        sl.qer.reserve((size_t)(qhi - j.qlo) + 64);
-        if (rhi > j.rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + j.rlo, (size_t)(rhi - j.rlo), cudaMemcpyHostToDevice, sl.stream));
-        if (qhi > j.qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + j.qlo, (size_t)(qhi - j.qlo), cudaMemcpyHostToDevice, sl.stream));
-        k.st.h2d_bytes += (rhi - j.rlo) + (qhi - j.qlo);
-        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - j.qlo, j.cnt, sl.stream, tier8_check, j.rlo, rhi, j.qlo, qhi);
-    };
-    /* gathered upload: (1) every helper thread sums the lengths of its share of the chunk's pairs, (2) exclusive prefix
-     * over the shares, (3) every thread copies its pairs' bases to their place in the pinned staging buffers and notes
-     * the new offsets; then pairs, offsets and the two dense buffers go up, and swap_offsets_kernel points the device
-     * copy of the records at the dense buffers */
-    auto upload_gathered = [&](Job &j) {
-        Slot &sl = *j.sl;
-        if (!k.pool) { k.pool = new Pool(); k.pool->start(std::max(1, k.gather)); }
-        const int T = k.pool->size();
-        std::vector<long long> sr(T + 1, 0), sq(T + 1, 0);
-        auto share = [&](int t, int &b, int &e) { b = j.first + (int)((long long)j.cnt * t / T); e = j.first + (int)((long long)j.cnt * (t + 1) / T); };
-        k.pool->run([&](int t) {
-            int b, e; share(t, b, e);
-            long long r = 0, q = 0;
-            for (int i = b; i < e; ++i) { r += std::max(pairs[i].len1, 0); q += std::max(pairs[i].len2, 0); }
-            sr[t + 1] = r; sq[t + 1] = q;
-        });
-        for (int t = 0; t < T; ++t) { sr[t + 1] += sr[t]; sq[t + 1] += sq[t]; }
-        const long long tot_r = sr[T], tot_q = sq[T];
-        if (tot_r >= ((long long)1 << 31) || tot_q >= ((long long)1 << 31)) die("chunk too large for 32-bit sequence offsets");
-        sl.st_ref.reserve((size_t)tot_r + 64); sl.st_qer.reserve((size_t)tot_q + 64); sl.st_off.reserve((size_t)j.cnt * sizeof(int2));
-        uint8_t *gr = (uint8_t *)sl.st_ref.p, *gq = (uint8_t *)sl.st_qer.p;
-        int2 *go = (int2 *)sl.st_off.p;
-        k.pool->run([&](int t) {
-            int b, e; share(t, b, e);
-            long long r = sr[t], q = sq[t];
-            for (int i = b; i < e; ++i) {
-                const int l1 = std::max(pairs[i].len1, 0), l2 = std::max(pairs[i].len2, 0);
-                memcpy(gr + r, ref + pairs[i].idr, (size_t)l1);
-                memcpy(gq + q, qer + pairs[i].idq, (size_t)l2);
-                go[i - j.first] = make_int2((int)r, (int)q);
-                r += l1; q += l2;
-            }
-        });
-        sl.ref.reserve((size_t)tot_r + 64); sl.qer.reserve((size_t)tot_q + 64); sl.off.reserve((size_t)j.cnt * sizeof(int2));
-        CK(cudaMemcpyAsync(sl.off.p, go, (size_t)j.cnt * sizeof(int2), cudaMemcpyHostToDevice, sl.stream));
-        if (tot_r > 0) CK(cudaMemcpyAsync(sl.ref.p, gr, (size_t)tot_r, cudaMemcpyHostToDevice, sl.stream));
-        if (tot_q > 0) CK(cudaMemcpyAsync(sl.qer.p, gq, (size_t)tot_q, cudaMemcpyHostToDevice, sl.stream));
-        k.st.h2d_bytes += tot_r + tot_q + (long long)j.cnt * (long long)sizeof(int2);
-        bswk::swap_offsets_kernel<<<(j.cnt + 255) / 256, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, (int2 *)sl.off.p, j.cnt);
-        CK(cudaGetLastError());
-        k.st.kernel_launches++;
-        j.rlo = 0; j.qlo = 0;
-        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p, j.cnt, sl.stream, tier8_check,
-                     0, std::max(tot_r, 1LL), 0, std::max(tot_q, 1LL));
+        DevCtx &x = *j.x;
+        const bsw_seqpair_t *d_pairs = (const bsw_seqpair_t *)sl.pairs.p;
+        /* query bases */
+        if (in_arena_q) {
+            CK(cudaStreamWaitEvent(sl.stream, x.arena_ev, 0));
+            j.d_qer = (const uint8_t *)x.arena_qer.p + (qer - k.arena_qer_h);
+            qlo = k.arena_qer_h - qer; qhi = qlo + (long long)k.arena_qer_n;
+        } else {
+            sl.qer.reserve((size_t)(qhi - qlo) + 64);
+            if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
+            k.st.h2d_bytes += qhi - qlo;
+            j.d_qer = (const uint8_t *)sl.qer.p - qlo;
+        }
+        /* target bases */
+        if (rref) {
+            /* expand the targets from the resident 2-bit reference into a dense scratch; the records' idr are rewritten on
+             * the device to point into it.  Its size is estimated from the sampled lengths (x 1.25) unless `exact`;
+             * the kernel reports an overflow through Plan::oob_pairs, like a pair outside the sampled byte ranges. */
+            const long long cap = exact ? l1s + 64 : (l1s * 32 * 5) / 4 + 65536;
+            CK(cudaMemsetAsync(sl.plan.p, 0, sizeof(Plan), sl.stream));
+            sl.reftmp.reserve((size_t)cap + 64);
+            sl.rpos.reserve((size_t)j.cnt * 8); sl.toff.reserve((size_t)j.cnt * 4 + 4);
+            CK(cudaMemcpyAsync(sl.rpos.p, rpos + j.first, (size_t)j.cnt * 8, cudaMemcpyHostToDevice, sl.stream));
+            k.st.h2d_bytes += (long long)j.cnt * 8;
+            size_t tmp_bytes = 0;
+            auto it = thrust::make_transform_iterator(thrust::make_counting_iterator(0), Len1Rounded{ d_pairs });
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, (int *)sl.toff.p, j.cnt, sl.stream));
+            sl.cubtmp.reserve(tmp_bytes);
+            CK(cub::DeviceScan::ExclusiveSum(sl.cubtmp.p, tmp_bytes, it, (int *)sl.toff.p, j.cnt, sl.stream));
+            const uint8_t *d_pac = rref->on(x.dev);
+            if (!d_pac) die("the reference was not uploaded to a device this handle uses");
+            ref_expand_kernel<<<(j.cnt + 31) / 32, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, j.cnt, (const long long *)sl.rpos.p,
+                                                                       (int *)sl.toff.p, d_pac, rref->l_pac, (uint8_t *)sl.reftmp.p,
+                                                                       cap, (Plan *)sl.plan.p);
+            CK(cudaGetLastError());
+            k.st.kernel_launches += 3;
+            j.d_ref = (const uint8_t *)sl.reftmp.p;
+            rlo = 0; rhi = cap;
+        } else if (in_arena_r) {
+            CK(cudaStreamWaitEvent(sl.stream, x.arena_ev, 0));
+            j.d_ref = (const uint8_t *)x.arena_ref.p + (ref - k.arena_ref_h);
+            rlo = k.arena_ref_h - ref; rhi = rlo + (long long)k.arena_ref_n;
+        } else {
+            sl.ref.reserve((size_t)(rhi - rlo) + 64);
+            if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
+            k.st.h2d_bytes += rhi - rlo;
+            j.d_ref = (const uint8_t *)sl.ref.p - rlo;
+        }
+        plan_enqueue(k, sl, d_pairs, j.d_qer, j.cnt, sl.stream, tier8_check, rlo, rhi, qlo, qhi, !rref);
     };
     std::vector<Job> jobs(nchunks);
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
     auto stage_a = [&](int ci) {
         Job &j = jobs[ci];
         j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
-        j.x = &k.ctx[ci % nd]; j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
-        slot_retire(k, *j.x, *j.sl);              /* its previous chunk must have landed */
+        j.di = ci % nd;
+        j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
+        slot_retire(*j.x, *j.sl);              /* its previous chunk must have landed */
         Slot &sl = *j.sl;
         CK(cudaSetDevice(j.x->dev));
         sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
         CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
         k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t);
-        if (k.gather > 0) upload_gathered(j);
-        else upload(j, false);
+        upload(j, false);
         sl.busy = true;
     };
     /* stage B: wait for the histogram, launch the DP kernels, download the results */
@@ -623,17 +635,15 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         CK(cudaSetDevice(j.x->dev));
         const Plan *pl = plan_wait(sl, sl.stream);
         if (pl->oob_pairs) {                      /* the sampled ranges missed a pair: redo with the exact scan */
-            if (k.gather > 0) die("internal: gathered offsets out of range");
+            if (rref) CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
             upload(j, true);
             pl = plan_wait(sl, sl.stream);
-            if (pl->oob_pairs) die("internal: exact extents still miss a pair");
+            if (pl->oob_pairs) die("a pair names bases outside its sequence buffer / declared arena");
         }
-        /* the kernels index the sequence buffers with the caller's idr/idq: rebase the pointers */
-        launch_bsw_dp(k, *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - j.rlo,
-                      (const uint8_t *)sl.qer.p - j.qlo, j.cnt, w, sl.stream);
-        if (k.gather > 0) {                       /* the caller's idr / idq go back into the records before the download */
-            bswk::swap_offsets_kernel<<<(j.cnt + 255) / 256, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, (int2 *)sl.off.p, j.cnt);
-            CK(cudaGetLastError());
+        /* the kernels index the sequence buffers with the caller's idr/idq: the pointers were rebased in upload() */
+        launch_bsw_dp(k, k.rt(j.di), *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, j.d_ref, j.d_qer, j.cnt, w, sl.stream);
+        if (rref) {                                /* the caller's idr come back untouched */
+            restore_idr_kernel<<<(j.cnt + 255) / 256, 256, 0, sl.stream>>>((bsw_seqpair_t *)sl.pairs.p, j.cnt, (const int *)sl.toff.p);
             k.st.kernel_launches++;
         }
         CK(cudaMemcpyAsync(pairs + j.first, sl.pairs.p, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyDeviceToHost, sl.stream));
@@ -647,93 +657,190 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
         if (ci + ahead < nchunks) stage_a(ci + ahead);
         stage_b(ci);
     }
-    for (DevCtx &x : k.ctx)
-        for (Slot &sl : x.slot) slot_retire(k, x, sl);
+    for (size_t i = 0; i < k.ctx.size(); ++i)
+        if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
 }
 
-/* ---- kswv host-pointer call: one slice per device (slot 0), synchronous -------------------------- */
-void host_call_kswv_part(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
-                         int n, int is8, int phase);
+/* ---- direct kswv call: chunks of BSW_CUDA_KSWV_CHUNK pairs, pipelined over the slots like BSW -----
+ * phase 0 writes aln[i]; phase 1 refines aln[regid]: the device computes the reverse pass of every pair into a dense
+ * per-chunk result array and the host applies the rule (score equal -> tb, qb), so no aln span goes up. */
+void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
+                      int n, int is8, int phase)
+{
+    const int nd = (int)k.devs.size();
+    const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
+    const int nchunks = (n + chunk - 1) / chunk;
+    struct Job { int first, cnt, di; DevCtx *x; Slot *sl; bsw_kswr_t *h_res; };
+    std::vector<Job> jobs(nchunks);
+    auto finish = [&](Job &j) {              /* chunk landed: phase 1 applies the refinement rule on the host */
+        slot_retire(*j.x, *j.sl);
+        if (phase == 1)
+            for (int i = 0; i < j.cnt; ++i) {
+                const bsw_kswr_t &rr = j.h_res[i];
+                bsw_kswr_t *a = &aln[pairs[j.first + i].regid];
+                if (a->score == rr.score) { a->tb = a->te - rr.te; a->qb = a->qe - rr.qe; }
+            }
+        j.h_res = nullptr;
+    };
+    auto stage = [&](int ci) {
+        Job &j = jobs[ci];
+        j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
+        j.di = ci % nd;
+        j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
+        if (ci >= nd * BSW_NSLOT) finish(jobs[ci - nd * BSW_NSLOT]);      /* the slot's previous chunk */
+        Slot &sl = *j.sl;
+        CK(cudaSetDevice(j.x->dev));
+        long long rlo, rhi, qlo, qhi;
+        extents_sampled(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            if (attempt == 1) extents(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
+            sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
+            sl.ref.reserve((size_t)(rhi - rlo) + 64); sl.qer.reserve((size_t)(qhi - qlo) + 64);
+            sl.aln.reserve((size_t)j.cnt * sizeof(bsw_kswr_t));
+            CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
+            if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
+            if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
+            k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
+            plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - qlo, j.cnt, sl.stream, 0, rlo, rhi, qlo, qhi);
+            const Plan *pl = plan_wait(sl, sl.stream);
+            if (!pl->oob_pairs) break;
+            if (attempt == 1) die("a pair names bases outside its sequence buffer");
+        }
+        /* the device always stores the raw pass result of pair i at chunk-local index i (phase-0 store rule) */
+        launch_kswv_dp(k, k.rt(j.di), *j.x, sl, sl.h_plan, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - rlo,
+                       (const uint8_t *)sl.qer.p - qlo, (bsw_kswr_t *)sl.aln.p, j.cnt, is8, 0, sl.stream);
+        if (phase == 0) j.h_res = aln + j.first;
+        else { sl.h_res.reserve((size_t)chunk * sizeof(bsw_kswr_t)); j.h_res = (bsw_kswr_t *)sl.h_res.p; }
+        CK(cudaMemcpyAsync(j.h_res, sl.aln.p, (size_t)j.cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, sl.stream));
+        CK(cudaEventRecord(sl.done, sl.stream));
+        sl.busy = true;
+        k.st.d2h_bytes += (int64_t)j.cnt * sizeof(bsw_kswr_t);
+    };
+    for (int ci = 0; ci < nchunks; ++ci) stage(ci);
+    for (int ci = std::max(0, nchunks - nd * BSW_NSLOT); ci < nchunks; ++ci) finish(jobs[ci]);
+}
 
-/* bounded device scratch: the row-maximum scratch is (max len1) x (pairs) x 2 B, so large calls go in parts of
- * BSW_CUDA_KSWV_PART pairs (phase 0 indexes aln by position, phase 1 by regid) */
+/* ================================================================ staged calls (engine.cuh) */
+
+/* the device with the fewest pairs outstanding in its engine */
+int pick_engine(Core &k)
+{
+    int best = 0; long long load = -1;
+    for (int i = 0; i < (int)k.devs.size(); ++i) {
+        const long long l = k.rt(i).eng().outstanding.load(std::memory_order_relaxed);
+        if (load < 0 || l < load) { load = l; best = i; }
+    }
+    return best;
+}
+
+inline bool bytes_have_n(const uint8_t *p, int len)
+{
+    uint8_t acc = 0;
+    for (int j = 0; j < len; ++j) acc |= p[j];
+    return (acc & 0xfc) != 0;
+}
+
+/* class of one pair: the same rules prep_kernel applies on the device (bsw_kernels.cuh) */
+inline int classify(const Core &k, const bsw_seqpair_t &p, const uint8_t *qer)
+{
+    const bool ok = k.mode == MODE_BSW ? packed_eligible(k.c, p.len1, p.len2, p.h0) : kswv_packed_eligible(k.c, p.len1, p.len2);
+    const int qb = (p.len2 + (k.mode == MODE_BSW ? BSW_SWEEP_SLACK : 1) + 15) >> 4;
+    if (!ok || qb > BSW_NBINS) return CLS_GENERAL;
+    if (k.mode == MODE_BSW && p.len2 > 0 && bytes_have_n(qer + p.idq, p.len2)) return BSW_NBINS + qb;
+    return qb;
+}
+
+/* one host-pointer call through the engine, in parts that fit a staging slot */
+void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln, int n, int w,
+                 int tier8_check, int is8, int phase)
+{
+    Engine &eng = k.rt(pick_engine(k)).eng();
+    const BatchKey key = make_key(k.mode, k.c, w, is8);
+    std::vector<uint8_t> cls;
+    int first = 0;
+    while (first < n) {
+        /* pass 1 over the part: contract, classes, byte sums */
+        int cnt[BSW_NCLASS]; memset(cnt, 0, sizeof cnt);
+        long long bytes = 0; int m = 0, bad = 0, ml1p = 0, ml2g = 0, ml1g = 0;
+        cls.clear();
+        for (int i = first; i < n && m < eng.cap_pairs; ++i, ++m) {
+            const bsw_seqpair_t &p = pairs[i];
+            if (p.len1 < 0 || p.len2 < 0 || (k.mode == MODE_BSW && p.h0 <= 0) ||
+                (tier8_check && (p.len1 >= BSW_MAX_SEQ_LEN8 || p.len2 >= BSW_MAX_SEQ_LEN8))) { ++bad; cls.push_back(0); continue; }
+            const long long b = (long long)p.len1 + p.len2;
+            if (bytes + b + 64 > eng.cap_bytes) {
+                if (m == 0) die("one pair is larger than a staging slot (raise BSW_CUDA_STAGE_MB)");
+                break;
+            }
+            bytes += b;
+            const int c = classify(k, p, qer);
+            cls.push_back((uint8_t)c); cnt[c]++;
+            if (c == CLS_GENERAL) { ml2g = std::max(ml2g, p.len2); ml1g = std::max(ml1g, p.len1); }
+            else ml1p = std::max(ml1p, p.len1);
+        }
+        if (bad) die_contract(bad);
+        Reservation r = eng.reserve(key, m, bytes, cnt, ml1p, ml2g, ml1g);
+        StagedSlot &s = *r.slot;
+        /* pass 2: pack */
+        {
+            int *rec = reinterpret_cast<int *>(s.h_rec + (size_t)r.pair_base * 24);
+            uint8_t *seq = reinterpret_cast<uint8_t *>(s.h_seq);
+            long long off = r.byte_base;
+            int pos[BSW_NCLASS]; memcpy(pos, r.cls_pos, sizeof pos);
+            for (int t = 0; t < m; ++t, rec += 6) {
+                const bsw_seqpair_t &p = pairs[first + t];
+                const int c = cls[t];
+                rec[0] = (int)off; rec[1] = (int)(off + p.len1);
+                rec[2] = (int)(((uint32_t)c << 24) | (uint32_t)pos[c]++);
+                rec[3] = p.len1; rec[4] = p.len2; rec[5] = p.h0;
+                memcpy(seq + off, ref + p.idr, (size_t)p.len1);
+                memcpy(seq + off + p.len1, qer + p.idq, (size_t)p.len2);
+                off += (long long)p.len1 + p.len2;
+            }
+        }
+        eng.packed(r, m);
+        eng.wait_done(r);
+        /* results */
+        if (k.mode == MODE_BSW) {
+            const char *res = s.h_res + (size_t)r.pair_base * 24;
+            for (int t = 0; t < m; ++t) memcpy(&pairs[first + t].score, res + (size_t)t * 24, 24);
+            k.st.d2h_bytes += (long long)m * 24;
+        } else {
+            const bsw_kswr_t *res = reinterpret_cast<const bsw_kswr_t *>(s.h_res) + r.pair_base;
+            if (phase == 0) memcpy(aln + first, res, (size_t)m * sizeof(bsw_kswr_t));
+            else
+                for (int t = 0; t < m; ++t) {
+                    bsw_kswr_t *a = &aln[pairs[first + t].regid];
+                    if (a->score == res[t].score) { a->tb = a->te - res[t].te; a->qb = a->qe - res[t].qe; }
+                }
+            k.st.d2h_bytes += (long long)m * (long long)sizeof(bsw_kswr_t);
+        }
+        eng.release(r, m);
+        k.st.h2d_bytes += (long long)m * 24 + bytes;
+        k.st.pairs += m; k.st.pairs_general += cnt[CLS_GENERAL]; k.st.pairs_packed += m - cnt[CLS_GENERAL];
+        first += m;
+    }
+}
+
+void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check)
+{
+    k.st.calls++;
+    if (n <= 0) return;
+    if (!pairs || !ref || !qer) die("null buffer passed to getScores");
+    if (n >= k.direct_min || k.count_cells || k.timing) direct_call_bsw(k, pairs, ref, qer, n, w, tier8_check);
+    else staged_call(k, pairs, ref, qer, nullptr, n, w, tier8_check, 0, 0);
+}
+
 void host_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
                     int n, int is8, int phase)
 {
     k.st.calls++;
-    const int part = std::max(1024, env_int("BSW_CUDA_KSWV_PART", 1 << 21));
-    for (int off = 0; off < n; off += part)
-        host_call_kswv_part(k, pairs + off, ref, qer, phase == 0 ? aln + off : aln, std::min(part, n - off), is8, phase);
-}
-
-void host_call_kswv_part(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln,
-                         int n, int is8, int phase)
-{
     if (n <= 0) return;
     if (!pairs || !ref || !qer || !aln) die("null buffer passed to kswv getScores");
-    const int nd = (int)k.ctx.size();
-    struct Slice { int first, cnt; long long rlo, rhi, qlo, qhi; int alo, ahi; };
-    std::vector<Slice> sl(nd);
-    for (int d = 0; d < nd; ++d) {
-        Slice &s = sl[d];
-        s.first = (int)((long long)n * d / nd);
-        s.cnt = (int)((long long)n * (d + 1) / nd) - s.first;
-        if (s.cnt <= 0) continue;
-        extents(pairs, s.first, s.cnt, s.rlo, s.rhi, s.qlo, s.qhi);
-        DevCtx &x = k.ctx[d];
-        Slot &t = x.slot[0];
-        CK(cudaSetDevice(x.dev));
-        t.pairs.reserve((size_t)s.cnt * sizeof(bsw_seqpair_t));
-        t.ref.reserve((size_t)(s.rhi - s.rlo) + 64);
-        t.qer.reserve((size_t)(s.qhi - s.qlo) + 64);
-        CK(cudaMemcpyAsync(t.pairs.p, pairs + s.first, (size_t)s.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, t.stream));
-        if (s.rhi > s.rlo) CK(cudaMemcpyAsync(t.ref.p, ref + s.rlo, (size_t)(s.rhi - s.rlo), cudaMemcpyHostToDevice, t.stream));
-        if (s.qhi > s.qlo) CK(cudaMemcpyAsync(t.qer.p, qer + s.qlo, (size_t)(s.qhi - s.qlo), cudaMemcpyHostToDevice, t.stream));
-        k.st.h2d_bytes += (int64_t)s.cnt * sizeof(bsw_seqpair_t) + (s.rhi - s.rlo) + (s.qhi - s.qlo);
-        if (phase == 0) { s.alo = s.first; s.ahi = s.first + s.cnt; t.aln.reserve((size_t)s.cnt * sizeof(bsw_kswr_t)); }
-        else {
-            /* phase 1 refines aln[regid]: send the span [min regid, max regid] this slice names */
-            int lo = 0x7fffffff, hi = -1;
-            for (int i = s.first; i < s.first + s.cnt; ++i) { lo = std::min(lo, pairs[i].regid); hi = std::max(hi, pairs[i].regid); }
-            if (lo < 0) die("kswv phase 1: negative regid");
-            s.alo = lo; s.ahi = hi + 1;
-            t.aln.reserve((size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t));
-            CK(cudaMemcpyAsync(t.aln.p, aln + lo, (size_t)(hi + 1 - lo) * sizeof(bsw_kswr_t), cudaMemcpyHostToDevice, t.stream));
-            k.st.h2d_bytes += (int64_t)(hi + 1 - lo) * sizeof(bsw_kswr_t);
-        }
-    }
-    for (int d = 0; d < nd; ++d) {
-        const Slice &s = sl[d];
-        if (s.cnt <= 0) continue;
-        DevCtx &x = k.ctx[d];
-        Slot &t = x.slot[0];
-        CK(cudaSetDevice(x.dev));
-        const uint8_t *d_ref = (const uint8_t *)t.ref.p - s.rlo;
-        const uint8_t *d_qer = (const uint8_t *)t.qer.p - s.qlo;
-        /* phase 0 indexes aln by slice-local pair index; phase 1 by regid, rebased to the span */
-        bsw_kswr_t *d_aln = (bsw_kswr_t *)t.aln.p - (phase == 0 ? 0 : s.alo);
-        launch_kswv(k, x, t, (const bsw_seqpair_t *)t.pairs.p, d_ref, d_qer, d_aln, s.cnt, is8, phase, t.stream);
-        const size_t cnt = (size_t)(s.ahi - s.alo);
-        if (phase == 0) {
-            CK(cudaMemcpyAsync(aln + s.alo, t.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, t.stream));
-        } else {
-            /* only tb/qb of the named entries change; copy back through a bounce so that entries of
-             * other devices inside the span are not clobbered */
-            std::vector<bsw_kswr_t> tmp(cnt);
-            CK(cudaMemcpyAsync(tmp.data(), t.aln.p, cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, t.stream));
-            CK(cudaStreamSynchronize(t.stream));
-            for (int i = s.first; i < s.first + s.cnt; ++i) {
-                const int r = pairs[i].regid;
-                aln[r].tb = tmp[r - s.alo].tb; aln[r].qb = tmp[r - s.alo].qb;
-            }
-        }
-        k.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_kswr_t);
-    }
-    for (int d = 0; d < nd; ++d) {
-        if (sl[d].cnt <= 0) continue;
-        CK(cudaSetDevice(k.ctx[d].dev));
-        CK(cudaStreamSynchronize(k.ctx[d].slot[0].stream));
-    }
+    if (phase == 1)
+        for (int i = 0; i < n; ++i) if (pairs[i].regid < 0) die("kswv phase 1: negative regid");
+    if (n >= k.direct_min || k.timing) direct_call_kswv(k, pairs, ref, qer, aln, n, is8, phase);
+    else staged_call(k, pairs, ref, qer, aln, n, 0, 0, is8, phase);
 }
 
 } /* namespace */
@@ -743,7 +850,7 @@ struct kswv_handle { Core k; int32_t maxRefLen, maxQerLen; };
 
 extern "C" {
 
-const char *bsw_version(void) { return "bsw-b200 0.1 (sm_100a, packed s16x2 DPX)"; }
+const char *bsw_version(void) { return "bsw-b200 0.2 (sm_100a, packed s16x2 DPX)"; }
 
 int bsw_device_count(void)
 {
@@ -785,13 +892,80 @@ void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_
     host_call_bsw(h->k, pairArray, seqBufRef, seqBufQer, numPairs, w, 0);
 }
 
+/* ---- sequence arenas ------------------------------------------------------------------------- */
+void bsw_arena_begin(bsw_t *h, const uint8_t *seqBufRef, size_t refBytes, const uint8_t *seqBufQer, size_t qerBytes)
+{
+    Core &k = h->k;
+    if (k.arena_on) die("bsw_arena_begin: an arena is already declared on this handle");
+    k.arena_ref_h = seqBufRef; k.arena_ref_n = seqBufRef ? refBytes : 0;
+    k.arena_qer_h = seqBufQer; k.arena_qer_n = seqBufQer ? qerBytes : 0;
+    for (int i = 0; i < (int)k.devs.size(); ++i) {
+        DevCtx &x = k.cx(i);
+        CK(cudaSetDevice(x.dev));
+        /* the slots may still read the previous arena's copies */
+        for (Slot &sl : x.slot) slot_retire(x, sl);
+        x.arena_ref.reserve(k.arena_ref_n + 64); x.arena_qer.reserve(k.arena_qer_n + 64);
+        if (k.arena_ref_n) CK(cudaMemcpyAsync(x.arena_ref.p, seqBufRef, k.arena_ref_n, cudaMemcpyHostToDevice, x.arena_stream));
+        if (k.arena_qer_n) CK(cudaMemcpyAsync(x.arena_qer.p, seqBufQer, k.arena_qer_n, cudaMemcpyHostToDevice, x.arena_stream));
+        CK(cudaEventRecord(x.arena_ev, x.arena_stream));
+        k.st.h2d_bytes += (long long)(k.arena_ref_n + k.arena_qer_n);
+    }
+    k.arena_on = true;
+}
+
+void bsw_arena_end(bsw_t *h)
+{
+    Core &k = h->k;
+    if (!k.arena_on) return;
+    for (size_t i = 0; i < k.ctx.size(); ++i)
+        if (k.ctx[i]) { CK(cudaSetDevice(k.ctx[i]->dev)); CK(cudaStreamSynchronize(k.ctx[i]->arena_stream)); }
+    k.arena_on = false;
+    k.arena_ref_h = k.arena_qer_h = nullptr; k.arena_ref_n = k.arena_qer_n = 0;
+}
+
+/* ---- resident reference --------------------------------------------------- */
+bsw_ref_t *bsw_ref_upload(const uint8_t *pac, int64_t l_pac)
+{
+    if (!pac || l_pac <= 0) die("bsw_ref_upload: empty reference");
+    bsw_ref_t *r = new bsw_ref();
+    r->l_pac = l_pac;
+    const size_t bytes = (size_t)((l_pac + 3) >> 2);
+    for (int d : pick_devices()) {
+        (void)devrt(d);
+        CK(cudaSetDevice(d));
+        RefCopy c; c.dev = d; c.d_pac = nullptr;
+        CK(cudaMalloc((void **)&c.d_pac, bytes + 16));
+        CK(cudaMemset(c.d_pac + bytes, 0, 16));
+        CK(cudaMemcpy(c.d_pac, pac, bytes, cudaMemcpyHostToDevice));
+        r->copies.push_back(c);
+    }
+    return r;
+}
+
+void bsw_ref_free(bsw_ref_t *r)
+{
+    if (!r) return;
+    for (RefCopy &c : r->copies) { cudaSetDevice(c.dev); cudaFree(c.d_pac); }
+    delete r;
+}
+
+void bsw_getScoresRef(bsw_t *h, bsw_seqpair_t *pairArray, const bsw_ref_t *ref, const int64_t *rpos,
+                      const uint8_t *seqBufQer, int32_t numPairs, int32_t w)
+{
+    Core &k = h->k;
+    k.st.calls++;
+    if (numPairs <= 0) return;
+    if (!pairArray || !ref || !rpos || !seqBufQer) die("null buffer passed to bsw_getScoresRef");
+    direct_call_bsw(k, pairArray, nullptr, seqBufQer, numPairs, w, 0, ref, rpos);
+}
+
 /* Device-resident calls rotate over the slots (sort keys, permutation, histogram mailbox, general-path scratch), so
  * that calls issued on DIFFERENT caller streams overlap: the next call's prep / sort / DP blocks fill the SMs while the
  * previous call's last warps drain (bench step of four 2.5M-pair calls: 18.54 ms on one stream, 18.16 ms on four).
  * Calls on one stream stay ordered by that stream.  A slot is reused only after the call that last used it has finished (stream-side wait). */
 static Slot &dev_slot(DevCtx &x, cudaStream_t s, bool rotate)
 {
-    /* kswv keeps to one slot: its row-maxima scratch is ~1 GB per million pairs, and a slot's buffers grow on first use */
+    /* kswv keeps to one slot: its row-maxima scratch is large, and a slot's buffers grow on first use */
     Slot &sl = x.slot[rotate ? x.dev_rr : 0];
     if (rotate) x.dev_rr = (x.dev_rr + 1) % BSW_NSLOT;
     if (sl.dev_used) CK(cudaStreamWaitEvent(s, sl.dev_done, 0));
@@ -802,11 +976,11 @@ static Slot &dev_slot(DevCtx &x, cudaStream_t s, bool rotate)
 void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
                        int32_t numPairs, int32_t w, void *stream)
 {
-    DevCtx &x = h->k.ctx[0];
+    DevCtx &x = h->k.cx(0);
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
     Slot &sl = dev_slot(x, (cudaStream_t)stream, true);
-    launch_bsw(h->k, x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
+    launch_bsw(h->k, h->k.rt(0), x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, w, (cudaStream_t)stream, 0);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
 }
 
@@ -814,7 +988,7 @@ void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_se
  * then up to maxBandTry-1 retries with the band doubled, each on the pairs the upstream rule selects (score changed by
  * the attempt and max_off >= 3/4 of the attempt's band), moved to a dense sub-array and back.  One 4-byte read-back per
  * retry (the count) on top of the histogram read-back of every BSW launch. */
-static void dev_extend_side(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+static void dev_extend_side(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
                             int n, int w, int max_try, cudaStream_t s)
 {
     if (n <= 0) return;
@@ -823,7 +997,7 @@ static void dev_extend_side(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs
     sl.px_list.reserve((size_t)n * sizeof(int));
     sl.px_count.reserve(sizeof(int));
     bswk::proto_save_score_kernel<<<G, T, 0, s>>>(d_pairs, n, (int *)sl.px_prev.p);
-    launch_bsw(k, x, sl, d_pairs, d_ref, d_qer, n, w, s, 0);
+    launch_bsw(k, rt, x, sl, d_pairs, d_ref, d_qer, n, w, s, 0);
     for (int attempt = 1; attempt < max_try; ++attempt) {
         const int w_prev = w << (attempt - 1), w_now = w << attempt;
         CK(cudaMemsetAsync(sl.px_count.p, 0, sizeof(int), s));
@@ -839,7 +1013,7 @@ static void dev_extend_side(Core &k, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs
         sl.px_sub.reserve((size_t)m * sizeof(bsw_seqpair_t));
         const int Gm = (m + T - 1) / T;
         bswk::proto_gather_kernel<<<Gm, T, 0, s>>>(d_pairs, (const int *)sl.px_list.p, m, (bsw_seqpair_t *)sl.px_sub.p);
-        launch_bsw(k, x, sl, (bsw_seqpair_t *)sl.px_sub.p, d_ref, d_qer, m, w_now, s, 0);
+        launch_bsw(k, rt, x, sl, (bsw_seqpair_t *)sl.px_sub.p, d_ref, d_qer, m, w_now, s, 0);
         bswk::proto_scatter_kernel<<<Gm, T, 0, s>>>((const bsw_seqpair_t *)sl.px_sub.p, (const int *)sl.px_list.p, m, d_pairs);
         CK(cudaGetLastError());
         k.st.kernel_launches += 2;
@@ -850,18 +1024,19 @@ void bsw_dev_extendChained(bsw_t *h, bsw_seqpair_t *d_left, const uint8_t *d_lef
                            bsw_seqpair_t *d_right, const uint8_t *d_rightRef, const uint8_t *d_rightQer, int32_t numRight,
                            int32_t w, int32_t maxBandTry, void *stream)
 {
-    DevCtx &x = h->k.ctx[0];
+    DevCtx &x = h->k.cx(0);
+    DevRt &rt = h->k.rt(0);
     CK(cudaSetDevice(x.dev));
     cudaStream_t s = (cudaStream_t)stream;
     h->k.st.calls++;
     Slot &sl = dev_slot(x, s, true);
     const int tries = maxBandTry < 1 ? 1 : maxBandTry;
-    dev_extend_side(h->k, x, sl, d_left, d_leftRef, d_leftQer, numLeft, w, tries, s);
+    dev_extend_side(h->k, rt, x, sl, d_left, d_leftRef, d_leftQer, numLeft, w, tries, s);
     if (numRight > 0) {
         bswk::proto_chain_h0_kernel<<<(numRight + 255) / 256, 256, 0, s>>>(d_left, numLeft, d_right, numRight);
         CK(cudaGetLastError());
         h->k.st.kernel_launches++;
-        dev_extend_side(h->k, x, sl, d_right, d_rightRef, d_rightQer, numRight, w, tries, s);
+        dev_extend_side(h->k, rt, x, sl, d_right, d_rightRef, d_rightQer, numRight, w, tries, s);
     }
     CK(cudaEventRecord(sl.dev_done, s));
 }
@@ -896,11 +1071,12 @@ void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBuf
 void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
                         bsw_kswr_t *d_aln, int32_t numPairs, int is8, int phase, void *stream)
 {
-    DevCtx &x = h->k.ctx[0];
+    DevCtx &x = h->k.cx(0);
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
     Slot &sl = dev_slot(x, (cudaStream_t)stream, false);
-    launch_kswv(h->k, x, sl, d_pairArray, d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase, (cudaStream_t)stream);
+    launch_kswv(h->k, h->k.rt(0), x, sl, const_cast<bsw_seqpair_t *>(d_pairArray), d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase,
+                (cudaStream_t)stream);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
 }
 
@@ -915,11 +1091,12 @@ void bsw_host_free(void *p) { if (p) CK(cudaFreeHost(p)); }
 static void stats_with_pending(Core &k, bsw_stats_t *out)
 {
     long long cells = 0;
-    for (DevCtx &x : k.ctx) {
-        CK(cudaSetDevice(x.dev));
+    for (DevCtx *x : k.ctx) {
+        if (!x) continue;
+        CK(cudaSetDevice(x->dev));
         CK(cudaDeviceSynchronize());
         unsigned long long c = 0;
-        CK(cudaMemcpy(&c, x.cells.p, sizeof c, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&c, x->cells.p, sizeof c, cudaMemcpyDeviceToHost));
         cells += (long long)c;
     }
     k.st.cells = cells;
@@ -928,10 +1105,11 @@ static void stats_with_pending(Core &k, bsw_stats_t *out)
 static void stats_reset(Core &k)
 {
     memset(&k.st, 0, sizeof k.st);
-    for (DevCtx &x : k.ctx) {
-        CK(cudaSetDevice(x.dev));
+    for (DevCtx *x : k.ctx) {
+        if (!x) continue;
+        CK(cudaSetDevice(x->dev));
         CK(cudaDeviceSynchronize());
-        CK(cudaMemset(x.cells.p, 0, sizeof(unsigned long long)));
+        CK(cudaMemset(x->cells.p, 0, sizeof(unsigned long long)));
     }
 }
 
@@ -939,9 +1117,28 @@ void bsw_get_stats(bsw_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); 
 void bsw_reset_stats(bsw_t *h) { stats_reset(h->k); }
 void bsw_set_timing(bsw_t *h, int on) { h->k.timing = on; }
 void bsw_set_cell_counting(bsw_t *h, int on) { h->k.count_cells = on; }
+void bsw_set_direct_min(bsw_t *h, int pairs) { h->k.direct_min = pairs; }
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
 void kswv_reset_stats(kswv_t *h) { stats_reset(h->k); }
 void kswv_set_timing(kswv_t *h, int on) { h->k.timing = on; }
+void kswv_set_direct_min(kswv_t *h, int pairs) { h->k.direct_min = pairs; }
+
+void bsw_engine_get_stats(int device, bsw_engine_stats_t *out)
+{
+    memset(out, 0, sizeof *out);
+    DevRt *r = nullptr;
+    { std::lock_guard<std::mutex> lk(g_rt_mu); if (device >= 0 && device < (int)g_rt.size()) r = g_rt[device]; }
+    if (!r || !r->engine) return;
+    const EngineStats s = r->engine->stats();
+    out->batches = s.batches; out->pairs = s.pairs; out->calls = s.calls; out->kernel_launches = s.launches;
+    out->h2d_bytes = s.h2d_bytes; out->d2h_bytes = s.d2h_bytes; out->max_batch_pairs = s.max_batch_pairs;
+}
+void bsw_engine_reset_stats(int device)
+{
+    DevRt *r = nullptr;
+    { std::lock_guard<std::mutex> lk(g_rt_mu); if (device >= 0 && device < (int)g_rt.size()) r = g_rt[device]; }
+    if (r && r->engine) r->engine->reset_stats();
+}
 
 double bsw_measure_dpx_peak(int device, int which)
 {

@@ -15,7 +15,9 @@
  *   - target bases come from a 4-row window per lane that is refilled by a warp-uniform branch every
  *     fourth row (one aligned word load per lane, issued four rows before it is needed).
  * Rows the fast path does not admit run the masked generic cell loop (exact for any band geometry).
- * The DP-cell counting variant (COUNT) stays on bsw_core.cuh's bsw_packed_thread.
+ * COUNT additionally tracks every lane's exact trimmed `beg` (A.1's left trim, which the sweep itself
+ * replaces by the lazy common start `t`) and sums end - beg over the rows entered: the oracle's DP-cell
+ * count.  Results are identical with and without it.
  *
  * Requires columns [0, max(len2)+3] of he/qs to exist (the kernel sizes the bin with 4 columns of slack).
  */
@@ -213,7 +215,7 @@ BSW_HD uint32_t twin_refill(TWin &t, int r)
 /*
  * One thread, two pairs (see bsw_core.cuh for the layout of he / qs and the exactness notes).
  */
-template <int S, bool SYM, bool QN>
+template <int S, bool SYM, bool QN, bool COUNT>
 BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const PairIn &B,
                                const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
                                uint32_t *he, uint16_t *qs, const uint32_t *lut5, PairOut &oa, PairOut &ob)
@@ -221,6 +223,8 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
     const PairIn *in[2] = { &A, &B };
     int qlen[2], tlen[2], h0[2], wb[2], end[2], smax[2], max_i[2], max_j[2], max_ie[2], gscore[2], max_off[2], clean[2];
     int act = 0;                                   /* bit p: lane p is live */
+    int beg[2] = { 0, 0 };                         /* COUNT: A.1's exact beg of each lane */
+    long long cells[2] = { 0, 0 };
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const PairIn &x = *in[p];
@@ -337,6 +341,10 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
             end[p] = mn(mn(end[p], i + wb[p] + 1), qlen[p]);
             st[p] = mx(t, lb[p]);
 #endif
+            if (COUNT && ((act >> p) & 1)) {                    /* A.1: beg = max(beg, i - w); cells += end - beg */
+                beg[p] = mx(beg[p], i - wb[p]);
+                if (end[p] > beg[p]) cells[p] += end[p] - beg[p];
+            }
             if (((act >> p) & 1) && st[p] >= end[p]) empty |= 1 << p;
         }
         if (empty) {
@@ -427,6 +435,12 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
             smax[p] = upd ? m : smax[p]; max_i[p] = upd ? i : max_i[p]; max_j[p] = upd ? mj : max_j[p];
             if (live && stop) dying |= 1 << p;
             if (live && !stop && h1p == 0) scan |= 1 << p;
+            if (COUNT && live && !stop) {                          /* A.1's left trim: first non-zero entry in [beg, end) */
+                const uint32_t hm = p ? 0xffff0000u : 0x0000ffffu;
+                int jj = beg[p];
+                while (jj < eold[p] && !(he[jj * S] & hm)) ++jj;
+                beg[p] = jj;
+            }
             end[p] = mn(end[p] + 2, qlen[p]);                      /* right trim when eh[end].h != 0; else the scan below */
         }
         if (scan | dying) {                                        /* the rare events of a row, one branch */
@@ -466,7 +480,7 @@ BSW_HD void bsw_packed_thread2(const Const &c, int w_in, const PairIn &A, const 
     for (int p = 0; p < 2; ++p) {
         out[p]->score = smax[p]; out[p]->qle = max_j[p] + 1; out[p]->tle = max_i[p] + 1;
         out[p]->gtle = max_ie[p] + 1; out[p]->gscore = gscore[p]; out[p]->max_off = max_off[p];
-        out[p]->cells = 0;
+        out[p]->cells = cells[p];
     }
 }
 

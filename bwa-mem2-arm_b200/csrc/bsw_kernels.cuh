@@ -17,6 +17,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stddef.h>
+#include <string.h>
 #include "../../include/bsw_cuda.h"
 #include "bsw_core.cuh"
 #include "bsw_core2.cuh"
@@ -35,6 +37,7 @@ struct Plan {
     int hist_n[BSW_NBINS + 2];     /* BSW: the subset of them whose query holds an N / invalid base (sorted first; counted here, not in hist) */
     int n_general;                 /* pairs routed to the general kernel */
     int max_len1;                  /* over all pairs                      */
+    int max_len1_packed;           /* over the pairs the packed kernels take (sizes kswv's row-maximum scratch) */
     int max_len2_general;
     int bad_pairs;                 /* contract violations seen by prep    */
     int oob_pairs;                 /* pairs whose bases fall outside the uploaded byte ranges */
@@ -66,9 +69,9 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, Plan *plan)
 {
     __shared__ int s_hist[2 * (BSW_NBINS + 2)];
-    __shared__ int s_misc[4];
+    __shared__ int s_misc[5];
     if (threadIdx.x < 2 * (BSW_NBINS + 2)) s_hist[threadIdx.x] = 0;
-    if (threadIdx.x < 4) s_misc[threadIdx.x] = 0;
+    if (threadIdx.x < 5) s_misc[threadIdx.x] = 0;
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -90,6 +93,7 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
             const bool qn = mode == MODE_BSW && len2 > 0 && iq0 >= qlo && iq0 + len2 <= qhi && query_has_n(qer, iq0, len2);
             if (qn) key |= 1u << 25;
             atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
+            atomicMax(&s_misc[4], len1);
         } else {
             atomicAdd(&s_misc[0], 1);
             atomicMax(&s_misc[2], len2);
@@ -110,18 +114,87 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
     if (threadIdx.x == 0) {
         if (s_misc[0]) atomicAdd(&plan->n_general, s_misc[0]);
         atomicMax(&plan->max_len1, s_misc[1]);
+        atomicMax(&plan->max_len1_packed, s_misc[4]);
         atomicMax(&plan->max_len2_general, s_misc[2]);
         if (s_misc[3]) atomicAdd(&plan->bad_pairs, s_misc[3]);
     }
 }
 
-__device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pairs, int pi)
+/* Where a kernel finds pair i's inputs and puts its results.  Inputs are the first 24 bytes of a SeqPair
+ * ({idr, idq, id, len1, len2, h0}) at in + i * in_stride; the six BSW result words go to out + i * out_stride.
+ *   resident / direct calls: the caller's 56-byte records, in place (in = pairs, out = &pairs[0].score, strides 56);
+ *   staged calls (engine.cuh): compact 24-byte input records and a separate dense 24-byte result array. */
+struct PairIO {
+    const char *in; char *out;
+    int in_stride, out_stride;
+};
+static inline PairIO pairio_records(bsw_seqpair_t *pairs)
+{
+    PairIO io; io.in = (const char *)pairs; io.out = (char *)pairs + offsetof(bsw_seqpair_t, score);
+    io.in_stride = io.out_stride = (int)sizeof(bsw_seqpair_t);
+    return io;
+}
+static inline PairIO pairio_compact(const void *in24, void *out24)
+{
+    PairIO io; io.in = (const char *)in24; io.out = (char *)out24; io.in_stride = io.out_stride = 24;
+    return io;
+}
+
+__device__ __forceinline__ PairIn load_pair(const PairIO &io, int pi)
 {
     PairIn p;
     if (pi < 0) { p.idr = p.idq = p.len1 = p.len2 = p.h0 = 0; p.valid = 0; return p; }
-    p.idr = pairs[pi].idr; p.idq = pairs[pi].idq; p.len1 = pairs[pi].len1; p.len2 = pairs[pi].len2;
-    p.h0 = pairs[pi].h0; p.valid = 1;
+    const int2 *r = reinterpret_cast<const int2 *>(io.in + (size_t)pi * io.in_stride);
+    const int2 a = r[0], b = r[1], c = r[2];        /* {idr, idq} {id, len1} {len2, h0} */
+    p.idr = a.x; p.idq = a.y; p.len1 = b.y; p.len2 = c.x; p.h0 = c.y; p.valid = 1;
     return p;
+}
+
+__device__ __forceinline__ void store_bsw(const PairIO &io, int pi, const PairOut &o)
+{
+    int2 *w = reinterpret_cast<int2 *>(io.out + (size_t)pi * io.out_stride);
+    w[0] = make_int2(o.score, o.tle); w[1] = make_int2(o.gtle, o.qle); w[2] = make_int2(o.gscore, o.max_off);
+}
+
+/* Which pairs a block of a packed kernel serves.  One launch covers one or more query-length bins: bin k owns
+ * blocks [first_block[k], first_block[k+1]) and the sorted pair slots [first_pair[k], first_pair[k+1]), 64 per
+ * block, and lays its rows out for ne[k] columns.  The per-bin launches of the large-call paths pass one bin; the
+ * staged small-call path (engine.cuh) passes all bins of a batch in ONE launch sized for the longest bin. */
+#define BSW_MAX_TBL 17
+struct BinTable {
+    int nbins;
+    int first_block[BSW_MAX_TBL + 1];
+    int first_pair[BSW_MAX_TBL + 1];
+    int ne[BSW_MAX_TBL];
+};
+static inline BinTable bintable_single(int first, int count, int NE)
+{
+    BinTable t; memset(&t, 0, sizeof t);
+    t.nbins = 1; t.first_block[0] = 0; t.first_block[1] = (count + 63) / 64;
+    t.first_pair[0] = first; t.first_pair[1] = first + count; t.ne[0] = NE;
+    return t;
+}
+/* block -> (first sorted slot of the block, end of its bin, columns) */
+__device__ __forceinline__ void bintable_lookup(const BinTable &t, int block, int &slot0, int &bin_end, int &NE)
+{
+    int k = 0;
+    while (k + 1 < t.nbins && block >= t.first_block[k + 1]) ++k;
+    slot0 = t.first_pair[k] + (block - t.first_block[k]) * 64;
+    bin_end = t.first_pair[k + 1];
+    NE = t.ne[k];
+}
+
+/* staged batches: pair i's compact record carries (class << 24 | position within the class) in its `id` word
+ * (written by the host thread that packed it); class_start[] is known once the batch is closed.  Deterministic
+ * inverse: sorted[class_start[class] + position] = i. */
+#define BSW_NCLASS 40
+struct ClassStart { int start[BSW_NCLASS]; };
+__global__ void class_scatter_kernel(const char *__restrict__ rec24, int n, ClassStart cs, uint32_t *__restrict__ sorted)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t id = reinterpret_cast<const uint32_t *>(rec24 + (size_t)i * 24)[2];
+    sorted[cs.start[id >> 24] + (int)(id & 0xffffffu)] = (uint32_t)i;
 }
 
 /* ------------------------------------------------------------------ 4a. BSW packed */
@@ -130,15 +203,17 @@ __device__ __forceinline__ PairIn load_pair(const bsw_seqpair_t *__restrict__ pa
 #endif
 template <bool COUNT, bool SYM, bool QN>
 __global__ void __launch_bounds__(32, BSW_MINBLOCKS)
-bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+bsw_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
                   const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
-                  int first, int bin_end, int NE, Const c, int w, unsigned long long *cells)
+                  const __grid_constant__ BinTable tbl, Const c, int w, unsigned long long *cells)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int lane = threadIdx.x;
+    int slot0, bin_end, NE;
+    bintable_lookup(tbl, blockIdx.x, slot0, bin_end, NE);
     uint32_t *he = reinterpret_cast<uint32_t *>(smem) + lane;
     uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 128) + lane;
-    const int slot = first + blockIdx.x * 64 + lane * 2;
+    const int slot = slot0 + lane * 2;
     const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
     const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
     /* per-row score tables by target base: byte q of lut_tbl[t] = score(t, q) */
@@ -147,18 +222,12 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
     __syncwarp();
     unsigned long long my_cells = 0;
     if (pa >= 0) {
-        PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+        PairIn A = load_pair(io, pa), B = load_pair(io, pb);
         PairOut oa, ob;
-        if (COUNT) bsw_packed_thread<32, true, SYM>(c, w, A, B, ref, qer, he, qs, oa, ob);
-        else bsw_packed_thread2<32, SYM, QN>(c, w, A, B, ref, qer, he, qs, lut_tbl, oa, ob);
-        int2 *o = reinterpret_cast<int2 *>(&pairs[pa].score);
-        o[0] = make_int2(oa.score, oa.tle); o[1] = make_int2(oa.gtle, oa.qle); o[2] = make_int2(oa.gscore, oa.max_off);
+        bsw_packed_thread2<32, SYM, QN, COUNT>(c, w, A, B, ref, qer, he, qs, lut_tbl, oa, ob);
+        store_bsw(io, pa, oa);
         my_cells += (unsigned long long)oa.cells;
-        if (pb >= 0) {
-            o = reinterpret_cast<int2 *>(&pairs[pb].score);
-            o[0] = make_int2(ob.score, ob.tle); o[1] = make_int2(ob.gtle, ob.qle); o[2] = make_int2(ob.gscore, ob.max_off);
-            my_cells += (unsigned long long)ob.cells;
-        }
+        if (pb >= 0) { store_bsw(io, pb, ob); my_cells += (unsigned long long)ob.cells; }
     }
     if (COUNT) {
         for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
@@ -167,7 +236,7 @@ bsw_packed_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__
 }
 
 /* ------------------------------------------------------------------ 5a. BSW general */
-__global__ void bsw_general_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+__global__ void bsw_general_kernel(PairIO io, const uint8_t *__restrict__ ref,
                                    const uint8_t *__restrict__ qer, const uint32_t *__restrict__ sorted_idx,
                                    int first, int count, Const c, int w, int2 *eh, unsigned long long *cells)
 {
@@ -175,11 +244,10 @@ __global__ void bsw_general_kernel(bsw_seqpair_t *__restrict__ pairs, const uint
     unsigned long long my_cells = 0;
     if (g < count) {
         const int pi = (int)sorted_idx[first + g];
-        PairIn P = load_pair(pairs, pi);
+        PairIn P = load_pair(io, pi);
         PairOut o;
         bsw_general_thread<long long>(c, w, P, ref, qer, eh + g, (long long)count, o);
-        pairs[pi].score = o.score; pairs[pi].tle = o.tle; pairs[pi].gtle = o.gtle; pairs[pi].qle = o.qle;
-        pairs[pi].gscore = o.gscore; pairs[pi].max_off = o.max_off;
+        store_bsw(io, pi, o);
         my_cells = (unsigned long long)o.cells;
     }
     for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
@@ -187,48 +255,53 @@ __global__ void bsw_general_kernel(bsw_seqpair_t *__restrict__ pairs, const uint
 }
 
 /* ------------------------------------------------------------------ kswv result write-back */
-__device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const bsw_seqpair_t *__restrict__ pairs,
+/* phase 0 (and the staged calls of either phase, whose host side applies the phase-1 rule): aln[pi] <- the pass result;
+ * phase 1 on resident records: refine aln[regid] (regid is word 7 of the 56-byte record) */
+__device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const PairIO &io,
                                            int pi, const KswOut &o, int phase)
 {
     if (phase == 0) {
         bsw_kswr_t r; r.score = o.score; r.te = o.te; r.qe = o.qe; r.score2 = o.score2; r.te2 = o.te2; r.tb = -1; r.qb = -1;
         aln[pi] = r;
     } else {
-        bsw_kswr_t *a = &aln[pairs[pi].regid];
+        const int regid = reinterpret_cast<const int *>(io.in + (size_t)pi * io.in_stride)[7];
+        bsw_kswr_t *a = &aln[regid];
         if (a->score == o.score) { a->tb = a->te - o.te; a->qb = a->qe - o.qe; }
     }
 }
 
 /* ------------------------------------------------------------------ 4b. kswv packed */
-template <bool SYM>
+template <bool SYM>   /* only <false> is instantiated: sharing h - oe puts a third op on kswv's f -> h -> f chain (3 % slower) */
 __global__ void __launch_bounds__(32)
-kswv_packed_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+kswv_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
                    const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
-                   const uint32_t *__restrict__ sorted_idx, int first, int bin_end, int NE, Const c, int is8, int phase,
+                   const uint32_t *__restrict__ sorted_idx, const __grid_constant__ BinTable tbl, Const c, int is8, int phase,
                    uint16_t *rowmax, long long rm_stride, unsigned long long *cells)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const int lane = threadIdx.x;
+    int slot0, bin_end, NE;
+    bintable_lookup(tbl, blockIdx.x, slot0, bin_end, NE);
     uint32_t *he = reinterpret_cast<uint32_t *>(smem) + lane;
     uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 128) + lane;
-    const int slot = first + blockIdx.x * 64 + lane * 2;
+    const int slot = slot0 + lane * 2;
     const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
     const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
     unsigned long long my_cells = 0;
     if (pa >= 0) {
-        PairIn A = load_pair(pairs, pa), B = load_pair(pairs, pb);
+        PairIn A = load_pair(io, pa), B = load_pair(io, pb);
         KswOut oa, ob;
         kswv_packed_thread<32, SYM>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
-        kswv_store(aln, pairs, pa, oa, phase);
+        kswv_store(aln, io, pa, oa, phase);
         my_cells += (unsigned long long)oa.cells;
-        if (pb >= 0) { kswv_store(aln, pairs, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
+        if (pb >= 0) { kswv_store(aln, io, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
     }
     for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
     if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
 }
 
 /* ------------------------------------------------------------------ 5b. kswv general */
-__global__ void kswv_general_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref,
+__global__ void kswv_general_kernel(PairIO io, const uint8_t *__restrict__ ref,
                                     const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
                                     const uint32_t *__restrict__ sorted_idx, int first, int count,
                                     Const c, int is8, int phase, int2 *he, int *rm, unsigned long long *cells)
@@ -237,10 +310,10 @@ __global__ void kswv_general_kernel(const bsw_seqpair_t *__restrict__ pairs, con
     unsigned long long my_cells = 0;
     if (g < count) {
         const int pi = (int)sorted_idx[first + g];
-        PairIn P = load_pair(pairs, pi);
+        PairIn P = load_pair(io, pi);
         KswOut o;
         kswv_general_thread<long long>(c, is8, P, ref, qer, he + g, (long long)count, rm + g, (long long)count, o);
-        kswv_store(aln, pairs, pi, o, phase);
+        kswv_store(aln, io, pi, o, phase);
         my_cells = (unsigned long long)o.cells;
     }
     for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
@@ -328,15 +401,63 @@ __global__ void proto_chain_h0_kernel(const bsw_seqpair_t *__restrict__ left, in
 }
 
 
-/* host-pointer path with gathered sequences: exchanges (idr, idq) of the device copy of every pair with the offsets
- * into the gathered buffers; a second run puts the caller's offsets back before the results are downloaded */
-__global__ void swap_offsets_kernel(bsw_seqpair_t *__restrict__ pairs, int2 *__restrict__ off, int n)
+/* ------------------------------------------------------------------ resident reference
+ * The reference lives in HBM in bwa's .pac layout: base x of the forward strand in byte x >> 2, bits ((~x & 3) << 1).
+ * Coordinates are bwa's doubled ones (bns_get_seq / bns_fetch_seq): 0 <= x < l_pac is the forward strand, l_pac <= x <
+ * 2 l_pac the reverse complement, base(x) = 3 - fwd(2 l_pac - 1 - x).  A pair's target is len1 bases starting at
+ * rpos: read upwards (x = rpos + k) when rpos >= 0, downwards (x = ~rpos - k) when rpos < 0 -- the reversed slices
+ * mem_chain2aln_across_reads_V2 builds for left extensions.  ref_expand_kernel writes the bases, one byte each, to
+ * dst + toff[i] (toff = exclusive prefix sum of the lengths rounded up to 4) and points the device copy of the record at
+ * them; the caller's idr is parked in toff[i] and put back by restore_idr_kernel before the records go home. */
+struct Len1Rounded {
+    const bsw_seqpair_t *p;
+    __host__ __device__ int operator()(int i) const { const int l = p[i].len1; return l > 0 ? (l + 3) & ~3 : 0; }
+};
+
+__device__ __forceinline__ uint32_t pac_base(const uint8_t *__restrict__ pac, long long l_pac, long long x)
+{
+    const bool rc = x >= l_pac;
+    const long long f = rc ? 2 * l_pac - 1 - x : x;
+    const uint32_t b = (__ldg(pac + (f >> 2)) >> ((~(uint32_t)f & 3u) << 1)) & 3u;
+    return rc ? 3u - b : b;
+}
+
+__global__ void ref_expand_kernel(bsw_seqpair_t *__restrict__ pairs, int n, const long long *__restrict__ rpos,
+                                  int *__restrict__ toff, const uint8_t *__restrict__ pac, long long l_pac,
+                                  uint8_t *__restrict__ dst, long long cap, Plan *plan)
+{
+    const int i = blockIdx.x * (blockDim.x >> 3) + (threadIdx.x >> 3), sub = threadIdx.x & 7;
+    if (i >= n) return;
+    const int len = pairs[i].len1, off = toff[i];
+    const long long rp = rpos[i];
+    const bool down = rp < 0;
+    const long long x0 = down ? ~rp : rp, xl = down ? x0 - (len - 1) : x0 + (len - 1);
+    const bool bad = len > 0 && (x0 < 0 || x0 >= 2 * l_pac || xl < 0 || xl >= 2 * l_pac);
+    const bool over = len > 0 && (long long)off + ((len + 3) & ~3) > cap;
+    __syncwarp();                                   /* every lane of the pair has read len / off before lane 0 rewrites the record */
+    if (sub == 0) {
+        if (bad) atomicAdd(&plan->bad_pairs, 1);
+        else if (over) atomicAdd(&plan->oob_pairs, 1);
+        toff[i] = pairs[i].idr;
+        pairs[i].idr = off;
+    }
+    if (bad || over || len <= 0) return;
+    uint32_t *out = reinterpret_cast<uint32_t *>(dst + off);
+    for (int k4 = sub; k4 * 4 < len; k4 += 8) {
+        uint32_t w = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k4 * 4 + u;
+            if (k < len) w |= pac_base(pac, l_pac, down ? x0 - k : x0 + k) << (8 * u);
+        }
+        out[k4] = w;
+    }
+}
+
+__global__ void restore_idr_kernel(bsw_seqpair_t *__restrict__ pairs, int n, const int *__restrict__ saved)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int2 o = off[i];
-    off[i] = make_int2(pairs[i].idr, pairs[i].idq);
-    pairs[i].idr = o.x; pairs[i].idq = o.y;
+    if (i < n) pairs[i].idr = saved[i];
 }
 
 } /* namespace bswk */

@@ -80,17 +80,27 @@ typedef struct kswv_handle kswv_t;
  * compatibility; like the reference's vector kernels, scoring uses
  * w_match / w_mismatch / ambig.
  * The handle binds to the CUDA device(s) named by BSW_CUDA_DEVICES (comma list,
- * default: LOCAL_RANK if set, else device 0).  With several devices every call
- * shards its pair array into contiguous slices, one per device. */
+ * default: LOCAL_RANK if set, else device 0).  With several devices a large call
+ * deals its chunks (BSW_CUDA_CHUNK_PAIRS pairs) round-robin to them and a small call
+ * goes to the device whose engine has the fewest pairs outstanding.
+ * Creating and destroying a handle is cheap (the reference builds its objects per
+ * task and per worker thread): streams, pinned mailboxes and device scratch are
+ * process-wide per device and pooled. */
 bsw_t *bsw_create(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
                   const int8_t *mat, int8_t w_match, int8_t w_mismatch, int numThreads);
 void   bsw_destroy(bsw_t *h);
 
 /* replaces BandedPairWiseSW::getScores8 / getScores16 (same argument order).
- * Host pointers.  Writes score,tle,gtle,qle,gscore,max_off of pairArray[0..numPairs)
- * in place; synchronous.  getScores8 enforces the reference's 8-bit contract
- * (len1,len2 < 128); both tiers compute in packed signed 16-bit lanes, which is
- * value-identical on admitted pairs (SURVEY.md A.1 note 2). */
+ * Host pointers (pageable or pinned).  Writes score,tle,gtle,qle,gscore,max_off of
+ * pairArray[0..numPairs) in place; synchronous; re-entrant across handles.
+ * getScores8 enforces the reference's 8-bit contract (len1,len2 < 128); both tiers
+ * compute in packed signed 16-bit lanes, which is value-identical on admitted
+ * pairs (SURVEY.md A.1 note 2).
+ * Calls below BSW_CUDA_DIRECT_MIN pairs (default 131072) -- the size the reference's
+ * worker threads issue, R:docs-archive/WEEK1_BENCHMARK_RESULTS.md:88-95 -- are merged
+ * with the concurrent calls of the other host threads into one device batch by a
+ * per-device engine thread; the calling thread itself makes no CUDA call.  Larger
+ * calls are cut into chunks and DMA'd straight from the caller's buffers. */
 void bsw_getScores8 (bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
                      const uint8_t *seqBufQer, int32_t numPairs, uint16_t numThreads, int32_t w);
 void bsw_getScores16(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
@@ -99,6 +109,35 @@ void bsw_getScores16(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRe
  * device path, no length limit other than memory. */
 void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBufRef,
                                 const uint8_t *seqBufQer, int32_t numPairs, int nthreads, int32_t w);
+
+/* ---- sequence arenas (optional) ----------------------------------------------
+ * bwa-mem2 passes ONE pair of sequence buffers to the getScores8 and getScores16
+ * calls of a batch and to both attempts of the band-retry loop (bwamem.cpp,
+ * mem_chain2aln_across_reads_V2).  Declaring them lets the large-call path upload
+ * them once: between bsw_arena_begin and bsw_arena_end every call on this handle
+ * whose buffers lie inside [seqBufRef, +refBytes) / [seqBufQer, +qerBytes) reads the
+ * device copy made by bsw_arena_begin (asynchronous upload) and sends only its
+ * SeqPair records.  The caller must not modify the arenas in between.  Small
+ * (staged) calls ignore the declaration. */
+void bsw_arena_begin(bsw_t *h, const uint8_t *seqBufRef, size_t refBytes, const uint8_t *seqBufQer, size_t qerBytes);
+void bsw_arena_end(bsw_t *h);
+
+/* ---- resident reference (no reference counterpart) -----------
+ * The host pipeline copies every target slice out of the 2-bit packed reference
+ * into seqBufRef (bns_fetch_seq / bns_get_seq) only to send it to the callee.
+ * bsw_ref_upload keeps the packed reference (bwa's .pac layout: base x in byte
+ * x >> 2, bits ((~x & 3) << 1), l_pac bases) on every device of BSW_CUDA_DEVICES;
+ * bsw_getScoresRef then takes, instead of target bases, one coordinate per pair in
+ * bwa's doubled coordinate system (0 <= x < l_pac forward strand, l_pac <= x < 2 l_pac
+ * reverse complement): rpos[i] >= 0 -> target[k] = base(rpos[i] + k) (right
+ * extensions); rpos[i] < 0 -> target[k] = base(~rpos[i] - k) (the reversed slices of
+ * left extensions).  pairArray[i].idr is ignored and preserved; everything else
+ * as bsw_getScores16 (no 8-bit length contract). */
+typedef struct bsw_ref bsw_ref_t;
+bsw_ref_t *bsw_ref_upload(const uint8_t *pac, int64_t l_pac);
+void       bsw_ref_free(bsw_ref_t *r);
+void bsw_getScoresRef(bsw_t *h, bsw_seqpair_t *pairArray, const bsw_ref_t *ref, const int64_t *rpos,
+                      const uint8_t *seqBufQer, int32_t numPairs, int32_t w);
 
 /* ---- kswv ------------------------------------------------------------------
  * replaces kswv::kswv(o_del,e_del,o_ins,e_ins,w_match,w_mismatch,numThreads,
@@ -182,6 +221,21 @@ void bsw_set_cell_counting(bsw_t *h, int on);
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out);
 void kswv_reset_stats(kswv_t *h);
 void kswv_set_timing(kswv_t *h, int on);
+/* pair count from which a host-pointer call takes the large-call path (default BSW_CUDA_DIRECT_MIN = 131072) */
+void bsw_set_direct_min(bsw_t *h, int pairs);
+void kswv_set_direct_min(kswv_t *h, int pairs);
+
+/* counters of the staged-call engine of one device (process-wide) */
+typedef struct bsw_engine_stats {
+    int64_t batches;          /* device batches submitted                              */
+    int64_t pairs;            /* pairs in them                                         */
+    int64_t calls;            /* boundary calls (or slot-sized parts of calls) merged  */
+    int64_t kernel_launches;
+    int64_t h2d_bytes, d2h_bytes;
+    int64_t max_batch_pairs;
+} bsw_engine_stats_t;
+void bsw_engine_get_stats(int device, bsw_engine_stats_t *out);
+void bsw_engine_reset_stats(int device);
 
 /* Measures the sustained issue rate of independent packed-16-bit DPX
  * instructions (VIMNMX3.S16x2 / VIADDMNMX.S16x2) on `device`: the roofline

@@ -46,19 +46,19 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
         int qm = A.len2 > B.len2 ? A.len2 : B.len2;
         std::vector<uint32_t> he(qm + 8); std::vector<uint16_t> qs(qm + 8);
         const bool sym = c.oe_del == c.oe_ins;
-        if (count_cells) { if (sym) bsw_packed_thread<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob);
-                           else bsw_packed_thread<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), oa, ob); }
-        else {
-            // the library's prep_kernel routes pairs whose query holds an N (or an invalid base) to the QN = true variant
+        {
+            // the library's prep_kernel routes pairs whose query holds an N (or an invalid base) to the QN = true variant;
+            // the cell-counting variant always runs QN = true (bsw_api.cu launch_bsw_dp)
             uint32_t lut5[5]; for (int t = 0; t < 5; ++t) lut5[t] = bsw_lutrow(((uint32_t)(-c.b) & 0xffu) * 0x01010101u, ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu, lut_hi(c), t * 8u);
             bool qn = false;
             for (int j = 0; j < A.len2; ++j) qn |= qer[A.idq + j] > 3;
             for (int j = 0; ib >= 0 && j < B.len2; ++j) qn |= qer[B.idq + j] > 3;
-            if (force_qn) qn = true;
-            if (sym) { if (qn) bsw_packed_thread2<1, true, true>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob);
-                       else bsw_packed_thread2<1, true, false>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob); }
-            else { if (qn) bsw_packed_thread2<1, false, true>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob);
-                   else bsw_packed_thread2<1, false, false>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob); }
+            if (force_qn || count_cells) qn = true;
+#define EMU_RUN(SYM, QN, COUNT) bsw_packed_thread2<1, SYM, QN, COUNT>(c, w, A, B, ref, qer, he.data(), qs.data(), lut5, oa, ob)
+            if (count_cells) { if (sym) EMU_RUN(true, true, true); else EMU_RUN(false, true, true); }
+            else if (sym) { if (qn) EMU_RUN(true, true, false); else EMU_RUN(true, false, false); }
+            else { if (qn) EMU_RUN(false, true, false); else EMU_RUN(false, false, false); }
+#undef EMU_RUN
         }
         put(pairs[ia], oa); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { put(pairs[ib], ob); if (cells_out) cells_out[ib] = ob.cells; }
@@ -96,8 +96,8 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         else B = { 0, 0, 0, 0, 0, 0 };
         int qm = A.len2 > B.len2 ? A.len2 : B.len2, tm = A.len1 > B.len1 ? A.len1 : B.len1;
         std::vector<uint32_t> he(qm + 2); std::vector<uint16_t> qs(qm + 2), rm(tm + 2);
-        if (c.oe_del == c.oe_ins) kswv_packed_thread<1, true>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
-        else kswv_packed_thread<1, false>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
+        // the library always launches kswv_packed_kernel<false> (bsw_api.cu launch_kswv_dp): that is what runs here
+        kswv_packed_thread<1, false>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
         kput(aln, pairs[ia], ia, oa, phase); if (cells_out) cells_out[ia] = oa.cells;
         if (ib >= 0) { kput(aln, pairs[ib], ib, ob, phase); if (cells_out) cells_out[ib] = ob.cells; }
     }

@@ -97,3 +97,14 @@ def test_kswv_overflow_and_tandem(ora):
     P, r, q = ora.gen_random(1000, 0, 40, 0, 80, sim=0.7, p_n=0.05, seed=3)
     P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 5
     _check_kswv(ora, P, r, q, 1)
+
+
+def test_bsw_count_tiny_queries_cheap_gaps(ora):
+    """the cell-counting variant once failed for a short or unclean lane next to a longer query (tiny
+    queries, h0 up to 250, cheap or free gap opens, unsorted pairing).  The counting variant is now the same row loop
+    (bsw_core2.cuh, COUNT) and must agree on results AND cells."""
+    for seed, (q1, t1) in enumerate(((12, 130), (5, 40), (12, 12))):
+        P, r, q = ora.gen_random(1200, 1, q1, 1, t1, h0min=1, h0max=250, sim=0.7, p_n=0.02, seed=100 + seed)
+        _check_bsw(ora, P, r, q, w=100, a=3, b=5, o_del=2, e_del=2, o_ins=3, e_ins=1)
+        _check_bsw(ora, P, r, q, w=2, o_del=0, o_ins=0)
+        _check_bsw(ora, P, r, q, w=100, zdrop=0, o_del=0, e_del=1, o_ins=0, e_ins=3, a=2, b=1)
