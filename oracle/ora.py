@@ -227,3 +227,91 @@ def kswv_phase1_inputs(pairs, ref, qer, aln, a=1):
     p1["h0"] = KSW_XSTOP | aln["score"][idx]
     p1["seqid"], p1["regid"] = idx, idx
     return p1, ref1, qer1
+
+
+# --------------------------------------------------------------------- caller protocol on the oracle
+
+def protocol_side(pairs, ref, qer, params, w=100, tries=2, nthreads=8, runner=None):
+    """One side of mem_chain2aln_across_reads_V2's band loop: attempt 0 with band w on all pairs, then (MAX_BAND_TRY = 2)
+    the pairs with score != score before the attempt and max_off >= (w >> 1) + (w >> 2) again with 2w.  `runner(sub, w)`
+    computes a sub-array in place (default: the oracle).  Returns (results, pairs submitted over all attempts, cells)."""
+    out = pairs.copy()
+    submitted, cells = 0, 0
+    prev = None
+    for attempt in range(tries):
+        wa = w << attempt
+        if attempt == 0:
+            todo = np.arange(len(out))
+        else:
+            wp = w << (attempt - 1)
+            todo = np.nonzero((out["score"] != prev) & (out["max_off"] >= (wp >> 1) + (wp >> 2)))[0]
+            if len(todo) == 0:
+                break
+        prev = out["score"].copy()
+        sub = np.ascontiguousarray(out[todo])
+        if runner is None:
+            cells += bsw_batch(sub, ref, qer, params, wa, nthreads)
+        else:
+            runner(sub, wa)
+        out[todo] = sub
+        submitted += len(todo)
+    return out, submitted, cells
+
+
+def kswv_align2_batch(pairs, ref, qer, params, nthreads=8):
+    """mem_sam_pe_batch's sequence on the oracle: phase 0 by precision, hand-off, phase 1.  Returns (aln, cells)."""
+    aln = np.zeros(len(pairs), KSWR)
+    is8 = (pairs["h0"] & KSW_XBYTE) != 0
+    cells = 0
+    for sel, flag in ((np.nonzero(is8)[0], 1), (np.nonzero(~is8)[0], 0)):
+        if len(sel) == 0:
+            continue
+        sub = np.ascontiguousarray(pairs[sel]); a = np.zeros(len(sel), KSWR)
+        cells += kswv_batch(sub, ref, qer, a, params, flag, 0, nthreads)
+        p1, r1, q1 = kswv_phase1_inputs(sub, ref, qer, a)
+        if len(p1):
+            cells += kswv_batch(p1, r1, q1, a, params, flag, 1, nthreads)
+        aln[sel] = a
+    return aln, cells
+
+
+STREAM_MAGIC = 0x35434d4145525453
+
+
+def write_stream_workload(path, mode, L, R, lref, lqer, rref, rqer, ltask, rtask):
+    """Binary workload of tools/stream_c5 (mode 0: BSW left/right extension tasks, 1: kswv tasks in L)."""
+    nT = len(ltask) - 1
+    hdr = np.array([STREAM_MAGIC, mode, len(L), len(R), nT, len(lref), len(lqer), len(rref), len(rqer)], dtype=np.int64)
+    with open(path, "wb") as f:
+        for a in (hdr, np.asarray(ltask, np.int64), np.asarray(rtask, np.int64), L, R, lref, lqer, rref, rqer):
+            f.write(np.ascontiguousarray(a).tobytes())
+
+
+def task_bounds(seqid, n_reads, task_reads):
+    """Pair-index boundaries of the tasks of `task_reads` consecutive reads (pairs are in read order)."""
+    edges = list(range(0, n_reads, task_reads)) + [n_reads]
+    return np.searchsorted(seqid, edges, side="left").astype(np.int64)
+
+
+# --------------------------------------------------------------------- reference-based targets (SURVEY.md 8(f).2)
+
+def pac_pack(bases):
+    """bwa .pac layout: base x in byte x >> 2, bits ((~x & 3) << 1)."""
+    b = np.asarray(bases, dtype=np.uint8)
+    pad = (-len(b)) % 4
+    if pad:
+        b = np.concatenate([b, np.zeros(pad, np.uint8)])
+    q = b.reshape(-1, 4)
+    return ((q[:, 0] << 6) | (q[:, 1] << 4) | (q[:, 2] << 2) | q[:, 3]).astype(np.uint8)
+
+
+def ref_slice(fwd, rpos, length):
+    """Target bases of one pair from the forward strand `fwd` (values 0..3) in bwa's doubled coordinates:
+    rpos >= 0 reads upwards from rpos, rpos < 0 downwards from ~rpos; x >= l_pac is the reverse complement."""
+    l_pac = len(fwd)
+    k = np.arange(length, dtype=np.int64)
+    x = (~rpos - k) if rpos < 0 else (rpos + k)
+    rc = x >= l_pac
+    f = np.where(rc, 2 * l_pac - 1 - x, x)
+    b = fwd[f]
+    return np.where(rc, 3 - b, b).astype(np.uint8)

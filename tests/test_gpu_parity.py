@@ -12,17 +12,25 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.fixture(scope="module")
-def sw(bsw):
+# Host-pointer calls take one of two routes (bsw_api.cu): below BSW_CUDA_DIRECT_MIN pairs the staged engine (merged
+# batches, compact records), above it the chunked DMA path.  Every test that goes through these fixtures runs on both.
+@pytest.fixture(scope="module", params=["staged", "direct"])
+def sw(bsw, request):
     assert bsw.device_count() > 0, "no CUDA device: the product has no CPU fallback"
     obj = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    if request.param == "direct":
+        obj.set_direct_min(0)
+    obj.route = request.param
     yield obj
     obj.close()
 
 
-@pytest.fixture(scope="module")
-def ks(bsw):
+@pytest.fixture(scope="module", params=["staged", "direct"])
+def ks(bsw, request):
     obj = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    if request.param == "direct":
+        obj.set_direct_min(0)
+    obj.route = request.param
     yield obj
     obj.close()
 
@@ -226,7 +234,8 @@ def test_kswv_c4(ora, ks, bsw):
         ks.reset_stats()
         f(P, r, q, ag, len(P), 1, 0)
         assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
-        assert ks.stats()["cells"] == int(cells.sum())
+        if ks.route == "direct":                         # the handle's cell counter covers the direct / resident routes
+            assert ks.stats()["cells"] == int(cells.sum())
         p1, r1, q1 = ora.kswv_phase1_inputs(P, r, q, ao)
         ora.kswv_batch(p1, r1, q1, ao, prm, is8, 1, 8)
         f(p1, r1, q1, ag, len(p1), 1, 1)
@@ -341,32 +350,6 @@ def test_device_side_caller_protocol(ora, sw, bsw, w, div, tries):
     _assert_same(Ro, Rg)
 
 
-@pytest.mark.parametrize("threads", [1, 5])
-def test_gathered_upload_of_host_calls(ora, bsw, monkeypatch, threads):
-    """Host-pointer calls with BSW_CUDA_GATHER_THREADS: the bases the pairs name are gathered into pinned staging by
-    helper threads and uploaded densely (the two tier calls share ONE sequence arena, so a byte-range upload carries the
-    other tier's bases too).  Same results, caller's idr / idq untouched, fewer H2D bytes."""
-    (L, lr, lq), _ = common.bsw_c1(30000, seed=0x6A)
-    o, _ = _oracle_bsw(ora, L, lr, lq)
-    tiers = ora.classify(L)
-    res = {}
-    for mode in (0, threads):
-        monkeypatch.setenv("BSW_CUDA_GATHER_THREADS", str(mode))
-        monkeypatch.setenv("BSW_CUDA_CHUNK_PAIRS", "4096")
-        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
-        g = L.copy()
-        for tier, fn in ((0, h.getScores8), (1, h.getScores16)):
-            sel = np.nonzero(tiers == tier)[0]
-            part = np.ascontiguousarray(g[sel])
-            fn(part, lr, lq, len(part), 1, 100)
-            g[sel] = part
-        res[mode] = (g, h.stats()["h2d_bytes"])
-        h.close()
-    _assert_same(o, res[0][0])
-    _assert_same(o, res[threads][0])
-    assert res[threads][1] < res[0][1]
-
-
 def test_properties_at_scale(ora, sw, bsw):
     """Size-independent properties on 1M C2-shaped pairs: idempotence, order independence
     (results do not depend on where a pair sits in the batch), all-match closed form."""
@@ -450,17 +433,256 @@ def test_concurrent_handles_from_host_threads(ora, bsw):
 
 
 def test_kswv_call_in_parts(ora, bsw, monkeypatch):
-    """Large kswv calls are served in parts (bounded row-maximum scratch): same answers, phase 0 and 1."""
-    monkeypatch.setenv("BSW_CUDA_KSWV_PART", "3000")
+    """Large kswv calls are served in chunks and, when the row-maximum scratch would exceed its budget, in several
+    launches per bin: same answers, phase 0 and 1."""
+    monkeypatch.setenv("BSW_CUDA_KSWV_CHUNK", "3000")
+    monkeypatch.setenv("BSW_CUDA_ROWMAX_MB", "1")            # floor is 16 MB: 500 rows x 2 B -> <= 16 k slots per launch
     prm = ora.make_params()
-    K, kr, kq = ora.gen_kswv(10000, seed=0x77)
+    K, kr, kq = ora.gen_kswv(40000, seed=0x77)
     ao = np.zeros(len(K), ora.KSWR); ag = np.zeros(len(K), bsw.KSWR)
     ora.kswv_batch(K, kr, kq, ao, prm, 1, 0, 8)
-    ks2 = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
-    ks2.getScores8(K, kr, kq, ag, len(K), 1, 0)
-    assert (ao == ag).all()
-    p1, r1, q1 = ora.kswv_phase1_inputs(K, kr, kq, ao)
-    ora.kswv_batch(p1, r1, q1, ao, prm, 1, 1, 8)
-    ks2.getScores8(p1, r1, q1, ag, len(p1), 1, 1)
-    ks2.close()
-    assert (ao == ag).all()
+    for chunk in ("3000", "1000000"):
+        monkeypatch.setenv("BSW_CUDA_KSWV_CHUNK", chunk)
+        ks2 = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+        ks2.set_direct_min(0)
+        ag[:] = 0
+        ks2.getScores8(K, kr, kq, ag, len(K), 1, 0)
+        assert (ao == ag).all()
+        a1 = ao.copy()
+        p1, r1, q1 = ora.kswv_phase1_inputs(K, kr, kq, a1)
+        ora.kswv_batch(p1, r1, q1, a1, prm, 1, 1, 8)
+        ks2.getScores8(p1, r1, q1, ag, len(p1), 1, 1)
+        ks2.close()
+        assert (a1 == ag).all()
+
+
+def test_staged_calls_from_many_threads(ora, bsw):
+    """The drop-in pattern (SURVEY.md 8b "Threading"): 12 host threads, each with per-task objects, small calls of
+    mixed kinds at once -- BSW with two bands and two scoring sets, kswv phase 0 and 1 -- merged into shared device
+    batches by the engine.  Every result equals the oracle's, whatever shared its batch."""
+    import threading
+    rng = np.random.default_rng(5)
+    jobs = []
+    for k in range(12):
+        kind = k % 4
+        if kind in (0, 1):
+            w = 100 if kind == 0 else 11
+            d = ora.gen_bsw(3000 + 211 * k, seed=0x900 + k)
+            parts = []
+            for side in ("left", "right"):
+                P, r, q = d[side]
+                o, _, _ = ora.protocol_side(P, r, q, ora.make_params(), w, 1, 4)
+                parts.append((P, r, q, o))
+            jobs.append(("bsw", (6, 1, 6, 1, 100, 5, 1, 4), w, parts))
+        elif kind == 2:
+            P, r, q = ora.gen_random(2500, 1, 127, 1, 200, h0min=1, h0max=60, sim=0.85, p_n=0.02, seed=40 + k)
+            prm = ora.make_params(o_del=4, e_del=2, o_ins=7, e_ins=1, zdrop=30, end_bonus=0, a=2, b=3)
+            o = P.copy(); ora.bsw_batch(o, r, q, prm, 37, 4)
+            jobs.append(("bsw", (4, 2, 7, 1, 30, 0, 2, 3), 37, [(P, r, q, o)]))
+        else:
+            K, kr, kq = ora.gen_kswv(2500, seed=0x50 + k)
+            ao, _ = ora.kswv_align2_batch(K, kr, kq, ora.make_params(), 4)
+            jobs.append(("kswv", None, 0, [(K, kr, kq, ao)]))
+    out = [None] * len(jobs)
+
+    def work(k):
+        kind, sc, w, parts = jobs[k]
+        res = []
+        for rep in range(3):                                   # per-task objects, repeated
+            res = []
+            if kind == "bsw":
+                for P, r, q, _ in parts:
+                    h = bsw.BandedPairWiseSW(sc[0], sc[1], sc[2], sc[3], sc[4], sc[5], None, sc[6], sc[7], 1)
+                    g = P.copy()
+                    step = 700 + 13 * k                        # several calls per object, ragged sizes
+                    for a0 in range(0, len(g), step):
+                        part = np.ascontiguousarray(g[a0:a0 + step])
+                        h.getScores16(part, r, q, len(part), 1, w)
+                        g[a0:a0 + step] = part
+                    h.close()
+                    res.append(g)
+            else:
+                K, kr, kq, _ = parts[0]
+                h = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+                ag = np.zeros(len(K), bsw.KSWR)
+                h.getScores8(K, kr, kq, ag, len(K), 1, 0)
+                p1, r1, q1 = ora.kswv_phase1_inputs(K, kr, kq, ag.view(ora.KSWR))
+                h.getScores8(p1, r1, q1, ag, len(p1), 1, 1)
+                h.close()
+                res.append(ag)
+        out[k] = res
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(len(jobs))]
+    for x in th: x.start()
+    for x in th: x.join()
+    for k, (kind, _, _, parts) in enumerate(jobs):
+        for (P, r, q, o), g in zip(parts, out[k]):
+            if kind == "bsw":
+                _assert_same(o, g)
+            else:
+                assert (o == g).all()
+    es = bsw.engine_stats(0)
+    assert es["batches"] > 0 and es["pairs"] > 0
+    assert es["calls"] >= es["batches"]                       # calls were merged (or at worst one per batch)
+
+
+def test_handle_creation_is_cheap(bsw):
+    """The reference builds its objects per task: creating + destroying a handle must not
+    create streams or pinned memory (0.57 s per handle in round 1)."""
+    import time
+    h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1); h.close()          # builds the per-device runtime
+    t0 = time.perf_counter()
+    for _ in range(200):
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1); h.close()
+        k = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256); k.close()
+    us = (time.perf_counter() - t0) / 400 * 1e6
+    assert us < 200, us
+
+
+def test_arena_upload_once(ora, bsw):
+    """bsw_arena_begin / bsw_arena_end: the tier-8 and tier-16 calls of a batch share one pair of sequence arenas
+    (bwamem.cpp passes the same buffers to both); declared, they go up once.  Same results, fewer H2D bytes."""
+    (L, lr, lq), _ = common.bsw_c1(30000, seed=0x6A)
+    o, _ = _oracle_bsw(ora, L, lr, lq)
+    tiers = ora.classify(L)
+    res = {}
+    for arena in (False, True):
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        h.set_direct_min(0)
+        g = L.copy()
+        for rep in range(2):                                  # a second batch on the same handle re-declares the arenas
+            if arena:
+                h.arena_begin(lr, lq)
+            for tier, fn in ((0, h.getScores8), (1, h.getScores16)):
+                sel = np.nonzero(tiers == tier)[0]
+                part = np.ascontiguousarray(g[sel])
+                fn(part, lr, lq, len(part), 1, 100)
+                g[sel] = part
+            if arena:
+                h.arena_end()
+        res[arena] = (g, h.stats()["h2d_bytes"])
+        h.close()
+    _assert_same(o, res[False][0])
+    _assert_same(o, res[True][0])
+    assert res[True][1] < 0.75 * res[False][1]
+
+
+def _ref_workload(ora, n, seed, l_pac=200000):
+    """Pairs whose targets are slices of a reference: both strands, both read directions."""
+    rng = np.random.default_rng(seed)
+    fwd = rng.integers(0, 4, l_pac).astype(np.uint8)
+    pairs = np.zeros(n, ora.SEQPAIR); rpos = np.zeros(n, np.int64)
+    refs, qers = [], []
+    ro = qo = 0
+    for i in range(n):
+        ql = int(rng.integers(1, 131)); tl = ql + int(rng.integers(0, 60))
+        down = bool(rng.integers(0, 2))
+        x0 = int(rng.integers(tl, 2 * l_pac - tl))
+        if (x0 < l_pac) != ((x0 - tl if down else x0 + tl) < l_pac):      # keep a slice on one strand, like bns_fetch_seq
+            x0 = int(rng.integers(tl, l_pac - tl))
+        rp = ~x0 if down else x0
+        t = ora.ref_slice(fwd, rp, tl)
+        q = t[:ql].copy()
+        m = rng.random(ql) < 0.04
+        q[m] = (q[m] + rng.integers(1, 4, m.sum())) % 4
+        if rng.random() < 0.05:
+            q[rng.integers(0, ql)] = 4
+        pairs[i]["idr"], pairs[i]["idq"], pairs[i]["id"] = ro, qo, i
+        pairs[i]["len1"], pairs[i]["len2"], pairs[i]["h0"] = tl, ql, int(rng.integers(1, 100))
+        rpos[i] = rp
+        refs.append(t); qers.append(q); ro += tl; qo += ql
+    ref = np.concatenate(refs + [np.zeros(64, np.uint8)]); qer = np.concatenate(qers + [np.zeros(64, np.uint8)])
+    return fwd, pairs, rpos, ref, qer
+
+
+def test_reference_resident_targets(ora, bsw, monkeypatch):
+    """bsw_ref_upload + bsw_getScoresRef: targets fetched on the device from the 2-bit reference at
+    (rpos, len1, direction, strand) == the same pairs with the target bases sent as bytes == the oracle."""
+    monkeypatch.setenv("BSW_CUDA_CHUNK_PAIRS", "2048")        # several chunks, the sampled size estimate at work
+    fwd, P, rpos, ref, qer = _ref_workload(ora, 9000, 77)
+    o, _ = _oracle_bsw(ora, P, ref, qer)
+    R = bsw.Reference(bsw.pack_pac(fwd), len(fwd))
+    h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    g = P.copy()
+    g["idr"] = 123456789                                      # ignored by the call, and preserved
+    h.getScoresRef(g, R, rpos, qer, len(g), 100)
+    assert (g["idr"] == 123456789).all()
+    g["idr"] = P["idr"]
+    _assert_same(o, g)
+    st = h.stats()
+    assert st["h2d_bytes"] < len(P) * 56 + len(qer) + len(P) * 8 + 4096       # no target bases went up
+    h.close(); R.close()
+
+
+def test_shim_classes_cpp_harness(ora, bsw, tmp_path):
+    """bandedSWA_b200.h compiled into tools/bin/stream_c5 (g++, links libbswcuda.so): worker threads with per-task
+    BandedPairWiseSW / kswv objects replay the caller protocol of both call sites; all pairs equal the oracle."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(HERE), "tools", "bin", "stream_c5")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(os.path.dirname(HERE), "tools"), "bin/stream_c5"])
+    prm = ora.make_params()
+    n_reads = 12000
+    d = ora.gen_bsw(n_reads, seed=0xC5)
+    L, lr, lq = d["left"]; R, rr, rq = d["right"]
+    Lo, _, _ = ora.protocol_side(L, lr, lq, prm, 100, 2, 8)
+    Rin = R.copy(); ora.chain_h0(Lo, Rin)
+    Ro, _, _ = ora.protocol_side(Rin, rr, rq, prm, 100, 2, 8)
+    w_in, w_out = str(tmp_path / "w.bin"), str(tmp_path / "r.bin")
+    ora.write_stream_workload(w_in, 0, L, R, lr, lq, rr, rq, ora.task_bounds(L["seqid"], n_reads, 512),
+                              ora.task_bounds(R["seqid"], n_reads, 512))
+    for pinned in (0, 1):
+        r = subprocess.run([exe, "--in", w_in, "--out", w_out, "--threads", "6", "--pinned", str(pinned)],
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr
+        info = json.loads(r.stdout.strip().splitlines()[-1])
+        assert info["handles_created"] >= 2 * ((n_reads + 511) // 512)
+        raw = np.fromfile(w_out, dtype=bsw.SEQPAIR)
+        _assert_same(Lo, raw[:len(L)])
+        Ro2 = Ro.copy(); Ro2["h0"] = Rin["h0"]
+        _assert_same(Ro2, raw[len(L):])
+    K, kr, kq = ora.gen_kswv(9000, seed=0xC7)
+    K16, kr16, kq16 = ora.gen_kswv(1000, qlen=250, tmin=400, tmax=700, seed=0xC8)
+    Kall, krall, kqall = common.concat_workloads([(K, kr, kq), (K16, kr16, kq16)])
+    perm = np.random.default_rng(3).permutation(len(Kall)); Kall = np.ascontiguousarray(Kall[perm])
+    ao, _ = ora.kswv_align2_batch(Kall, krall, kqall, prm, 8)
+    tb = np.arange(0, len(Kall) + 2499, 2500).clip(max=len(Kall)).astype(np.int64)
+    ora.write_stream_workload(w_in, 1, Kall, Kall[:0], krall, kqall, krall[:0], kqall[:0], tb, np.zeros(len(tb), np.int64))
+    r = subprocess.run([exe, "--in", w_in, "--out", w_out, "--threads", "4"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    ag = np.fromfile(w_out, dtype=bsw.KSWR)
+    assert (ao == ag.view(ora.KSWR)).all()
+
+
+def test_multi_device_handle(ora, bsw, monkeypatch):
+    """In-process multi-GPU (BSW_CUDA_DEVICES=0,1,...): the route an unchanged single-process bwa-mem2 would use.  Large
+    calls deal their chunks round-robin, small calls go to the least-loaded engine; results equal the oracle's."""
+    import threading
+    nd = bsw.device_count()
+    if nd < 2:
+        pytest.skip("needs 2 or more GPUs")
+    monkeypatch.setenv("BSW_CUDA_DEVICES", ",".join(str(i) for i in range(nd)))
+    monkeypatch.setenv("BSW_CUDA_CHUNK_PAIRS", "8192")
+    (L, lr, lq), _ = common.bsw_c1(60000, seed=0x2D)
+    o, _ = _oracle_bsw(ora, L, lr, lq)
+    h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    h.set_direct_min(0)
+    g = L.copy(); h.getScores16(g, lr, lq, len(g), 1, 100)
+    _assert_same(o, g)
+    h.close()
+    out = [None] * 8
+
+    def work(k):
+        hh = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        gg = np.ascontiguousarray(L[k::8])
+        for a0 in range(0, len(gg), 1500):
+            part = np.ascontiguousarray(gg[a0:a0 + 1500]); hh.getScores16(part, lr, lq, len(part), 1, 100); gg[a0:a0 + 1500] = part
+        hh.close(); out[k] = gg
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(8)]
+    for x in th: x.start()
+    for x in th: x.join()
+    for k in range(8):
+        _assert_same(o[k::8], out[k])
+    used = sum(1 for dv in range(nd) if bsw.engine_stats(dv)["batches"] > 0)
+    assert used >= 2
