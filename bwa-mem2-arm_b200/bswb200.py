@@ -31,13 +31,13 @@ EXPORTS = (
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
     "bsw_arena_begin", "bsw_arena_end", "bsw_ref_upload", "bsw_ref_free", "bsw_getScoresRef",
-    "bsw_set_direct_min", "kswv_set_direct_min", "bsw_engine_get_stats", "bsw_engine_reset_stats",
+    "bsw_set_direct_min", "kswv_set_direct_min", "bsw_set_wide_max", "bsw_engine_get_stats", "bsw_engine_reset_stats",
 )
 
 
 class Stats(C.Structure):
     _fields_ = [("calls", C.c_int64), ("pairs", C.c_int64), ("pairs_packed", C.c_int64),
-                ("pairs_general", C.c_int64), ("cells", C.c_int64), ("kernel_launches", C.c_int64),
+                ("pairs_general", C.c_int64), ("pairs_wide", C.c_int64), ("cells", C.c_int64), ("kernel_launches", C.c_int64),
                 ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("kernel_ms", C.c_double)]
 
     def asdict(self):
@@ -46,7 +46,8 @@ class Stats(C.Structure):
 
 class EngineStats(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("batches", "pairs", "calls", "kernel_launches", "h2d_bytes", "d2h_bytes",
-                                          "max_batch_pairs")]
+                                          "max_batch_pairs", "wide_batches", "scan_ns", "reserve_ns", "pack_ns",
+                                          "wait_ns", "unpack_ns", "packers_ns", "submit_ns", "flight_ns")]
 
     def asdict(self):
         return {f: getattr(self, f) for f, _ in self._fields_}
@@ -103,7 +104,7 @@ def lib():
     L.bsw_ref_free.argtypes = [vp]
     L.bsw_getScoresRef.restype = None
     L.bsw_getScoresRef.argtypes = [vp, vp, vp, vp, vp, i32, i32]
-    for f in (L.bsw_set_direct_min, L.kswv_set_direct_min):
+    for f in (L.bsw_set_direct_min, L.kswv_set_direct_min, L.bsw_set_wide_max):
         f.argtypes = [vp, C.c_int]
     L.bsw_engine_get_stats.argtypes = [C.c_int, C.POINTER(EngineStats)]
     L.bsw_engine_reset_stats.argtypes = [C.c_int]
@@ -196,6 +197,9 @@ class BandedPairWiseSW:
 
     def set_direct_min(self, pairs):
         self._L.bsw_set_direct_min(self._h, int(pairs))
+
+    def set_wide_max(self, pairs):
+        self._L.bsw_set_wide_max(self._h, int(pairs))
 
     def stats(self):
         s = Stats()

@@ -199,6 +199,7 @@ struct Core {
     int chunk_pairs = 1 << 19;
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
+    int wide_max = 16384;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
     int mode = MODE_BSW;
     /* arenas declared with bsw_arena_begin */
     const uint8_t *arena_ref_h = nullptr, *arena_qer_h = nullptr;
@@ -249,6 +250,7 @@ void core_init(Core &k, int mode)
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
+    k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 16384);
 }
 
 void core_destroy(Core &k)
@@ -295,7 +297,7 @@ void plan_enqueue(Core &k, Slot &x, const bsw_seqpair_t *d_pairs, const uint8_t 
     Plan *d_plan = (Plan *)x.plan.p;
     if (clear_plan) CK(cudaMemsetAsync(d_plan, 0, sizeof(Plan), s));     /* else: cleared before ref_expand_kernel reported into it */
     const int max_elems = BSW_NBINS * 16;
-    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, d_qer, n, k.c, k.mode, max_elems, tier8_check, rlo, rhi, qlo, qhi,
+    prep_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_pairs, d_qer, n, k.c, k.mode, max_elems, tier8_check, k.count_cells ? 0 : 1, rlo, rhi, qlo, qhi,
                                                  (uint32_t *)x.keys_a.p, (uint32_t *)x.idx_a.p, d_plan);
     CK(cudaGetLastError());
     CK(cub::DeviceRadixSort::SortPairsDescending(x.cubtmp.p, tmp_bytes, (uint32_t *)x.keys_a.p, (uint32_t *)x.keys_b.p,
@@ -351,18 +353,28 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
     int n_packed = 0;
     CK(cudaEventRecord(x.fork_ev, s));
     unsigned used = 0;
-    /* sorted order: pairs whose query holds an N first (key bit 25), then the others; each longest query first */
+    /* sorted order: pairs whose query holds an N first (key bit 25), then the others; each longest query first.
+     * Small calls (n <= BSW_CUDA_WIDE_MAX) are latency-bound in the thread-owns-two-pairs kernel (its longest pair
+     * sets the call's duration): their bins go to the lanes-per-pair kernel instead, like the wide-only pairs below. */
+    const bool sym = k.c.oe_del == k.c.oe_ins;
+    const bool small = n <= k.wide_max && !k.count_cells && wide_eligible(k.c, 0, 0, 1);
     for (int pass = 0; pass < 2; ++pass)
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
             const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
             if (cnt <= 0) continue;
+            if (small) {
+                launch_wide(wide_cfg_of_bin(qb), sym, io, d_ref, d_qer, sorted, n_packed, cnt, k.c, w, s);
+                CK(cudaGetLastError());
+                k.st.kernel_launches++;
+                n_packed += cnt;
+                continue;
+            }
             const int NE = qb * 16, grid = (cnt + 63) / 64;
             cudaStream_t bs = rt.lvl_stream[level_of[qb]][qb];
             if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             used |= 1u << qb;
             /* template flags: exact cell counting; symmetric gap sums (one packed add less per cell); general score
              * table for queries with an N (the counting variant always uses it) */
-            const bool sym = k.c.oe_del == k.c.oe_ins;
             auto kern = k.count_cells ? (sym ? bsw_packed_kernel<true, true, true> : bsw_packed_kernel<true, false, true>)
                       : pass == 0     ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
                                       : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
@@ -381,6 +393,16 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
             CK(cudaEventRecord(x.bin_ev[qb], bs));
             CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
         }
+    /* pairs only the 16-bit lanes-per-pair kernel admits: sorted after the packed ones, largest configuration first */
+    int n_wide = 0;
+    for (int cfg = BSW_WIDE_NCFG - 1; cfg >= 0; --cfg) {
+        const int cnt = pl->hist_w[cfg];
+        if (cnt <= 0) continue;
+        launch_wide(cfg, sym, io, d_ref, d_qer, sorted, n_packed + n_wide, cnt, k.c, w, s);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+        n_wide += cnt;
+    }
     if (pl->n_general > 0) {
         /* bounded scratch: at most ~1 GiB of eh rows per launch */
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2);
@@ -388,7 +410,7 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
         sl.scratch.reserve((size_t)chunk * per_pair);
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, sorted, n_packed + first, cnt,
+            bsw_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, sorted, n_packed + n_wide + first, cnt,
                                                               k.c, w, (int2 *)sl.scratch.p, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -408,7 +430,8 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
             fprintf(stderr, "\n");
         }
     }
-    k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
+    k.st.pairs += n; k.st.pairs_general += pl->n_general;
+    if (small) k.st.pairs_wide += n_packed + n_wide; else { k.st.pairs_packed += n_packed; k.st.pairs_wide += n_wide; }
 }
 
 void launch_bsw(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
@@ -745,7 +768,10 @@ inline int classify(const Core &k, const bsw_seqpair_t &p, const uint8_t *qer)
 {
     const bool ok = k.mode == MODE_BSW ? packed_eligible(k.c, p.len1, p.len2, p.h0) : kswv_packed_eligible(k.c, p.len1, p.len2);
     const int qb = (p.len2 + (k.mode == MODE_BSW ? BSW_SWEEP_SLACK : 1) + 15) >> 4;
-    if (!ok || qb > BSW_NBINS) return CLS_GENERAL;
+    if (!ok || qb > BSW_NBINS) {
+        if (k.mode == MODE_BSW && wide_eligible(k.c, p.len1, p.len2, p.h0)) return CLS_WIDE0 + wide_cfg_for(p.len2);
+        return CLS_GENERAL;
+    }
     if (k.mode == MODE_BSW && p.len2 > 0 && bytes_have_n(qer + p.idq, p.len2)) return BSW_NBINS + qb;
     return qb;
 }
@@ -755,11 +781,12 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
                  int tier8_check, int is8, int phase)
 {
     Engine &eng = k.rt(pick_engine(k)).eng();
-    const BatchKey key = make_key(k.mode, k.c, w, is8);
+    const BatchKey key = make_key(k.mode, k.c, w, is8, k.wide_max);
     std::vector<uint8_t> cls;
     int first = 0;
     while (first < n) {
         /* pass 1 over the part: contract, classes, byte sums */
+        const long long t0 = now_ns();
         int cnt[BSW_NCLASS]; memset(cnt, 0, sizeof cnt);
         long long bytes = 0; int m = 0, bad = 0, ml1p = 0, ml2g = 0, ml1g = 0;
         cls.clear();
@@ -776,11 +803,13 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
             const int c = classify(k, p, qer);
             cls.push_back((uint8_t)c); cnt[c]++;
             if (c == CLS_GENERAL) { ml2g = std::max(ml2g, p.len2); ml1g = std::max(ml1g, p.len1); }
-            else ml1p = std::max(ml1p, p.len1);
+            else if (c < CLS_GENERAL) ml1p = std::max(ml1p, p.len1);
         }
         if (bad) die_contract(bad);
+        const long long t1 = now_ns();
         Reservation r = eng.reserve(key, m, bytes, cnt, ml1p, ml2g, ml1g);
         StagedSlot &s = *r.slot;
+        const long long t2 = now_ns();
         /* pass 2: pack */
         {
             int *rec = reinterpret_cast<int *>(s.h_rec + (size_t)r.pair_base * 24);
@@ -799,7 +828,9 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
             }
         }
         eng.packed(r, m);
+        const long long t3 = now_ns();
         eng.wait_done(r);
+        const long long t4 = now_ns();
         /* results */
         if (k.mode == MODE_BSW) {
             const char *res = s.h_res + (size_t)r.pair_base * 24;
@@ -816,8 +847,18 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
             k.st.d2h_bytes += (long long)m * (long long)sizeof(bsw_kswr_t);
         }
         eng.release(r, m);
+        {
+            const long long t5 = now_ns();
+            EngineProf &pf = eng.prof;
+            pf.scan_ns += t1 - t0; pf.reserve_ns += t2 - t1; pf.pack_ns += t3 - t2; pf.wait_ns += t4 - t3; pf.unpack_ns += t5 - t4;
+        }
         k.st.h2d_bytes += (long long)m * 24 + bytes;
-        k.st.pairs += m; k.st.pairs_general += cnt[CLS_GENERAL]; k.st.pairs_packed += m - cnt[CLS_GENERAL];
+        k.st.pairs += m; k.st.pairs_general += cnt[CLS_GENERAL];
+        {   /* which kernel served the packed-eligible classes is the engine's choice per batch (engine stats); the handle
+             * books them as packed and the wide-only classes as wide */
+            int nw = 0; for (int cf = 0; cf < BSW_WIDE_NCFG; ++cf) nw += cnt[CLS_WIDE0 + cf];
+            k.st.pairs_wide += nw; k.st.pairs_packed += m - cnt[CLS_GENERAL] - nw;
+        }
         first += m;
     }
 }
@@ -1118,6 +1159,7 @@ void bsw_reset_stats(bsw_t *h) { stats_reset(h->k); }
 void bsw_set_timing(bsw_t *h, int on) { h->k.timing = on; }
 void bsw_set_cell_counting(bsw_t *h, int on) { h->k.count_cells = on; }
 void bsw_set_direct_min(bsw_t *h, int pairs) { h->k.direct_min = pairs; }
+void bsw_set_wide_max(bsw_t *h, int pairs) { h->k.wide_max = pairs; }
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
 void kswv_reset_stats(kswv_t *h) { stats_reset(h->k); }
 void kswv_set_timing(kswv_t *h, int on) { h->k.timing = on; }
@@ -1131,7 +1173,9 @@ void bsw_engine_get_stats(int device, bsw_engine_stats_t *out)
     if (!r || !r->engine) return;
     const EngineStats s = r->engine->stats();
     out->batches = s.batches; out->pairs = s.pairs; out->calls = s.calls; out->kernel_launches = s.launches;
-    out->h2d_bytes = s.h2d_bytes; out->d2h_bytes = s.d2h_bytes; out->max_batch_pairs = s.max_batch_pairs;
+    out->h2d_bytes = s.h2d_bytes; out->d2h_bytes = s.d2h_bytes; out->max_batch_pairs = s.max_batch_pairs; out->wide_batches = s.wide_batches;
+    out->scan_ns = s.scan_ns; out->reserve_ns = s.reserve_ns; out->pack_ns = s.pack_ns; out->wait_ns = s.wait_ns; out->unpack_ns = s.unpack_ns;
+    out->packers_ns = s.packers_ns; out->submit_ns = s.submit_ns; out->flight_ns = s.flight_ns;
 }
 void bsw_engine_reset_stats(int device)
 {

@@ -23,6 +23,7 @@
 #include "bsw_core.cuh"
 #include "bsw_core2.cuh"
 #include "kswv_core.cuh"
+#include "bsw_wide.cuh"
 
 namespace bswk {
 
@@ -35,6 +36,7 @@ namespace bswk {
 struct Plan {
     int hist[BSW_NBINS + 2];       /* [qb] = packed-admissible pairs whose rows need qb x 16 columns */
     int hist_n[BSW_NBINS + 2];     /* BSW: the subset of them whose query holds an N / invalid base (sorted first; counted here, not in hist) */
+    int hist_w[BSW_WIDE_NCFG + 1]; /* BSW: pairs only the lanes-per-pair kernel admits (16-bit state), by configuration */
     int n_general;                 /* pairs routed to the general kernel */
     int max_len1;                  /* over all pairs                      */
     int max_len1_packed;           /* over the pairs the packed kernels take (sizes kswv's row-maximum scratch) */
@@ -62,16 +64,19 @@ __device__ __forceinline__ bool query_has_n(const uint8_t *__restrict__ qer, lon
     return (acc & 0xfcfcfcfcu) != 0;
 }
 
-#define BSW_KEY_BITS 26         /* (has-N flag) << 25 | (len2 + 1) << 16 | (len1 / 2) << 8 | h0 */
+#define BSW_KEY_BITS 26         /* packed pairs: (has-N flag) << 25 | (len2 + 1) << 16 | (len1 / 2) << 8 | h0  (>= 0x10000);
+                                 * wide-only pairs: (configuration + 1) << 13 | len1 / 2  (< 0x10000); general pairs: 0 */
 
 __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ qer, int n, Const c, int mode,
-                            int max_elems, int tier8_check, long long rlo, long long rhi, long long qlo, long long qhi,
+                            int max_elems, int tier8_check, int allow_wide, long long rlo, long long rhi, long long qlo, long long qhi,
                             uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, Plan *plan)
 {
     __shared__ int s_hist[2 * (BSW_NBINS + 2)];
     __shared__ int s_misc[5];
+    __shared__ int s_wide[BSW_WIDE_NCFG];
     if (threadIdx.x < 2 * (BSW_NBINS + 2)) s_hist[threadIdx.x] = 0;
     if (threadIdx.x < 5) s_misc[threadIdx.x] = 0;
+    if (threadIdx.x < BSW_WIDE_NCFG) s_wide[threadIdx.x] = 0;
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -94,6 +99,12 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
             if (qn) key |= 1u << 25;
             atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
             atomicMax(&s_misc[4], len1);
+        } else if (mode == MODE_BSW && allow_wide && wide_eligible(c, len1, len2, h0)) {
+            /* too long or too high-scoring for the byte-packed rows: the 16-bit lanes-per-pair kernel takes it */
+            const int cfg = wide_cfg_for(len2);
+            const uint32_t l1 = (uint32_t)(len1 >> 1) > 8191u ? 8191u : (uint32_t)(len1 >> 1);
+            key = ((uint32_t)(cfg + 1) << 13) | l1;
+            atomicAdd(&s_wide[cfg], 1);
         } else {
             atomicAdd(&s_misc[0], 1);
             atomicMax(&s_misc[2], len2);
@@ -111,6 +122,7 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
     __syncthreads();
     if (threadIdx.x < 2 * (BSW_NBINS + 2) && s_hist[threadIdx.x])      /* hist and hist_n are adjacent in Plan */
         atomicAdd(&plan->hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (threadIdx.x < BSW_WIDE_NCFG && s_wide[threadIdx.x]) atomicAdd(&plan->hist_w[threadIdx.x], s_wide[threadIdx.x]);
     if (threadIdx.x == 0) {
         if (s_misc[0]) atomicAdd(&plan->n_general, s_misc[0]);
         atomicMax(&plan->max_len1, s_misc[1]);
@@ -234,6 +246,45 @@ bsw_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
         if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
     }
 }
+
+/* ------------------------------------------------------------------ 4c. BSW wide (lanes per pair, bsw_wide.cuh)
+ * G lanes per pair, 128 threads per block; pair of group g = sorted slot first + g. */
+template <int G, int R, bool SYM>
+__global__ void __launch_bounds__(128)
+bsw_wide_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                const uint32_t *__restrict__ sorted_idx, int first, int count, Const c, int w)
+{
+    const int gid = (blockIdx.x * 128 + threadIdx.x) / G, gl = threadIdx.x % G;
+    const int pi = gid < count ? (int)sorted_idx[first + gid] : -1;
+    const PairIn P = load_pair(io, pi);
+    PairOut o;
+    bsw_wide_lane<G, R, SYM>(c, w, P, ref, qer, gl, o);
+    if (pi >= 0 && gl == 0) store_bsw(io, pi, o);
+}
+
+/* launches the configuration `cfg` (bsw_wide.cuh wide_cfg_*) over sorted slots [first, first + count) */
+static inline void launch_wide(int cfg, bool sym, PairIO io, const uint8_t *ref, const uint8_t *qer, const uint32_t *sorted,
+                               int first, int count, const Const &c, int w, cudaStream_t s)
+{
+    if (count <= 0) return;
+    const int G = wide_cfg_lanes(cfg), per_block = 128 / G, grid = (count + per_block - 1) / per_block;
+#define BSW_WIDE_LAUNCH(GG, RR)                                                                             \
+    do {                                                                                                    \
+        if (sym) bsw_wide_kernel<GG, RR, true><<<grid, 128, 0, s>>>(io, ref, qer, sorted, first, count, c, w);   \
+        else bsw_wide_kernel<GG, RR, false><<<grid, 128, 0, s>>>(io, ref, qer, sorted, first, count, c, w);      \
+    } while (0)
+    switch (cfg) {
+    case 0: BSW_WIDE_LAUNCH(8, 5); break;
+    case 1: BSW_WIDE_LAUNCH(8, 9); break;
+    case 2: BSW_WIDE_LAUNCH(16, 9); break;
+    case 3: BSW_WIDE_LAUNCH(32, 9); break;
+    default: BSW_WIDE_LAUNCH(32, 16); break;
+    }
+#undef BSW_WIDE_LAUNCH
+}
+
+/* configuration that serves the packed bin qb (queries of up to qb * 16 - 4 bases) */
+static inline int wide_cfg_of_bin(int qb) { return wide_cfg_for(qb * 16 - BSW_SWEEP_SLACK); }
 
 /* ------------------------------------------------------------------ 5a. BSW general */
 __global__ void bsw_general_kernel(PairIO io, const uint8_t *__restrict__ ref,

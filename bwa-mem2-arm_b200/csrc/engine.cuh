@@ -51,20 +51,36 @@ struct BatchKey {
     Const c;
     int w;               /* BSW band */
     int is8;             /* kswv precision rule */
+    int wide_max;        /* BSW: batches up to this many pairs run on the lanes-per-pair kernel (handle setting) */
     bool operator==(const BatchKey &o) const { return memcmp(this, &o, sizeof *this) == 0; }
 };
-static inline BatchKey make_key(int mode, const Const &c, int w, int is8)
+static inline BatchKey make_key(int mode, const Const &c, int w, int is8, int wide_max)
 {
     BatchKey k; memset(&k, 0, sizeof k);
     k.mode = mode; k.c = c; k.w = mode == MODE_BSW ? w : 0; k.is8 = mode == MODE_KSWV ? is8 : 0;
+    k.wide_max = mode == MODE_BSW ? wide_max : 0;
     return k;
 }
 
-enum { CLS_GENERAL = 33 };                 /* classes 1..16: packed, bin = class; 17..32: packed with an N in the query */
+/* classes 1..16: packed, bin = class; 17..32: packed with an N in the query; 33: general 32-bit kernel;
+ * 34..38: only the 16-bit lanes-per-pair kernel admits them (bsw_wide.cuh), by configuration */
+enum { CLS_GENERAL = 33, CLS_WIDE0 = 34 };
+static_assert(CLS_WIDE0 + BSW_WIDE_NCFG <= BSW_NCLASS, "class table too small");
 
 struct EngineStats {
-    long long batches, pairs, calls, launches, h2d_bytes, d2h_bytes, max_batch_pairs;
+    long long batches, pairs, calls, launches, h2d_bytes, d2h_bytes, max_batch_pairs, wide_batches;
+    /* where the time goes, ns summed over calls (caller side) and batches (engine side) */
+    long long scan_ns, reserve_ns, pack_ns, wait_ns, unpack_ns;      /* callers: steps 1..5 of the header comment */
+    long long packers_ns, submit_ns, flight_ns;                     /* engine: wait for packers, enqueue, submit -> done seen */
 };
+struct EngineProf {
+    std::atomic<long long> scan_ns{0}, reserve_ns{0}, pack_ns{0}, wait_ns{0}, unpack_ns{0}, packers_ns{0}, submit_ns{0}, flight_ns{0};
+    void clear() { scan_ns = 0; reserve_ns = 0; pack_ns = 0; wait_ns = 0; unpack_ns = 0; packers_ns = 0; submit_ns = 0; flight_ns = 0; }
+};
+static inline long long now_ns()
+{
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 struct Reservation {
     struct StagedSlot *slot = nullptr;
@@ -93,6 +109,7 @@ struct StagedSlot {
     DevBuf scratch, rowmax;
     cudaStream_t stream = nullptr;
     cudaEvent_t done_ev = nullptr;
+    long long t_submit = 0;
 };
 
 class Engine {
@@ -197,8 +214,16 @@ public:
         if (--r.slot->ncallers == 0) { r.slot->state = StagedSlot::FREE; cv_free.notify_all(); }
     }
 
-    EngineStats stats() { std::lock_guard<std::mutex> lk(mu); return st; }
-    void reset_stats() { std::lock_guard<std::mutex> lk(mu); memset(&st, 0, sizeof st); }
+    EngineProf prof;
+    EngineStats stats()
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        EngineStats r = st;
+        r.scan_ns = prof.scan_ns; r.reserve_ns = prof.reserve_ns; r.pack_ns = prof.pack_ns; r.wait_ns = prof.wait_ns;
+        r.unpack_ns = prof.unpack_ns; r.packers_ns = prof.packers_ns; r.submit_ns = prof.submit_ns; r.flight_ns = prof.flight_ns;
+        return r;
+    }
+    void reset_stats() { std::lock_guard<std::mutex> lk(mu); memset(&st, 0, sizeof st); prof.clear(); }
 
 private:
     std::unique_ptr<StagedSlot[]> slots;
@@ -265,6 +290,7 @@ private:
                 if (s.state == StagedSlot::INFLIGHT) {
                     if (cudaEventQuery(s.done_ev) == cudaSuccess) {
                         s.state = StagedSlot::DONE;
+                        prof.flight_ns += now_ns() - s.t_submit;
                         done_gens[(size_t)(&s - slots.get())].store(s.gen, std::memory_order_release);
                         progress = true;
                     } else ++inflight;
@@ -280,8 +306,12 @@ private:
                 cv_free.notify_all();                      /* callers waiting for a full slot to leave the OPEN set */
                 lk.unlock();
                 for (StagedSlot *s : todo) {
+                    const long long t0 = now_ns();
                     while (s->packed.load(std::memory_order_acquire) < s->npairs) cpu_relax();   /* packers are quick and never block */
+                    const long long t1 = now_ns();
                     submit(*s);
+                    s->t_submit = now_ns();
+                    prof.packers_ns += t1 - t0; prof.submit_ns += s->t_submit - t1;
                 }
                 lk.lock();
                 for (StagedSlot *s : todo) {
@@ -316,27 +346,49 @@ inline void Engine::submit(StagedSlot &s)
     CK(cudaMemcpyAsync(s.d_rec, s.h_rec, (size_t)n * 24, cudaMemcpyHostToDevice, q));
     if (s.nbytes > 0) CK(cudaMemcpyAsync(s.d_seq, s.h_seq, (size_t)s.nbytes + 16, cudaMemcpyHostToDevice, q));
     long long launches = 0;
-    /* class order = sorted order: queries with an N first, then the plain ones, longest bin first; general pairs last */
+    /* class order = sorted order.  Large batches: queries with an N first, then the plain ones, each longest bin first
+     * (one multi-bin launch of the thread-owns-two-pairs kernel per kind).  Small BSW batches run on the lanes-per-pair
+     * kernel, which reads N natively: bins longest first with the N and plain pairs of a bin adjacent, so that the bins of
+     * one configuration are one launch.  Then the wide-only classes, then the general pairs. */
     ClassStart cs; memset(&cs, 0, sizeof cs);
     BinTable tb[2]; memset(tb, 0, sizeof tb);          /* [0]: N classes (BSW only), [1]: plain classes */
+    const bool use_wide = key.mode == MODE_BSW && n <= key.wide_max && wide_eligible(key.c, 0, 0, 1);
     int pos = 0, maxne[2] = { 0, 0 };
-    for (int pass = 0; pass < 2; ++pass) {
-        BinTable &t = tb[pass];
-        int blocks = 0;
-        for (int qb = BSW_NBINS; qb >= 1; --qb) {
-            const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls];
-            cs.start[cls] = pos;
-            if (cnt <= 0) continue;
-            t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos; t.ne[t.nbins] = qb * 16;
-            maxne[pass] = std::max(maxne[pass], qb * 16);
-            t.nbins++;
-            blocks += (cnt + 63) / 64; pos += cnt;
+    int wfirst[BSW_WIDE_NCFG], wcount[BSW_WIDE_NCFG];   /* small batches: sorted range served by each configuration */
+    for (int cf = 0; cf < BSW_WIDE_NCFG; ++cf) { wfirst[cf] = 0; wcount[cf] = 0; }
+    if (use_wide) {
+        for (int qb = BSW_NBINS; qb >= 1; --qb)
+            for (int pass = 0; pass < 2; ++pass) {
+                const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls], cf = wide_cfg_of_bin(qb);
+                cs.start[cls] = pos;
+                if (cnt <= 0) continue;
+                if (wcount[cf] == 0) wfirst[cf] = pos;
+                wcount[cf] += cnt; pos += cnt;
+            }
+    } else {
+        for (int pass = 0; pass < 2; ++pass) {
+            BinTable &t = tb[pass];
+            int blocks = 0;
+            for (int qb = BSW_NBINS; qb >= 1; --qb) {
+                const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls];
+                cs.start[cls] = pos;
+                if (cnt <= 0) continue;
+                t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos; t.ne[t.nbins] = qb * 16;
+                maxne[pass] = std::max(maxne[pass], qb * 16);
+                t.nbins++;
+                blocks += (cnt + 63) / 64; pos += cnt;
+            }
+            t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos;
         }
-        t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos;
     }
     const int n_packed = pos;
+    int wo_first[BSW_WIDE_NCFG], wo_count[BSW_WIDE_NCFG];   /* wide-only classes */
+    for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf) {
+        cs.start[CLS_WIDE0 + cf] = pos; wo_first[cf] = pos; wo_count[cf] = s.cls_cnt[CLS_WIDE0 + cf];
+        pos += wo_count[cf];
+    }
     cs.start[CLS_GENERAL] = pos;
-    const int n_general = s.cls_cnt[CLS_GENERAL];
+    const int n_general = s.cls_cnt[CLS_GENERAL], gen_first = pos;
     class_scatter_kernel<<<(n + 255) / 256, 256, 0, q>>>(s.d_rec, n, cs, s.d_sorted);
     ++launches;
     const PairIO io = pairio_compact(s.d_rec, s.d_res);
@@ -344,18 +396,25 @@ inline void Engine::submit(StagedSlot &s)
     unsigned long long *d_cells = (unsigned long long *)cells.p;
     if (key.mode == MODE_BSW) {
         const bool sym = key.c.oe_del == key.c.oe_ins;
-        for (int pass = 0; pass < 2; ++pass) {
-            const BinTable &t = tb[pass];
-            const int blocks = t.first_block[t.nbins];
-            if (blocks <= 0) continue;
-            auto kern = pass == 0 ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
-                                  : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
-            kern<<<blocks, 32, maxne[pass] * BSW_WARP_ELEM_BYTES, q>>>(io, seq, seq, s.d_sorted, t, key.c, key.w, d_cells);
-            ++launches;
+        if (use_wide) {
+            for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf)
+                if (wcount[cf] > 0) { launch_wide(cf, sym, io, seq, seq, s.d_sorted, wfirst[cf], wcount[cf], key.c, key.w, q); ++launches; }
+        } else {
+            for (int pass = 0; pass < 2; ++pass) {
+                const BinTable &t = tb[pass];
+                const int blocks = t.first_block[t.nbins];
+                if (blocks <= 0) continue;
+                auto kern = pass == 0 ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
+                                      : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
+                kern<<<blocks, 32, maxne[pass] * BSW_WARP_ELEM_BYTES, q>>>(io, seq, seq, s.d_sorted, t, key.c, key.w, d_cells);
+                ++launches;
+            }
         }
+        for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf)
+            if (wo_count[cf] > 0) { launch_wide(cf, sym, io, seq, seq, s.d_sorted, wo_first[cf], wo_count[cf], key.c, key.w, q); ++launches; }
         if (n_general > 0) {
             s.scratch.reserve((size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2));
-            bsw_general_kernel<<<(n_general + 63) / 64, 64, 0, q>>>(io, seq, seq, s.d_sorted, n_packed, n_general, key.c, key.w,
+            bsw_general_kernel<<<(n_general + 63) / 64, 64, 0, q>>>(io, seq, seq, s.d_sorted, gen_first, n_general, key.c, key.w,
                                                                     (int2 *)s.scratch.p, d_cells);
             ++launches;
         }
@@ -371,7 +430,7 @@ inline void Engine::submit(StagedSlot &s)
         if (n_general > 0) {
             const size_t he_b = (size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2);
             s.scratch.reserve(he_b + (size_t)n_general * ((size_t)s.max_len1_general + 2) * sizeof(int));
-            kswv_general_kernel<<<(n_general + 63) / 64, 64, 0, q>>>(io, seq, seq, d_aln, s.d_sorted, n_packed, n_general, key.c,
+            kswv_general_kernel<<<(n_general + 63) / 64, 64, 0, q>>>(io, seq, seq, d_aln, s.d_sorted, gen_first, n_general, key.c,
                                                                      key.is8, 0, (int2 *)s.scratch.p, (int *)((char *)s.scratch.p + he_b), d_cells);
             ++launches;
         }
@@ -382,6 +441,7 @@ inline void Engine::submit(StagedSlot &s)
     CK(cudaEventRecord(s.done_ev, q));
     std::lock_guard<std::mutex> lk(mu);
     st.launches += launches;
+    if (use_wide) st.wide_batches++;
     st.h2d_bytes += (long long)n * 24 + s.nbytes;
     st.d2h_bytes += (long long)res_b;
 }

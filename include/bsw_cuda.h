@@ -205,6 +205,8 @@ typedef struct bsw_stats {
     int64_t pairs;            /* pairs processed                             */
     int64_t pairs_packed;     /* pairs served by the packed s16x2 kernel     */
     int64_t pairs_general;    /* pairs served by the general 32-bit kernel   */
+    int64_t pairs_wide;       /* pairs served by the lanes-per-pair 16-bit kernel (large / resident calls: as launched;
+                                 small staged calls: the pairs only that kernel admits) */
     int64_t cells;            /* DP cells evaluated, oracle definition (8d); BSW counts them
                                  only while bsw_set_cell_counting(h,1) is on    */
     int64_t kernel_launches;  /* CUDA kernels launched by this library       */
@@ -223,6 +225,10 @@ void kswv_reset_stats(kswv_t *h);
 void kswv_set_timing(kswv_t *h, int on);
 /* pair count from which a host-pointer call takes the large-call path (default BSW_CUDA_DIRECT_MIN = 131072) */
 void bsw_set_direct_min(bsw_t *h, int pairs);
+/* calls / merged batches of up to this many pairs run on the lanes-per-pair kernel (latency), larger ones on the
+ * thread-owns-two-pairs kernel (throughput); default BSW_CUDA_WIDE_MAX = 16384.  0: never (pairs only the 16-bit
+ * kernel admits still use it). */
+void bsw_set_wide_max(bsw_t *h, int pairs);
 void kswv_set_direct_min(kswv_t *h, int pairs);
 
 /* counters of the staged-call engine of one device (process-wide) */
@@ -233,6 +239,17 @@ typedef struct bsw_engine_stats {
     int64_t kernel_launches;
     int64_t h2d_bytes, d2h_bytes;
     int64_t max_batch_pairs;
+    int64_t wide_batches;     /* batches run on the lanes-per-pair kernel (<= BSW_CUDA_WIDE_MAX pairs) */
+    /* where the time of staged calls goes, nanoseconds.  Caller threads, summed over calls: */
+    int64_t scan_ns;          /*   contract checks + class of every pair                              */
+    int64_t reserve_ns;       /*   waiting for room in a staging slot                                 */
+    int64_t pack_ns;          /*   compact records + named bases into pinned staging                  */
+    int64_t wait_ns;          /*   asleep until the batch is back                                     */
+    int64_t unpack_ns;        /*   results into the caller's SeqPair / kswr_t array                   */
+    /* engine thread, summed over batches: */
+    int64_t packers_ns;       /*   waiting for the last packer of a closed batch                      */
+    int64_t submit_ns;        /*   enqueueing copies + kernels                                        */
+    int64_t flight_ns;        /*   enqueue done -> completion seen (copies + kernels on the device)   */
 } bsw_engine_stats_t;
 void bsw_engine_get_stats(int device, bsw_engine_stats_t *out);
 void bsw_engine_reset_stats(int device);

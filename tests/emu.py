@@ -15,12 +15,14 @@ def lib():
     if _lib is None:
         so = os.path.join(HERE, "emu", "libbswemu.so")
         src = os.path.join(HERE, "emu", "emu.cpp")
-        deps = [src] + [os.path.join(ROOT, "bwa-mem2-arm_b200", "csrc", f) for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh")]
+        deps = [src, os.path.join(HERE, "emu", "warp_emu.h")] + [os.path.join(ROOT, "bwa-mem2-arm_b200", "csrc", f)
+                                                                 for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh", "bsw_wide.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
         _lib = C.CDLL(so)
         _lib.emu_bsw.restype = C.c_int
         _lib.emu_kswv.restype = C.c_int
+        _lib.emu_bsw_wide.restype = C.c_int
     return _lib
 
 
@@ -42,3 +44,12 @@ def kswv(pairs, ref, qer, aln, is8, phase, o_del=6, e_del=1, o_ins=6, e_ins=1, a
     npk = lib().emu_kswv(_p(pairs), _p(ref), _p(qer), _p(aln), len(pairs), o_del, e_del, o_ins, e_ins, a, b, -1,
                          is8, phase, force_general, _p(cells))
     return cells, npk
+
+
+def bsw_wide(pairs, ref, qer, w=100, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=100, end_bonus=5, a=1, b=4, min_cfg=0):
+    """Lanes-per-pair kernel (bsw_wide.cuh) on an emulated warp.  Returns (results, mask of the pairs it admits)."""
+    out = pairs.copy()
+    taken = np.zeros(len(out), np.uint8)
+    lib().emu_bsw_wide(_p(out), _p(ref), _p(qer), len(out), o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, -1, w,
+                       min_cfg, _p(taken))
+    return out, taken.astype(bool)

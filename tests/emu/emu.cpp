@@ -5,9 +5,12 @@
 #include <vector>
 #include <cstring>
 #include <cstdint>
+#include <algorithm>
+#include "warp_emu.h"
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core2.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/kswv_core.cuh"
+#include "../../bwa-mem2-arm_b200/csrc/bsw_wide.cuh"
 #include "../../include/bsw_cuda.h"
 
 using namespace bswk;
@@ -22,6 +25,57 @@ static Const mk(int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_b
 
 static void put(bsw_seqpair_t &sp, const PairOut &o)
 { sp.score = o.score; sp.tle = o.tle; sp.gtle = o.gtle; sp.qle = o.qle; sp.gscore = o.gscore; sp.max_off = o.max_off; }
+
+// lanes-per-pair kernel (bsw_wide.cuh): one emulated warp per 32 / G pairs.  min_cfg forces a larger configuration than
+// the query needs (more idle lanes, same results).  Returns the number of pairs it took; the others are left untouched.
+template <int G, int R>
+static void wide_warp(const Const &c, int w, const bsw_seqpair_t *pairs, const int *ids, int cnt, const uint8_t *ref,
+                      const uint8_t *qer, bsw_seqpair_t *out)
+{
+    PairOut res[32 / G];
+    warp_emu::run([&](int lane) {
+        const int g = lane / G, gl = lane % G;
+        PairIn P = { 0, 0, 0, 0, 0, 0 };
+        if (g < cnt) { const bsw_seqpair_t &p = pairs[ids[g]]; P = { p.idr, p.idq, p.len1, p.len2, p.h0, 1 }; }
+        PairOut o;
+        if (c.oe_del == c.oe_ins) bsw_wide_lane<G, R, true>(c, w, P, ref, qer, gl, o);
+        else bsw_wide_lane<G, R, false>(c, w, P, ref, qer, gl, o);
+        if (gl == 0 && g < cnt) res[g] = o;
+    });
+    for (int g = 0; g < cnt; ++g) put(out[ids[g]], res[g]);
+}
+
+int emu_bsw_wide_impl(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
+                            int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
+                            int a, int b, int ambig, int w, int min_cfg, unsigned char *taken)
+{
+    Const c = mk(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig);
+    std::vector<int> by_cfg[BSW_WIDE_NCFG];
+    int tot = 0;
+    for (int i = 0; i < n; ++i) {
+        taken[i] = 0;
+        if (!wide_eligible(c, pairs[i].len1, pairs[i].len2, pairs[i].h0)) continue;
+        int k = wide_cfg_for(pairs[i].len2);
+        if (k < 0) continue;
+        if (k < min_cfg) k = min_cfg;
+        by_cfg[k].push_back(i); taken[i] = 1; ++tot;
+    }
+    for (int k = 0; k < BSW_WIDE_NCFG; ++k) {
+        const std::vector<int> &v = by_cfg[k];
+        const int per = 32 / wide_cfg_lanes(k);
+        for (size_t f = 0; f < v.size(); f += per) {
+            const int cnt = (int)std::min<size_t>(per, v.size() - f);
+            switch (k) {
+            case 0: wide_warp<8, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 1: wide_warp<8, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 2: wide_warp<16, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 3: wide_warp<32, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            default: wide_warp<32, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            }
+        }
+    }
+    return tot;
+}
 
 extern "C" {
 
@@ -73,6 +127,11 @@ int emu_bsw(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
     return (int)el.size();
 }
 
+
+int emu_bsw_wide(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n,
+                 int o_del, int e_del, int o_ins, int e_ins, int zdrop, int end_bonus,
+                 int a, int b, int ambig, int w, int min_cfg, unsigned char *taken)
+{ return emu_bsw_wide_impl(pairs, ref, qer, n, o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig, w, min_cfg, taken); }
 
 static void kput(bsw_kswr_t *aln, const bsw_seqpair_t &sp, int i, const KswOut &o, int phase)
 {

@@ -52,3 +52,17 @@ def test_product_does_not_touch_oracle():
                 assert m is None, (f, m.group(0))
     mk = open(os.path.join(pkg, "Makefile")).read()
     assert "-lcudart" in mk and "oracle" not in mk
+
+
+def test_shim_header_compiles_and_links(tmp_path):
+    """bandedSWA_b200.h (the drop-in classes a bwa-mem2 tree would include) compiles as C++ and links against the
+    library: the C5 harness is its translation unit."""
+    import subprocess
+    exe = tmp_path / "stream_c5"
+    pkg = os.path.join(ROOT, "bwa-mem2-arm_b200")
+    cmd = ["g++", "-O1", "-std=c++17", "-Wall", "-Werror", "-pthread", "-o", str(exe), os.path.join(ROOT, "tools", "stream_c5.cpp"),
+           "-L" + pkg, "-lbswcuda", "-Wl,-rpath," + pkg, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    r = subprocess.run([str(exe)], capture_output=True, text=True)     # no --in: usage, exit 2, no CUDA call
+    assert r.returncode == 2 and "--in" in r.stderr

@@ -14,13 +14,17 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 # Host-pointer calls take one of two routes (bsw_api.cu): below BSW_CUDA_DIRECT_MIN pairs the staged engine (merged
 # batches, compact records), above it the chunked DMA path.  Every test that goes through these fixtures runs on both.
-@pytest.fixture(scope="module", params=["staged", "direct"])
+# Each route runs with both DP kernels: "wide" = lanes-per-pair 16-bit kernel for every pair it admits (the default for calls /
+# batches of up to 16384 pairs), "thread" = thread-owns-two-pairs kernel (large calls), wide only for what it alone admits.
+@pytest.fixture(scope="module", params=["staged-wide", "staged-thread", "direct-wide", "direct-thread"])
 def sw(bsw, request):
     assert bsw.device_count() > 0, "no CUDA device: the product has no CPU fallback"
     obj = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
-    if request.param == "direct":
+    route, kern = request.param.split("-")
+    if route == "direct":
         obj.set_direct_min(0)
-    obj.route = request.param
+    obj.set_wide_max(1 << 30 if kern == "wide" else 0)
+    obj.route = route
     yield obj
     obj.close()
 
@@ -168,20 +172,25 @@ def test_c3_long_reads_zdrop(ora, sw):
                 assert cells.sum() < 0.8 * full           # early exits really happen
 
 
-def test_general_path_long_and_high_scores(ora, sw):
-    """Pairs the packed kernel does not admit (score bound > 255 or query > 255) go to the
-    32-bit kernel: 400 bp near-identical pairs, and a 1500 x 2000 pair."""
+def test_16bit_tier_and_general_path(ora, sw):
+    """Pairs the byte-packed kernel does not admit (score bound > 255 or query > 252 columns) run on the 16-bit
+    lanes-per-pair kernel up to 1023 columns / scores of 16383 -- 400 bp near-identical pairs, h0 up to 300 -- and
+    only what is beyond that on the 32-bit kernel: a 1500 x 2000 pair."""
     P, r, q = ora.gen_random(300, 256, 400, 256, 500, h0min=100, h0max=300, sim=0.97, p_n=0.001, seed=99)
     o, _ = _oracle_bsw(ora, P, r, q)
     g = P.copy()
+    sw.reset_stats()
     sw.getScores16(g, r, q, len(g), 1, 100)
     _assert_same(o, g)
-    assert sw.stats()["pairs_general"] > 0
+    st = sw.stats()
+    assert st["pairs_general"] == 0 and st["pairs_wide"] > 0     # the 16-bit tier stays on chip (row a4)
     P, r, q = ora.gen_random(3, 1500, 1500, 2000, 2000, h0min=40, h0max=40, sim=0.98, p_n=0.0, seed=5)
     o, _ = _oracle_bsw(ora, P, r, q)
     g = P.copy()
+    sw.reset_stats()
     sw.scalarBandedSWAWrapper(g, r, q, len(g), 1, 100)
     _assert_same(o, g)
+    assert sw.stats()["pairs_general"] == 3                       # beyond 1023 columns: the 32-bit kernel
 
 
 def test_mixed_lengths_and_cells(ora, sw):

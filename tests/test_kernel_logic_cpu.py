@@ -108,3 +108,43 @@ def test_bsw_count_tiny_queries_cheap_gaps(ora):
         _check_bsw(ora, P, r, q, w=100, a=3, b=5, o_del=2, e_del=2, o_ins=3, e_ins=1)
         _check_bsw(ora, P, r, q, w=2, o_del=0, o_ins=0)
         _check_bsw(ora, P, r, q, w=100, zdrop=0, o_del=0, e_del=1, o_ins=0, e_ins=3, a=2, b=1)
+
+
+def _check_wide(ora, pairs, ref, qer, **kw):
+    prm = ora.make_params(**{k: v for k, v in kw.items() if k not in ("w", "min_cfg")})
+    o = pairs.copy()
+    ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4)
+    e, taken = emu.bsw_wide(pairs, ref, qer, **kw)
+    bad = common.diff_fields(o, e, common.BSW_FIELDS) & taken
+    assert not bad.any(), common.describe_first(o, e, bad)
+    return taken
+
+
+def test_bsw_wide_lanes_per_pair(ora):
+    """bsw_wide.cuh (G lanes per pair, 16-bit register state, prefix-max f) on an emulated warp: edge cases, bands, z-drop,
+    scoring variants, unclean initial rows (h0 up to 250 against short bands), forced larger configurations."""
+    p, r, q = common.edge_case_pairs()
+    for w in (100, 7, 1):
+        assert _check_wide(ora, p, r, q, w=w).all()
+    P, r, q = ora.gen_random(160, 0, 140, 0, 300, h0min=1, h0max=250, sim=0.85, p_n=0.02, seed=11)
+    assert _check_wide(ora, P, r, q).all()
+    _check_wide(ora, P, r, q, w=5, zdrop=10)
+    _check_wide(ora, P, r, q, w=1, zdrop=0, end_bonus=0)
+    _check_wide(ora, P, r, q, w=30, min_cfg=2)
+    _check_wide(ora, P, r, q, w=37, o_del=4, e_del=2, o_ins=7, e_ins=1, zdrop=30, end_bonus=0, a=2, b=3)
+    _check_wide(ora, P, r, q, w=2, o_del=0, o_ins=0)
+
+
+def test_bsw_wide_16bit_tier(ora):
+    """Scores > 255 and queries up to 1023 columns (row a4): every configuration, plus C3-shaped pairs with z-drop."""
+    P, r, q = ora.gen_random(50, 200, 600, 200, 900, h0min=100, h0max=600, sim=0.95, p_n=0.002, seed=12)
+    assert _check_wide(ora, P, r, q).all()
+    _check_wide(ora, P, r, q, w=20, zdrop=50)
+    P, r, q = ora.gen_random(12, 900, 1023, 900, 1400, h0min=10, h0max=900, sim=0.97, p_n=0.001, seed=13)
+    assert _check_wide(ora, P, r, q).all()
+    d = ora.gen_bsw(100, read_len=250, seed=0xC3, div=0.05)
+    L, lr, lq = d["left"]
+    assert _check_wide(ora, L, lr, lq).all()
+    _check_wide(ora, L, lr, lq, w=10, zdrop=20)
+    P, r, q = ora.gen_random(4, 1100, 1200, 1100, 1200, h0min=10, h0max=20, sim=0.9, seed=14)       # too long: not admitted
+    assert not _check_wide(ora, P, r, q).any()
