@@ -31,7 +31,7 @@ EXPORTS = (
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
     "bsw_arena_begin", "bsw_arena_end", "bsw_ref_upload", "bsw_ref_free", "bsw_getScoresRef",
-    "bsw_set_direct_min", "kswv_set_direct_min", "bsw_set_wide_max", "bsw_engine_get_stats", "bsw_engine_reset_stats",
+    "bsw_set_direct_min", "kswv_set_direct_min", "bsw_set_wide_max", "bsw_set_wide_policy", "bsw_engine_get_stats", "bsw_engine_reset_stats",
 )
 
 
@@ -106,6 +106,7 @@ def lib():
     L.bsw_getScoresRef.argtypes = [vp, vp, vp, vp, vp, i32, i32]
     for f in (L.bsw_set_direct_min, L.kswv_set_direct_min, L.bsw_set_wide_max):
         f.argtypes = [vp, C.c_int]
+    L.bsw_set_wide_policy.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     L.bsw_engine_get_stats.argtypes = [C.c_int, C.POINTER(EngineStats)]
     L.bsw_engine_reset_stats.argtypes = [C.c_int]
     L.bsw_measure_dpx_peak.restype = C.c_double
@@ -200,6 +201,9 @@ class BandedPairWiseSW:
 
     def set_wide_max(self, pairs):
         self._L.bsw_set_wide_max(self._h, int(pairs))
+
+    def set_wide_policy(self, wide_max, wide_lat, wide_split):
+        self._L.bsw_set_wide_policy(self._h, int(wide_max), int(wide_lat), int(wide_split))
 
     def stats(self):
         s = Stats()

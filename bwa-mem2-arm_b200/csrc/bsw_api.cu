@@ -199,7 +199,9 @@ struct Core {
     int chunk_pairs = 1 << 19;
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
-    int wide_max = 16384;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
+    int wide_max = 32768;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
+    int wide_lat = 8192;             /* ... and up to this many on its shapes with more lanes per pair (latency) */
+    int wide_split = 0;              /* staged batches in between: bins up to this index stay on the thread kernel */
     int mode = MODE_BSW;
     /* arenas declared with bsw_arena_begin */
     const uint8_t *arena_ref_h = nullptr, *arena_qer_h = nullptr;
@@ -250,7 +252,9 @@ void core_init(Core &k, int mode)
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
-    k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 16384);
+    k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 32768);
+    k.wide_lat = env_int("BSW_CUDA_WIDE_LAT", 8192);
+    k.wide_split = env_int("BSW_CUDA_WIDE_SPLIT", 0);
 }
 
 void core_destroy(Core &k)
@@ -358,14 +362,15 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
      * sets the call's duration): their bins go to the lanes-per-pair kernel instead, like the wide-only pairs below. */
     const bool sym = k.c.oe_del == k.c.oe_ins;
     const bool small = n <= k.wide_max && !k.count_cells && wide_eligible(k.c, 0, 0, 1);
+    std::vector<WideSeg> segs;             /* everything the lanes-per-pair kernel runs: one launch (bsw_kernels.cuh) */
     for (int pass = 0; pass < 2; ++pass)
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
             const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
             if (cnt <= 0) continue;
             if (small) {
-                launch_wide(wide_cfg_of_bin(qb), sym, io, d_ref, d_qer, sorted, n_packed, cnt, k.c, w, s);
-                CK(cudaGetLastError());
-                k.st.kernel_launches++;
+                const int cf = wide_cfg_of_bin(qb);
+                if (!segs.empty() && segs.back().cfg == cf && segs.back().first + segs.back().count == n_packed) segs.back().count += cnt;
+                else segs.push_back(WideSeg{ cf, n_packed, cnt });
                 n_packed += cnt;
                 continue;
             }
@@ -398,10 +403,12 @@ void launch_bsw_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_
     for (int cfg = BSW_WIDE_NCFG - 1; cfg >= 0; --cfg) {
         const int cnt = pl->hist_w[cfg];
         if (cnt <= 0) continue;
-        launch_wide(cfg, sym, io, d_ref, d_qer, sorted, n_packed + n_wide, cnt, k.c, w, s);
-        CK(cudaGetLastError());
-        k.st.kernel_launches++;
+        segs.push_back(WideSeg{ cfg, n_packed + n_wide, cnt });
         n_wide += cnt;
+    }
+    if (!segs.empty()) {
+        k.st.kernel_launches += launch_wide_segs(segs.data(), (int)segs.size(), n <= k.wide_lat, sym, io, d_ref, d_qer, sorted, k.c, w, s);
+        CK(cudaGetLastError());
     }
     if (pl->n_general > 0) {
         /* bounded scratch: at most ~1 GiB of eh rows per launch */
@@ -781,7 +788,7 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
                  int tier8_check, int is8, int phase)
 {
     Engine &eng = k.rt(pick_engine(k)).eng();
-    const BatchKey key = make_key(k.mode, k.c, w, is8, k.wide_max);
+    const BatchKey key = make_key(k.mode, k.c, w, is8, k.wide_max, k.wide_lat, k.wide_split);
     std::vector<uint8_t> cls;
     int first = 0;
     while (first < n) {
@@ -1160,6 +1167,7 @@ void bsw_set_timing(bsw_t *h, int on) { h->k.timing = on; }
 void bsw_set_cell_counting(bsw_t *h, int on) { h->k.count_cells = on; }
 void bsw_set_direct_min(bsw_t *h, int pairs) { h->k.direct_min = pairs; }
 void bsw_set_wide_max(bsw_t *h, int pairs) { h->k.wide_max = pairs; }
+void bsw_set_wide_policy(bsw_t *h, int wide_max, int wide_lat, int wide_split) { h->k.wide_max = wide_max; h->k.wide_lat = wide_lat; h->k.wide_split = wide_split; }
 void kswv_get_stats(kswv_t *h, bsw_stats_t *out) { stats_with_pending(h->k, out); }
 void kswv_reset_stats(kswv_t *h) { stats_reset(h->k); }
 void kswv_set_timing(kswv_t *h, int on) { h->k.timing = on; }

@@ -262,25 +262,88 @@ bsw_wide_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__res
     if (pi >= 0 && gl == 0) store_bsw(io, pi, o);
 }
 
-/* launches the configuration `cfg` (bsw_wide.cuh wide_cfg_*) over sorted slots [first, first + count) */
-static inline void launch_wide(int cfg, bool sym, PairIO io, const uint8_t *ref, const uint8_t *qer, const uint32_t *sorted,
-                               int first, int count, const Const &c, int w, cudaStream_t s)
+/* Kernel shapes (G lanes x R registers x 2 halves).  0..4 are the configurations of bsw_wide.cuh (smallest that holds a
+ * query: the throughput choice); 5 and 6 are their latency alternates: the same columns on twice / four times the lanes,
+ * i.e. a shorter chain per row, for batches too small to fill the device anyway. */
+#define BSW_WIDE_NSHAPE 7
+static inline int wide_shape_lanes(int sh) { return sh <= 1 ? 8 : (sh == 2 || sh == 5) ? 16 : 32; }
+static inline int wide_latency_shape(int cfg) { return cfg == 1 ? 5 : cfg == 2 ? 6 : cfg; }   /* (8,9) -> (16,5); (16,9) -> (32,5) */
+
+#define BSW_WIDE_MAXSEG 8
+struct WideTable {
+    int nseg;
+    int first_block[BSW_WIDE_MAXSEG + 1];
+    int first_pair[BSW_WIDE_MAXSEG], count[BSW_WIDE_MAXSEG], shape[BSW_WIDE_MAXSEG];
+};
+
+template <int G, int R, bool SYM>
+__device__ __forceinline__ void wide_block(const PairIO &io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                                           const uint32_t *__restrict__ sorted_idx, int first, int count, const Const &c, int w, int block)
 {
-    if (count <= 0) return;
-    const int G = wide_cfg_lanes(cfg), per_block = 128 / G, grid = (count + per_block - 1) / per_block;
-#define BSW_WIDE_LAUNCH(GG, RR)                                                                             \
-    do {                                                                                                    \
-        if (sym) bsw_wide_kernel<GG, RR, true><<<grid, 128, 0, s>>>(io, ref, qer, sorted, first, count, c, w);   \
-        else bsw_wide_kernel<GG, RR, false><<<grid, 128, 0, s>>>(io, ref, qer, sorted, first, count, c, w);      \
-    } while (0)
-    switch (cfg) {
-    case 0: BSW_WIDE_LAUNCH(8, 5); break;
-    case 1: BSW_WIDE_LAUNCH(8, 9); break;
-    case 2: BSW_WIDE_LAUNCH(16, 9); break;
-    case 3: BSW_WIDE_LAUNCH(32, 9); break;
-    default: BSW_WIDE_LAUNCH(32, 16); break;
+    const int gid = (block * 128 + (int)threadIdx.x) / G, gl = (int)threadIdx.x % G;
+    const int pi = gid < count ? (int)sorted_idx[first + gid] : -1;
+    const PairIn P = load_pair(io, pi);
+    PairOut o;
+    bsw_wide_lane<G, R, SYM>(c, w, P, ref, qer, gl, o);
+    if (pi >= 0 && gl == 0) store_bsw(io, pi, o);
+}
+
+/* several shapes in ONE launch: a small batch is two or three short segments, and launching them one after another
+ * on a stream adds their latencies (each 50-150 us) */
+template <bool SYM>
+__global__ void __launch_bounds__(128)
+bsw_wide_multi_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                      const uint32_t *__restrict__ sorted_idx, const __grid_constant__ WideTable t, Const c, int w)
+{
+    int s = 0;
+    while (s + 1 < t.nseg && (int)blockIdx.x >= t.first_block[s + 1]) ++s;
+    const int block = (int)blockIdx.x - t.first_block[s], first = t.first_pair[s], count = t.count[s];
+    switch (t.shape[s]) {
+    case 0: wide_block<8, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 1: wide_block<8, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 2: wide_block<16, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 3: wide_block<32, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 5: wide_block<16, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    default: wide_block<32, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
     }
-#undef BSW_WIDE_LAUNCH
+}
+
+/* one sorted range per configuration */
+struct WideSeg { int cfg, first, count; };
+
+/* launches the segments (configuration cfg of bsw_wide.cuh over sorted slots [first, first + count)); returns the number
+ * of kernel launches.  latency = true picks the shapes with more lanes per pair. */
+static inline int launch_wide_segs(const WideSeg *segs, int nseg, bool latency, bool sym, PairIO io, const uint8_t *ref,
+                                   const uint8_t *qer, const uint32_t *sorted, const Const &c, int w, cudaStream_t s)
+{
+    WideTable t; memset(&t, 0, sizeof t);
+    int launches = 0, blocks = 0;
+    auto flush = [&] {
+        t.first_block[t.nseg] = blocks;
+        if (blocks > 0) {
+            if (sym) bsw_wide_multi_kernel<true><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+            else bsw_wide_multi_kernel<false><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+            ++launches;
+        }
+        memset(&t, 0, sizeof t); blocks = 0;
+    };
+    for (int k = 0; k < nseg; ++k) {
+        if (segs[k].count <= 0) continue;
+        if (segs[k].cfg >= 4) {               /* (32, 16): 128 registers, its own kernel */
+            const int grid = (segs[k].count + 3) / 4;
+            if (sym) bsw_wide_kernel<32, 16, true><<<grid, 128, 0, s>>>(io, ref, qer, sorted, segs[k].first, segs[k].count, c, w);
+            else bsw_wide_kernel<32, 16, false><<<grid, 128, 0, s>>>(io, ref, qer, sorted, segs[k].first, segs[k].count, c, w);
+            ++launches;
+            continue;
+        }
+        if (t.nseg == BSW_WIDE_MAXSEG) flush();
+        const int sh = latency ? wide_latency_shape(segs[k].cfg) : segs[k].cfg, per_block = 128 / wide_shape_lanes(sh);
+        t.first_block[t.nseg] = blocks; t.first_pair[t.nseg] = segs[k].first; t.count[t.nseg] = segs[k].count; t.shape[t.nseg] = sh;
+        blocks += (segs[k].count + per_block - 1) / per_block;
+        t.nseg++;
+    }
+    flush();
+    return launches;
 }
 
 /* configuration that serves the packed bin qb (queries of up to qb * 16 - 4 bases) */

@@ -47,6 +47,13 @@ __device__ __forceinline__ uint32_t w_shfl_up(uint32_t v, int d, int G) { return
 __device__ __forceinline__ uint32_t w_shfl_xor(uint32_t v, int m, int G) { return __shfl_xor_sync(0xffffffffu, v, m, G); }
 __device__ __forceinline__ uint32_t w_shfl(uint32_t v, int src, int G) { return __shfl_sync(0xffffffffu, v, src, G); }
 __device__ __forceinline__ bool w_any(bool p) { return __any_sync(0xffffffffu, p) != 0; }
+/* maximum over the G-lane group (REDUX.SYNC: one instruction instead of log2 G shuffle + max steps) */
+__device__ __forceinline__ uint32_t w_redmax(uint32_t v, int G)
+{
+    unsigned lane; asm("mov.u32 %0, %%laneid;" : "=r"(lane));
+    const unsigned mask = G >= 32 ? 0xffffffffu : ((1u << G) - 1u) << (lane & ~(unsigned)(G - 1));
+    return __reduce_max_sync(mask, v);
+}
 __device__ __forceinline__ uint32_t p_addmax(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2(a, b, c); }
 __device__ __forceinline__ uint32_t p_minu(uint32_t a, uint32_t b) { return __vminu2(a, b); }
 __device__ __forceinline__ int ctz32(uint32_t v) { return __ffs((int)v) - 1; }
@@ -55,6 +62,7 @@ uint32_t w_shfl_up(uint32_t v, int d, int G);       /* tests/emu/warp_emu.h */
 uint32_t w_shfl_xor(uint32_t v, int m, int G);
 uint32_t w_shfl(uint32_t v, int src, int G);
 bool w_any(bool p);
+uint32_t w_redmax(uint32_t v, int G);
 static inline uint32_t p_addmax(uint32_t a, uint32_t b, uint32_t c)
 { return pk(imax((int16_t)(lo16(a) + lo16(b)), lo16(c)), imax((int16_t)(hi16(a) + hi16(b)), hi16(c))); }
 static inline uint32_t p_minu(uint32_t a, uint32_t b)
@@ -229,9 +237,20 @@ BSW_HD void bsw_wide_lane(const Const &c, int w_in, const PairIn &P, const uint8
         }
 
         /* ---- row bookkeeping (A.1), identical in every lane of the group ---- */
-        int m = (int)mx((int)(hmaxp & 0xffffu), (int)(hmaxp >> 16));
+        /* row maximum and its LAST column in one group reduction: key = m << 10 | column.  Per lane: the maximum of its
+         * own columns, then per half a bit string of "differs from it" flags, register 0 first. */
+        int m, mj;
+        {
+            const uint32_t ml = (uint32_t)mx((int)(hmaxp & 0xffffu), (int)(hmaxp >> 16));
+            const uint32_t mm = ml * 0x00010001u;
+            uint32_t acc = 0u;
 #pragma unroll
-        for (int d = G >> 1; d >= 1; d >>= 1) { const int y = (int)w_shfl_xor((uint32_t)m, d, G); m = m > y ? m : y; }
+            for (int r = 0; r < R; ++r) acc = acc * 2u + p_minu(h[r] ^ mm, 0x00010001u);
+            const uint32_t rm = (1u << R) - 1u, eq_lo = ~acc & rm, eq_hi = (~acc >> 16) & rm;
+            const int cand = eq_hi ? base_hi + R - 1 - ctz32(eq_hi) : base_lo + R - 1 - ctz32(eq_lo | (1u << (R - 1)));
+            const uint32_t key = w_redmax(ml ? (ml << 10) | (uint32_t)cand : 0u, G);
+            m = (int)(key >> 10); mj = (int)(key & 1023u);
+        }
         int h1 = 0;
         {
             const int ce = live ? endc - 1 : 0;
@@ -239,22 +258,6 @@ BSW_HD void bsw_wide_lane(const Const &c, int w_in, const PairIn &P, const uint8
             h1 = (ce % C) >= R ? (int)(v >> 16) : (int)(v & 0xffffu);
         }
         if (live && endc == qlen) { max_ie = gscore > h1 ? max_ie : i; gscore = gscore > h1 ? gscore : h1; }
-        const bool need_mj = live && m > 0 && (m > smax || (c.zdrop > 0 && smax - m > c.zdrop));
-        int mj = -1;
-        if (w_any(need_mj)) {
-            /* last column whose h equals the row maximum: per half a bit string of "differs" flags, register 0 first */
-            const uint32_t mm = (uint32_t)m * 0x00010001u;
-            uint32_t acc = 0u;
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc = acc * 2u + p_minu(h[r] ^ mm, 0x00010001u);
-            const uint32_t rm = (1u << R) - 1u, eq_lo = ~acc & rm, eq_hi = (~acc >> 16) & rm;
-            int cand = -1;
-            if (eq_hi) cand = base_hi + R - 1 - ctz32(eq_hi);
-            else if (eq_lo) cand = base_lo + R - 1 - ctz32(eq_lo);
-#pragma unroll
-            for (int d = G >> 1; d >= 1; d >>= 1) { const int y = (int)w_shfl_xor((uint32_t)cand, d, G); cand = cand > y ? cand : y; }
-            mj = cand;
-        }
         bool stop = false, scan = false;
         if (live) {
             stop = m == 0;
@@ -280,12 +283,11 @@ BSW_HD void bsw_wide_lane(const Const &c, int w_in, const PairIn &P, const uint8
 #pragma unroll
             for (int r = 0; r < R; ++r) acc = acc * 2u + p_minu((Hs[r] | E[r]) & K[r], 0x00010001u);
             const uint32_t nz_lo = acc & 0xffffu, nz_hi = acc >> 16;
-            int cand = -1;
-            if (nz_hi) cand = base_hi + R - 1 - ctz32(nz_hi);
-            else if (nz_lo) cand = base_lo + R - 1 - ctz32(nz_lo);
-#pragma unroll
-            for (int d = G >> 1; d >= 1; d >>= 1) { const int y = (int)w_shfl_xor((uint32_t)cand, d, G); cand = cand > y ? cand : y; }
-            if (scan) end = mn(cand + 2, qlen);
+            uint32_t cand = 0u;                      /* column + 1; 0: none in this lane */
+            if (nz_hi) cand = (uint32_t)(base_hi + R - ctz32(nz_hi));
+            else if (nz_lo) cand = (uint32_t)(base_lo + R - ctz32(nz_lo));
+            cand = w_redmax(cand, G);
+            if (scan) end = mn((int)cand + 1, qlen);
         }
         if (stop) act = false;
         ++i;

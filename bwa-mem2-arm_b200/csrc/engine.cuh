@@ -51,14 +51,18 @@ struct BatchKey {
     Const c;
     int w;               /* BSW band */
     int is8;             /* kswv precision rule */
-    int wide_max;        /* BSW: batches up to this many pairs run on the lanes-per-pair kernel (handle setting) */
+    int wide_max;        /* BSW: batches up to this many pairs run on the lanes-per-pair kernel (handle settings) */
+    int wide_lat;        /*      ... up to this many on its shapes with more lanes per pair */
+    int wide_split;      /*      ... bins up to this index stay on the thread kernel in between (0: none) */
     bool operator==(const BatchKey &o) const { return memcmp(this, &o, sizeof *this) == 0; }
 };
-static inline BatchKey make_key(int mode, const Const &c, int w, int is8, int wide_max)
+static inline BatchKey make_key(int mode, const Const &c, int w, int is8, int wide_max, int wide_lat, int wide_split)
 {
     BatchKey k; memset(&k, 0, sizeof k);
     k.mode = mode; k.c = c; k.w = mode == MODE_BSW ? w : 0; k.is8 = mode == MODE_KSWV ? is8 : 0;
     k.wide_max = mode == MODE_BSW ? wide_max : 0;
+    k.wide_lat = mode == MODE_BSW ? wide_lat : 0;
+    k.wide_split = mode == MODE_BSW ? wide_split : 0;
     return k;
 }
 
@@ -107,9 +111,11 @@ struct StagedSlot {
     char *d_rec = nullptr, *d_seq = nullptr, *d_res = nullptr;
     uint32_t *d_sorted = nullptr;
     DevBuf scratch, rowmax;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t done_ev = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;
+    cudaEvent_t done_ev = nullptr, fork_ev = nullptr, join_ev = nullptr;
     long long t_submit = 0;
+    std::mutex done_mu;
+    std::condition_variable done_cv;
 };
 
 class Engine {
@@ -118,6 +124,7 @@ public:
     int cap_pairs = 1 << 16;
     long long cap_bytes = 32ll << 20;
     int nslots = 6, max_inflight = 3;
+    int spin_iters = 400;                         /* wait_done: pause iterations before blocking */
     int smem_optin = 0;
     std::atomic<long long> outstanding{0};        /* pairs reserved and not yet handed back: load measure for device choice */
 
@@ -127,6 +134,7 @@ public:
         cap_bytes = (long long)std::max(1, env_int("BSW_CUDA_STAGE_MB", 32)) << 20;
         nslots = std::max(2, std::min(16, env_int("BSW_CUDA_STAGE_SLOTS", nslots)));
         max_inflight = std::max(1, std::min(nslots - 1, env_int("BSW_CUDA_INFLIGHT", max_inflight)));
+        spin_iters = std::max(0, env_int("BSW_CUDA_SPIN", spin_iters));
         memset(&st, 0, sizeof st);
         slots.reset(new StagedSlot[nslots]);
         done_gens.reset(new std::atomic<int>[nslots]);
@@ -198,12 +206,12 @@ public:
     void wait_done(const Reservation &r)
     {
         StagedSlot *s = r.slot;
-        for (int spin = 0; spin < 2000; ++spin) {          /* short spin: a wake-up through the futex costs more than a small batch */
+        for (int spin = 0; spin < spin_iters; ++spin) {    /* short spin: a wake-up through the futex costs more than a small batch */
             if (done_gen(s) >= r.gen) return;
             cpu_relax();
         }
-        std::unique_lock<std::mutex> lk(mu);
-        cv_done.wait(lk, [&] { return s->state == StagedSlot::DONE && s->gen == r.gen; });
+        std::unique_lock<std::mutex> lk(s->done_mu);       /* per slot: a landing batch wakes its own callers only */
+        s->done_cv.wait(lk, [&] { return done_gen(s) >= r.gen; });
     }
 
     /* step 5 done */
@@ -231,7 +239,7 @@ private:
     struct SlotRange { StagedSlot *b, *e; StagedSlot *begin() const { return b; } StagedSlot *end() const { return e; } };
     SlotRange all() { return SlotRange{ slots.get(), slots.get() + nslots }; }
     std::mutex mu;
-    std::condition_variable cv_engine, cv_free, cv_done, cv_ready;
+    std::condition_variable cv_engine, cv_free, cv_ready;
     std::thread th;
     bool stop = false, ready = false;
     std::atomic<int> engine_sleeping{0};
@@ -267,7 +275,10 @@ private:
             CK(cudaMemset(s.d_seq, 0, seq));
             CK(cudaMalloc((void **)&s.d_sorted, (size_t)cap_pairs * 4));
             CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+            CK(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
             CK(cudaEventCreateWithFlags(&s.done_ev, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&s.fork_ev, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&s.join_ev, cudaEventDisableTiming));
         }
         cells.reserve(sizeof(unsigned long long));
         CK(cudaMemset(cells.p, 0, sizeof(unsigned long long)));
@@ -280,25 +291,37 @@ private:
         init_device();
         { std::lock_guard<std::mutex> lk(mu); ready = true; }
         cv_ready.notify_all();
-        std::vector<StagedSlot *> todo;
+        std::vector<StagedSlot *> todo, flying, landed;
         auto last_activity = std::chrono::steady_clock::now();
         std::unique_lock<std::mutex> lk(mu);
         while (!stop) {
             bool progress = false;
-            int inflight = 0;
-            for (StagedSlot &s : all())
-                if (s.state == StagedSlot::INFLIGHT) {
-                    if (cudaEventQuery(s.done_ev) == cudaSuccess) {
-                        s.state = StagedSlot::DONE;
-                        prof.flight_ns += now_ns() - s.t_submit;
-                        done_gens[(size_t)(&s - slots.get())].store(s.gen, std::memory_order_release);
-                        progress = true;
-                    } else ++inflight;
+            /* 1. completions: the event queries run without the engine mutex (callers reserve and release under it) */
+            if (!flying.empty()) {
+                lk.unlock();
+                landed.clear();
+                for (size_t k = 0; k < flying.size();) {
+                    if (cudaEventQuery(flying[k]->done_ev) == cudaSuccess) { landed.push_back(flying[k]); flying[k] = flying.back(); flying.pop_back(); }
+                    else ++k;
                 }
-            if (progress) cv_done.notify_all();
+                const long long t = landed.empty() ? 0 : now_ns();
+                lk.lock();
+                for (StagedSlot *s : landed) { s->state = StagedSlot::DONE; prof.flight_ns += t - s->t_submit; }
+                if (!landed.empty()) {
+                    lk.unlock();
+                    for (StagedSlot *s : landed) {
+                        done_gens[(size_t)(s - slots.get())].store(s->gen, std::memory_order_release);
+                        { std::lock_guard<std::mutex> g(s->done_mu); }
+                        s->done_cv.notify_all();
+                    }
+                    lk.lock();
+                    progress = true;
+                }
+            }
+            /* 2. close what the device has room for */
             todo.clear();
             for (StagedSlot &s : all())
-                if (s.state == StagedSlot::OPEN && s.npairs > 0 && (s.want_close || inflight + (int)todo.size() < max_inflight)) {
+                if (s.state == StagedSlot::OPEN && s.npairs > 0 && (s.want_close || (int)(flying.size() + todo.size()) < max_inflight)) {
                     s.state = StagedSlot::CLOSED;
                     todo.push_back(&s);
                 }
@@ -316,16 +339,17 @@ private:
                 lk.lock();
                 for (StagedSlot *s : todo) {
                     s->state = StagedSlot::INFLIGHT;
+                    flying.push_back(s);
                     st.batches++; st.pairs += s->npairs; st.max_batch_pairs = std::max<long long>(st.max_batch_pairs, s->npairs);
                 }
                 progress = true;
             }
             if (progress) { last_activity = std::chrono::steady_clock::now(); continue; }
-            bool pending = inflight > 0;
+            bool pending = !flying.empty();
             for (StagedSlot &s : all()) if (s.state == StagedSlot::OPEN && s.npairs > 0) pending = true;
             if (pending || std::chrono::steady_clock::now() - last_activity < std::chrono::microseconds(300)) {
                 lk.unlock();                               /* busy period: poll (events + new arrivals) */
-                for (int k = 0; k < 64; ++k) cpu_relax();
+                for (int k = 0; k < 32; ++k) cpu_relax();
                 lk.lock();
             } else {
                 engine_sleeping.store(1, std::memory_order_release);
@@ -346,46 +370,52 @@ inline void Engine::submit(StagedSlot &s)
     CK(cudaMemcpyAsync(s.d_rec, s.h_rec, (size_t)n * 24, cudaMemcpyHostToDevice, q));
     if (s.nbytes > 0) CK(cudaMemcpyAsync(s.d_seq, s.h_seq, (size_t)s.nbytes + 16, cudaMemcpyHostToDevice, q));
     long long launches = 0;
-    /* class order = sorted order.  Large batches: queries with an N first, then the plain ones, each longest bin first
-     * (one multi-bin launch of the thread-owns-two-pairs kernel per kind).  Small BSW batches run on the lanes-per-pair
-     * kernel, which reads N natively: bins longest first with the N and plain pairs of a bin adjacent, so that the bins of
-     * one configuration are one launch.  Then the wide-only classes, then the general pairs. */
+    /* class order = sorted order.  Which kernel serves the packed-eligible bins of a BSW batch depends on its size:
+     *   n <= wide_lat   every bin on the lanes-per-pair kernel, shapes with more lanes (a pair takes 50-100 us);
+     *   n <= wide_max   the bins above wide_split x 16 columns on the lanes-per-pair kernel (throughput shapes), the
+     *                   shorter ones on the thread-owns-two-pairs kernel, side by side on two streams.  Measured
+     *                   (profiles/r02_stream_matrix.jsonl): a thread needs ~0.4 ms even for <= 76-column pairs when the
+     *                   device is this empty, so the default split is 0 = every bin on the lanes-per-pair kernel;
+     *   larger          every bin on the thread kernel (throughput; the batch is big enough to hide its latency).
+     * Thread-kernel classes: queries with an N first, then the plain ones, each longest bin first (one multi-bin launch
+     * per kind).  Lanes-per-pair classes: bins longest first with the N and plain pairs of a bin adjacent, the bins of
+     * one configuration forming one segment of ONE launch.  Then the wide-only classes, then the general pairs. */
     ClassStart cs; memset(&cs, 0, sizeof cs);
     BinTable tb[2]; memset(tb, 0, sizeof tb);          /* [0]: N classes (BSW only), [1]: plain classes */
-    const bool use_wide = key.mode == MODE_BSW && n <= key.wide_max && wide_eligible(key.c, 0, 0, 1);
+    int split = BSW_NBINS;
+    if (key.mode == MODE_BSW && n <= key.wide_max && wide_eligible(key.c, 0, 0, 1)) split = n <= key.wide_lat ? 0 : std::max(0, std::min(key.wide_split, BSW_NBINS));
+    const bool use_wide = split < BSW_NBINS;
     int pos = 0, maxne[2] = { 0, 0 };
-    int wfirst[BSW_WIDE_NCFG], wcount[BSW_WIDE_NCFG];   /* small batches: sorted range served by each configuration */
-    for (int cf = 0; cf < BSW_WIDE_NCFG; ++cf) { wfirst[cf] = 0; wcount[cf] = 0; }
-    if (use_wide) {
-        for (int qb = BSW_NBINS; qb >= 1; --qb)
-            for (int pass = 0; pass < 2; ++pass) {
-                const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls], cf = wide_cfg_of_bin(qb);
-                cs.start[cls] = pos;
-                if (cnt <= 0) continue;
-                if (wcount[cf] == 0) wfirst[cf] = pos;
-                wcount[cf] += cnt; pos += cnt;
-            }
-    } else {
-        for (int pass = 0; pass < 2; ++pass) {
-            BinTable &t = tb[pass];
-            int blocks = 0;
-            for (int qb = BSW_NBINS; qb >= 1; --qb) {
-                const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls];
-                cs.start[cls] = pos;
-                if (cnt <= 0) continue;
-                t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos; t.ne[t.nbins] = qb * 16;
-                maxne[pass] = std::max(maxne[pass], qb * 16);
-                t.nbins++;
-                blocks += (cnt + 63) / 64; pos += cnt;
-            }
-            t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos;
+    std::vector<WideSeg> segs;
+    for (int pass = 0; pass < 2; ++pass) {
+        BinTable &t = tb[pass];
+        int blocks = 0;
+        for (int qb = split; qb >= 1; --qb) {
+            const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls];
+            cs.start[cls] = pos;
+            if (cnt <= 0) continue;
+            t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos; t.ne[t.nbins] = qb * 16;
+            maxne[pass] = std::max(maxne[pass], qb * 16);
+            t.nbins++;
+            blocks += (cnt + 63) / 64; pos += cnt;
         }
+        t.first_block[t.nbins] = blocks; t.first_pair[t.nbins] = pos;
     }
-    const int n_packed = pos;
-    int wo_first[BSW_WIDE_NCFG], wo_count[BSW_WIDE_NCFG];   /* wide-only classes */
-    for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf) {
-        cs.start[CLS_WIDE0 + cf] = pos; wo_first[cf] = pos; wo_count[cf] = s.cls_cnt[CLS_WIDE0 + cf];
-        pos += wo_count[cf];
+    const int n_thread = pos;
+    for (int qb = BSW_NBINS; qb > split; --qb)
+        for (int pass = 0; pass < 2; ++pass) {
+            const int cls = pass == 0 ? BSW_NBINS + qb : qb, cnt = s.cls_cnt[cls], cf = wide_cfg_of_bin(qb);
+            cs.start[cls] = pos;
+            if (cnt <= 0) continue;
+            if (!segs.empty() && segs.back().cfg == cf) segs.back().count += cnt; else segs.push_back(WideSeg{ cf, pos, cnt });
+            pos += cnt;
+        }
+    const int n_packed = n_thread;   /* kswv: the packed classes */
+    for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf) {      /* wide-only classes */
+        const int cnt = s.cls_cnt[CLS_WIDE0 + cf];
+        cs.start[CLS_WIDE0 + cf] = pos;
+        if (cnt > 0) segs.push_back(WideSeg{ cf, pos, cnt });
+        pos += cnt;
     }
     cs.start[CLS_GENERAL] = pos;
     const int n_general = s.cls_cnt[CLS_GENERAL], gen_first = pos;
@@ -396,22 +426,23 @@ inline void Engine::submit(StagedSlot &s)
     unsigned long long *d_cells = (unsigned long long *)cells.p;
     if (key.mode == MODE_BSW) {
         const bool sym = key.c.oe_del == key.c.oe_ins;
-        if (use_wide) {
-            for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf)
-                if (wcount[cf] > 0) { launch_wide(cf, sym, io, seq, seq, s.d_sorted, wfirst[cf], wcount[cf], key.c, key.w, q); ++launches; }
-        } else {
-            for (int pass = 0; pass < 2; ++pass) {
-                const BinTable &t = tb[pass];
-                const int blocks = t.first_block[t.nbins];
-                if (blocks <= 0) continue;
-                auto kern = pass == 0 ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
-                                      : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
-                kern<<<blocks, 32, maxne[pass] * BSW_WARP_ELEM_BYTES, q>>>(io, seq, seq, s.d_sorted, t, key.c, key.w, d_cells);
-                ++launches;
-            }
+        /* the lanes-per-pair segments run beside the thread kernel on the slot's second stream */
+        const bool fork = !segs.empty() && n_thread > 0;
+        if (fork) { CK(cudaEventRecord(s.fork_ev, q)); CK(cudaStreamWaitEvent(s.stream2, s.fork_ev, 0)); }
+        for (int pass = 0; pass < 2; ++pass) {
+            const BinTable &t = tb[pass];
+            const int blocks = t.first_block[t.nbins];
+            if (blocks <= 0) continue;
+            auto kern = pass == 0 ? (sym ? bsw_packed_kernel<false, true, true> : bsw_packed_kernel<false, false, true>)
+                                  : (sym ? bsw_packed_kernel<false, true, false> : bsw_packed_kernel<false, false, false>);
+            kern<<<blocks, 32, maxne[pass] * BSW_WARP_ELEM_BYTES, q>>>(io, seq, seq, s.d_sorted, t, key.c, key.w, d_cells);
+            ++launches;
         }
-        for (int cf = BSW_WIDE_NCFG - 1; cf >= 0; --cf)
-            if (wo_count[cf] > 0) { launch_wide(cf, sym, io, seq, seq, s.d_sorted, wo_first[cf], wo_count[cf], key.c, key.w, q); ++launches; }
+        if (!segs.empty()) {
+            launches += launch_wide_segs(segs.data(), (int)segs.size(), n <= key.wide_lat, sym, io, seq, seq, s.d_sorted, key.c, key.w,
+                                         fork ? s.stream2 : q);
+            if (fork) { CK(cudaEventRecord(s.join_ev, s.stream2)); CK(cudaStreamWaitEvent(q, s.join_ev, 0)); }
+        }
         if (n_general > 0) {
             s.scratch.reserve((size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2));
             bsw_general_kernel<<<(n_general + 63) / 64, 64, 0, q>>>(io, seq, seq, s.d_sorted, gen_first, n_general, key.c, key.w,

@@ -226,9 +226,14 @@ void kswv_set_timing(kswv_t *h, int on);
 /* pair count from which a host-pointer call takes the large-call path (default BSW_CUDA_DIRECT_MIN = 131072) */
 void bsw_set_direct_min(bsw_t *h, int pairs);
 /* calls / merged batches of up to this many pairs run on the lanes-per-pair kernel (latency), larger ones on the
- * thread-owns-two-pairs kernel (throughput); default BSW_CUDA_WIDE_MAX = 16384.  0: never (pairs only the 16-bit
+ * thread-owns-two-pairs kernel (throughput); default BSW_CUDA_WIDE_MAX = 32768.  0: never (pairs only the 16-bit
  * kernel admits still use it). */
 void bsw_set_wide_max(bsw_t *h, int pairs);
+/* the whole kernel-choice policy of a handle: wide_max as above; calls / batches of up to wide_lat pairs (default
+ * BSW_CUDA_WIDE_LAT = 8192) use the kernel's shapes with more lanes per pair (lowest latency); staged batches between
+ * wide_lat and wide_max keep the bins of up to wide_split x 16 columns on the thread kernel (default
+ * BSW_CUDA_WIDE_SPLIT = 0: none).  Results never depend on it. */
+void bsw_set_wide_policy(bsw_t *h, int wide_max, int wide_lat, int wide_split);
 void kswv_set_direct_min(kswv_t *h, int pairs);
 
 /* counters of the staged-call engine of one device (process-wide) */

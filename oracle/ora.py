@@ -59,7 +59,7 @@ class KswvCfg(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle.c", "workload.c", "oracle.h", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle.c", "workload.c", "bsw_avx2.c", "oracle.h", "Makefile")]
     stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
@@ -81,6 +81,8 @@ def lib():
                                      vp, vp, vp, vp, vp, vp]
         L.ora_bsw_batch.restype = C.c_int64
         L.ora_bsw_batch.argtypes = [vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int32, C.c_int, vp]
+        L.ora_bsw_batch_avx2.restype = C.c_int64
+        L.ora_bsw_batch_avx2.argtypes = [vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int32, C.c_int]
         L.ora_kswv_batch.restype = C.c_int64
         L.ora_kswv_batch.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int, C.c_int, C.c_int, vp]
         L.ora_ksw_align2.restype = None
@@ -107,6 +109,13 @@ def bsw_batch(pairs, ref, qer, params, w=100, nthreads=1, want_cells=False):
     cells = np.zeros(len(pairs), dtype=np.int64) if want_cells else None
     tot = lib().ora_bsw_batch(_p(pairs), _p(ref), _p(qer), len(pairs), C.byref(params), w, nthreads, _p(cells))
     return (tot, cells) if want_cells else tot
+
+
+def bsw_batch_avx2(pairs, ref, qer, params, w=100, nthreads=1):
+    """Inter-sequence AVX2 port (bsw_avx2.c: 16 pairs in the 16-bit lanes of a register, as the reference's
+    smithWaterman256_16 organises them); same contract and results as bsw_batch.  Returns total cells."""
+    assert pairs.dtype == SEQPAIR and pairs.flags.c_contiguous
+    return lib().ora_bsw_batch_avx2(_p(pairs), _p(ref), _p(qer), len(pairs), C.byref(params), w, nthreads)
 
 
 def kswv_batch(pairs, ref, qer, aln, params, is8, phase, nthreads=1, want_cells=False):

@@ -65,6 +65,12 @@ int64_t ora_bsw_batch(ora_seqpair_t *pairs, const uint8_t *ref, const uint8_t *q
                       int32_t n, const ora_bsw_params_t *p, int32_t w, int nthreads,
                       int64_t *cells_out);
 
+/* the same batch through the inter-sequence AVX2 port (bsw_avx2.c): 16 pairs per register in 16-bit lanes, sorted by
+ * length, per-lane band / trimming / z-drop state -- the organisation of the reference's smithWaterman256_16.
+ * Identical results; returns the total cells. */
+int64_t ora_bsw_batch_avx2(ora_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
+                           int32_t n, const ora_bsw_params_t *p, int32_t w, int nthreads);
+
 /* one pair, one pass of ksw_u8 / ksw_i16 semantics in exact arithmetic
  * (SURVEY.md Appendix A.2). is8 selects the 8-bit overflow rule. */
 void ora_ksw_pass(int qlen, const uint8_t *query, int tlen, const uint8_t *target,

@@ -46,10 +46,11 @@ def kswv(pairs, ref, qer, aln, is8, phase, o_del=6, e_del=1, o_ins=6, e_ins=1, a
     return cells, npk
 
 
-def bsw_wide(pairs, ref, qer, w=100, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=100, end_bonus=5, a=1, b=4, min_cfg=0):
-    """Lanes-per-pair kernel (bsw_wide.cuh) on an emulated warp.  Returns (results, mask of the pairs it admits)."""
+def bsw_wide(pairs, ref, qer, w=100, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=100, end_bonus=5, a=1, b=4, min_cfg=0, latency=False):
+    """Lanes-per-pair kernel (bsw_wide.cuh) on an emulated warp.  Returns (results, mask of the pairs it admits).
+    latency: the shapes with more lanes per pair that small batches run on."""
     out = pairs.copy()
     taken = np.zeros(len(out), np.uint8)
     lib().emu_bsw_wide(_p(out), _p(ref), _p(qer), len(out), o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, -1, w,
-                       min_cfg, _p(taken))
+                       min_cfg | (0x100 if latency else 0), _p(taken))
     return out, taken.astype(bool)

@@ -51,6 +51,8 @@ int emu_bsw_wide_impl(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *q
 {
     Const c = mk(o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, ambig);
     std::vector<int> by_cfg[BSW_WIDE_NCFG];
+    const bool latency = (min_cfg & 0x100) != 0;      // the shapes with more lanes per pair (bsw_kernels.cuh wide_latency_shape)
+    min_cfg &= 0xff;
     int tot = 0;
     for (int i = 0; i < n; ++i) {
         taken[i] = 0;
@@ -62,10 +64,13 @@ int emu_bsw_wide_impl(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *q
     }
     for (int k = 0; k < BSW_WIDE_NCFG; ++k) {
         const std::vector<int> &v = by_cfg[k];
-        const int per = 32 / wide_cfg_lanes(k);
+        const int shape = latency ? (k == 1 ? 5 : k == 2 ? 6 : k) : k;
+        const int per = 32 / (shape <= 1 ? 8 : (shape == 2 || shape == 5) ? 16 : 32);
         for (size_t f = 0; f < v.size(); f += per) {
             const int cnt = (int)std::min<size_t>(per, v.size() - f);
-            switch (k) {
+            switch (shape) {
+            case 5: wide_warp<16, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 6: wide_warp<32, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
             case 0: wide_warp<8, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
             case 1: wide_warp<8, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
             case 2: wide_warp<16, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;

@@ -90,6 +90,13 @@ inline uint32_t w_shfl(uint32_t v, int src, int G)
     const int lane = warp_emu::lane_id(), b = warp_emu::exchange(v);
     return warp_emu::g_w->val[b][(lane / G) * G + (src % G)];
 }
+inline uint32_t w_redmax(uint32_t v, int G)
+{
+    const int lane = warp_emu::lane_id(), b = warp_emu::exchange(v), g0 = (lane / G) * G;
+    uint32_t r = 0;
+    for (int l = g0; l < g0 + G; ++l) r = warp_emu::g_w->val[b][l] > r ? warp_emu::g_w->val[b][l] : r;
+    return r;
+}
 inline bool w_any(bool p)
 {
     const int b = warp_emu::exchange(p ? 1u : 0u);

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 # Host-pointer calls take one of two routes (bsw_api.cu): below BSW_CUDA_DIRECT_MIN pairs the staged engine (merged
 # batches, compact records), above it the chunked DMA path.  Every test that goes through these fixtures runs on both.
 # Each route runs with both DP kernels: "wide" = lanes-per-pair 16-bit kernel for every pair it admits (the default for calls /
-# batches of up to 16384 pairs), "thread" = thread-owns-two-pairs kernel (large calls), wide only for what it alone admits.
+# batches of up to 32768 pairs), "thread" = thread-owns-two-pairs kernel (large calls), wide only for what it alone admits.
 @pytest.fixture(scope="module", params=["staged-wide", "staged-thread", "direct-wide", "direct-thread"])
 def sw(bsw, request):
     assert bsw.device_count() > 0, "no CUDA device: the product has no CPU fallback"
@@ -533,6 +533,26 @@ def test_staged_calls_from_many_threads(ora, bsw):
     es = bsw.engine_stats(0)
     assert es["batches"] > 0 and es["pairs"] > 0
     assert es["calls"] >= es["batches"]                       # calls were merged (or at worst one per batch)
+
+
+def test_staged_batch_size_regimes(ora, bsw):
+    """engine.cuh submit(): a staged BSW batch runs on the lanes-per-pair kernel alone (small), on both kernels side by side
+    (long bins lanes-per-pair, short bins thread-owns-two-pairs) or on the thread kernel alone (large).  Same results."""
+    d = ora.gen_bsw(60000, seed=0x7A1)
+    P, r, q = d["left"]
+    o, _ = _oracle_bsw(ora, P, r, q)
+    for n, wide_max, wide_lat, wide_split in ((1500, 32768, 8192, 0), (9000, 32768, 4096, 5), (9000, 32768, 4096, 0),
+                                              (40000, 1 << 30, 8192, 9), (40000, 16384, 8192, 0)):
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        h.set_direct_min(1 << 30); h.set_wide_policy(wide_max, wide_lat, wide_split)
+        bsw.engine_reset_stats(0)
+        g = np.ascontiguousarray(P[:n])
+        h.getScores16(g, r, q, n, 1, 100)
+        _assert_same(o[:n], g)
+        es = bsw.engine_stats(0)
+        assert es["pairs"] == n and es["batches"] == 1
+        assert es["wide_batches"] == (1 if n <= wide_max else 0)
+        h.close()
 
 
 def test_handle_creation_is_cheap(bsw):

@@ -111,7 +111,7 @@ def test_bsw_count_tiny_queries_cheap_gaps(ora):
 
 
 def _check_wide(ora, pairs, ref, qer, **kw):
-    prm = ora.make_params(**{k: v for k, v in kw.items() if k not in ("w", "min_cfg")})
+    prm = ora.make_params(**{k: v for k, v in kw.items() if k not in ("w", "min_cfg", "latency")})
     o = pairs.copy()
     ora.bsw_batch(o, ref, qer, prm, kw.get("w", 100), 4)
     e, taken = emu.bsw_wide(pairs, ref, qer, **kw)
@@ -133,6 +133,12 @@ def test_bsw_wide_lanes_per_pair(ora):
     _check_wide(ora, P, r, q, w=30, min_cfg=2)
     _check_wide(ora, P, r, q, w=37, o_del=4, e_del=2, o_ins=7, e_ins=1, zdrop=30, end_bonus=0, a=2, b=3)
     _check_wide(ora, P, r, q, w=2, o_del=0, o_ins=0)
+    # the shapes small batches run on: (16, 5) for up to 160 and (32, 5) for up to 320 columns
+    assert _check_wide(ora, P, r, q, latency=True).all()
+    _check_wide(ora, P, r, q, w=9, zdrop=15, latency=True)
+    P, r, q = ora.gen_random(60, 100, 300, 100, 400, h0min=1, h0max=200, sim=0.9, p_n=0.01, seed=15)
+    assert _check_wide(ora, P, r, q, latency=True).all()
+    _check_wide(ora, P, r, q, w=33, o_del=4, e_del=2, o_ins=7, e_ins=1, zdrop=30, a=2, b=3, latency=True)
 
 
 def test_bsw_wide_16bit_tier(ora):
