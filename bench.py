@@ -159,15 +159,54 @@ def gen_bsw_workload(ora, name, reads, seed_add, nthreads):
     return d, n_reads, desc
 
 
-def oracle_sides(ora, d, tries, cores):
+def oracle_sides(ora, d, tries, cores, simd=False):
     """Expected results of both sides through the caller protocol (tries = 1: plain calls).  Returns (Lo, Rin, Ro, cells,
-    pairs submitted)."""
+    pairs submitted).  simd: the inter-sequence AVX2 port instead of the scalar restatement (same results)."""
     prm = ora.make_params()
     L, lr, lq = d["left"]; R, rr, rq = d["right"]
-    Lo, nl, cl = ora.protocol_side(L, lr, lq, prm, W_BAND, tries, cores)
+    cells = [0]
+
+    def side(P, r, q):
+        if not simd:
+            o, n, c = ora.protocol_side(P, r, q, prm, W_BAND, tries, cores)
+            cells[0] += c
+            return o, n
+
+        def runner(sub, w):
+            cells[0] += ora.bsw_batch_avx2(sub, r, q, prm, w, cores)
+        o, n, _ = ora.protocol_side(P, r, q, prm, W_BAND, tries, cores, runner=runner)
+        return o, n
+    Lo, nl = side(L, lr, lq)
     Rin = R.copy(); ora.chain_h0(Lo, Rin)
-    Ro, nr, cr = ora.protocol_side(Rin, rr, rq, prm, W_BAND, tries, cores)
-    return Lo, Rin, Ro, cl + cr, nl + nr
+    Ro, nr = side(Rin, rr, rq)
+    return Lo, Rin, Ro, cells[0], nl + nr
+
+
+def stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, task_reads, threads, pinned, reps, tag="s", env=None):
+    """Runs tools/bin/stream_c5 on the workload; returns (its JSON line, the SeqPair records it wrote: left then right)."""
+    exe = os.path.join(ROOT, "tools", "bin", "stream_c5")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "tools"), "bin/stream_c5"])
+    tmp = os.path.join(ROOT, "gpurun_out", "stream_tmp"); os.makedirs(tmp, exist_ok=True)
+    w_in, w_out = os.path.join(tmp, f"w_{tag}.bin"), os.path.join(tmp, f"r_{tag}.bin")
+    if not os.path.exists(w_in):
+        ora.write_stream_workload(w_in, 0, L, R, lr, lq, rr, rq, ora.task_bounds(L["seqid"], n_reads, task_reads),
+                                  ora.task_bounds(R["seqid"], n_reads, task_reads))
+    r = subprocess.run([exe, "--in", w_in, "--out", w_out, "--threads", str(threads), "--pinned", str(pinned), "--reps", str(reps)],
+                       capture_output=True, text=True, env=env or dict(os.environ), timeout=1800)
+    if r.returncode != 0:
+        raise SystemExit("stream_c5 failed: " + r.stderr[-2000:])
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    raw = np.fromfile(w_out, dtype=bswb200.SEQPAIR)
+    os.remove(w_out)
+    return info, raw
+
+
+def stream_cleanup(tag):
+    try:
+        os.remove(os.path.join(ROOT, "gpurun_out", "stream_tmp", f"w_{tag}.bin"))
+    except OSError:
+        pass
 
 
 # ------------------------------------------------------------------------------------------------ reference arm (CPU)
@@ -193,7 +232,7 @@ def run_reference(args):
         d, n_reads, desc = gen_bsw_workload(ora, wl, args.reads, 0, cores)
         tries = 2 if wl == "c1" else 1
         def step():
-            return oracle_sides(ora, d, tries, cores)[3]
+            return oracle_sides(ora, d, tries, cores, simd=True)[3]
         npairs = len(d["left"][0]) + len(d["right"][0])
         metric = "bsw_gcups"
     times, cells = [], 0
@@ -208,13 +247,16 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": metric, "value": val, "unit": "GCUPS", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int32 (scalar CPU)", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": "int32 (scalar CPU)" if wl == "kswv_c4" else "int16 x16 (AVX2)", "data": "synthetic",
         "pairs_per_s": npairs / (ms * 1e-3),
         "config": {"workload": desc, "pairs_per_step": npairs, "cells_per_step": int(cells), "band_w": W_BAND,
                    "same_config_as_gpu_arm": True},
-        "cpu_baseline": {"value": val, "unit": "GCUPS", "cores": cores, "kind": "port",
-                         "sample": f"the whole config: {npairs} pairs per step, oracle restatement (ksw_extend2 / ksw_align2, scalar C), "
-                                   f"pthreads x{cores}; the reference's SSE/AVX2 sources are not in /root/reference"},
+        "cpu_baseline": {"value": val, "unit": "GCUPS", "cores": cores, "kind": "port" if wl == "kswv_c4" else "port-avx2",
+                         "sample": f"the whole config: {npairs} pairs per step, "
+                                   + ("oracle restatement of ksw_u8 / ksw_align2 (scalar C, exact arithmetic)" if wl == "kswv_c4" else
+                                      "inter-sequence AVX2 port (oracle/bsw_avx2.c: 16 pairs per register in 16-bit lanes, sorted by length, "
+                                      "bit-exact with the scalar restatement)")
+                                   + f", pthreads x{cores}; the reference's own x86 sources are not in /root/reference"},
         "e2e": {"value": val, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -299,15 +341,21 @@ def reduce_and_print(c, args, line_fn, times, sums):
 def cpu_baseline_bsw(ora, c, args, L, lr, lq):
     """Oracle port on all host threads on a bounded sample of the workload (rank 0)."""
     prm = ora.make_params()
-    ns = min(args.cpu_sample, len(L))
+    ns = min(args.cpu_sample * 4, len(L))
     samp = np.ascontiguousarray(L[:ns])
     t0 = time.perf_counter()
-    cells = ora.bsw_batch(samp, lr, lq, prm, W_BAND, c.cores)
+    cells = ora.bsw_batch_avx2(samp, lr, lq, prm, W_BAND, c.cores)
     dt = time.perf_counter() - t0
-    return {"value": cells / dt / 1e9, "unit": "GCUPS", "cores": c.cores, "kind": "port", "pairs_per_s": ns / dt,
-            "sample": f"first {ns} left-extension pairs of the workload ({cells} cells, {dt:.2f} s), oracle restatement of "
-                      f"ksw_extend2 (scalar C, pthreads x{c.cores}); the reference's SSE4.1/AVX2 build is unavailable (no source "
-                      f"in /root/reference); `--impl reference` runs the whole config"}
+    samp2 = np.ascontiguousarray(L[:ns // 4])
+    t0 = time.perf_counter()
+    cells2 = ora.bsw_batch(samp2, lr, lq, prm, W_BAND, c.cores)
+    dt2 = time.perf_counter() - t0
+    return {"value": cells / dt / 1e9, "unit": "GCUPS", "cores": c.cores, "kind": "port-avx2", "pairs_per_s": ns / dt,
+            "scalar_port_gcups": cells2 / dt2 / 1e9,
+            "sample": f"first {ns} left-extension pairs of the workload ({cells} cells, {dt:.2f} s) on the inter-sequence AVX2 port "
+                      f"(oracle/bsw_avx2.c: 16 pairs per register in 16-bit lanes, sorted by length -- the organisation of the reference's "
+                      f"smithWaterman256_16 -- bit-exact with the scalar restatement), pthreads x{c.cores}; the reference's own x86 build "
+                      f"is unavailable (no source in /root/reference); `--impl reference` runs the whole config"}
 
 
 def roofline(bswb200, c, ops_per_cell, cells_step, kernel_ms, ms_step, kernel, traffic_key=None):
@@ -470,26 +518,20 @@ def run_bsw(args):
                                                "(SURVEY.md 8(f).2); targets with N replaced by a base, expected results recomputed"}
             Rf.close()
     else:
-        hL, hR = pin(L), pin(R)
-
-        def run_side_host(P, hr, hq):
-            def runner(sub, w):
-                t = ora.classify(sub)
-                for tier, fn in ((0, sw.getScores8), (1, sw.getScores16)):
-                    sel = np.nonzero(t == tier)[0]
-                    if len(sel):
-                        part = np.ascontiguousarray(sub[sel]); fn(part, hr, hq, len(part), 1, w); sub[sel] = part
-            return ora.protocol_side(P, hr, hq, None, W_BAND, tries, runner=runner)[0]
-
-        res = {}
-
-        def step_e2e():
-            sw.arena_begin(h_lr, h_lq); res["L"] = run_side_host(hL, h_lr, h_lq); sw.arena_end()
-            Rin2 = hR.copy(); ora.chain_h0(res["L"], Rin2)
-            sw.arena_begin(h_rr, h_rq); res["R"] = run_side_host(Rin2, h_rr, h_rq); sw.arena_end()
-        sw.reset_stats(); e2e_ms = time_host(c, args, step_e2e); est = sw.stats()
-        check("e2e left (host protocol)", Lo, res["L"]); check("e2e right (host protocol)", Ro, res["R"])
-        e2e_api = "caller protocol on the host over bsw_getScores8/16 (numpy bookkeeping between the calls included in the time)"
+        # the caller's protocol in C++: tools/stream_c5.cpp (worker threads over per-task slices, per-task shim objects, band retry)
+        T = max(1, c.cores // max(1, c.world))
+        info, raw = stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, args.task_reads, T, 0, 3, tag=f"c1_{c.rank}")
+        Ro2 = Ro.copy(); Ro2["h0"] = Rin["h0"]
+        check("e2e left (C++ harness)", Lo, raw[:len(L)]); check("e2e right (C++ harness)", Ro2, raw[len(L):])
+        e2e_ms = info["wall_s"] * 1e3 * args.steps
+        est = {"h2d_bytes": info["engine_h2d_bytes"] * (args.steps + max(1, min(2, args.warmup))),
+               "d2h_bytes": info["engine_d2h_bytes"] * (args.steps + max(1, min(2, args.warmup)))}
+        variants["stream_harness"] = {"ms_per_step": info["wall_s"] * 1e3, "h2d_bytes_per_step": info["engine_h2d_bytes"], "threads": T,
+                                      "reads_per_task": args.task_reads, "us_per_call": info["us_per_call"],
+                                      "engine_pairs_per_batch": info["engine_pairs_per_batch"],
+                                      "api": "tools/stream_c5.cpp: BandedPairWiseSW::getScores8/16 of bandedSWA_b200.h from worker threads"}
+        e2e_api = (f"mem_chain2aln_across_reads_V2's protocol in C++ (tools/stream_c5.cpp): {T} worker threads, tasks of {args.task_reads} reads, "
+                   "per-task BandedPairWiseSW objects, pageable buffers, band retry; best of 3 passes over the whole config")
     sampler.stop()
     st_all = sw.stats()
 
@@ -651,38 +693,26 @@ def run_stream(args):
         return
     t_setup = time.perf_counter()
     cores = host_threads()
-    exe = os.path.join(ROOT, "tools", "bin", "stream_c5")
-    if not os.path.exists(exe):
-        subprocess.check_call(["make", "-C", os.path.join(ROOT, "tools"), "bin/stream_c5"])
     n_reads = args.reads or 1000000
     prm = ora.make_params()
     d = ora.gen_bsw(n_reads, seed=0xC5, nthreads=cores)
     L, lr, lq = d["left"]; R, rr, rq = d["right"]
-    Lo, Rin, Ro, cells, submitted = oracle_sides(ora, d, 2, cores)
-    tmp = os.path.join(ROOT, "gpurun_out", "stream_tmp"); os.makedirs(tmp, exist_ok=True)
-    w_in, w_out = os.path.join(tmp, "w.bin"), os.path.join(tmp, "r.bin")
-    ora.write_stream_workload(w_in, 0, L, R, lr, lq, rr, rq, ora.task_bounds(L["seqid"], n_reads, args.task_reads),
-                              ora.task_bounds(R["seqid"], n_reads, args.task_reads))
+    Lo, Rin, Ro, cells, submitted = oracle_sides(ora, d, 2, cores, simd=True)
     gpus = args.gpus
     env = dict(os.environ); env["BSW_CUDA_DEVICES"] = ",".join(str(i) for i in range(gpus))
     rows, parity = [], {"pairs": 0, "mismatches": 0, "fields": list(ora.BSW_OUT), "checked": []}
     Ro2 = Ro.copy(); Ro2["h0"] = Rin["h0"]
     for T in [int(x) for x in args.threads.split(",")]:
         for pinned in (0, 1):
-            r = subprocess.run([exe, "--in", w_in, "--out", w_out, "--threads", str(T), "--pinned", str(pinned), "--reps", "2"],
-                               capture_output=True, text=True, env=env, timeout=1800)
-            if r.returncode != 0:
-                raise SystemExit("stream_c5 failed: " + r.stderr[-2000:])
-            info = json.loads(r.stdout.strip().splitlines()[-1])
-            raw = np.fromfile(w_out, dtype=bswb200.SEQPAIR)
+            info, raw = stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, args.task_reads, T, pinned, 2, tag="c5", env=env)
             bad = mismatches(Lo, raw[:len(L)], ora.BSW_OUT) + mismatches(Ro2, raw[len(L):], ora.BSW_OUT)
             parity["pairs"] += len(L) + len(R); parity["mismatches"] += bad; parity["checked"].append(f"T={T} pinned={pinned}")
             info["gcups"] = cells / info["wall_s"] / 1e9
             rows.append(info)
-    os.remove(w_in); os.remove(w_out)
+    stream_cleanup("c5")
     best = max(rows, key=lambda x: x["pairs_per_s"])
     t0 = time.perf_counter()
-    samp = np.ascontiguousarray(L[:min(args.cpu_sample, len(L))]); cc = ora.bsw_batch(samp, lr, lq, prm, W_BAND, cores); dt = time.perf_counter() - t0
+    samp = np.ascontiguousarray(L[:min(args.cpu_sample * 4, len(L))]); cc = ora.bsw_batch_avx2(samp, lr, lq, prm, W_BAND, cores); dt = time.perf_counter() - t0
     line = {
         "metric": "bsw_gcups", "value": best["gcups"], "unit": "GCUPS", "n_gpus": gpus, "steps": 2, "warmup": 1,
         "ms_per_step": best["wall_s"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -693,11 +723,11 @@ def run_stream(args):
                    "pairs_submitted": int(submitted), "cells": int(cells)},
         "parity": parity,
         "e2e": {"value": best["gcups"], "unit": "GCUPS", "pairs_per_s": best["pairs_per_s"],
-                "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
+                "h2d_bytes_per_step": best["engine_h2d_bytes"], "d2h_bytes_per_step": best["engine_d2h_bytes"],
                 "api": "BandedPairWiseSW::getScores8/16 of bandedSWA_b200.h from worker threads (the whole run is host-buffer calls; best row)"},
         "stream_table": rows,
-        "cpu_baseline": {"value": cc / dt / 1e9, "unit": "GCUPS", "cores": cores, "kind": "port", "pairs_per_s": len(samp) / dt,
-                         "sample": f"first {len(samp)} left pairs, oracle restatement, pthreads x{cores}"},
+        "cpu_baseline": {"value": cc / dt / 1e9, "unit": "GCUPS", "cores": cores, "kind": "port-avx2", "pairs_per_s": len(samp) / dt,
+                         "sample": f"first {len(samp)} left pairs, inter-sequence AVX2 port (oracle/bsw_avx2.c), pthreads x{cores}"},
         "gpu_launches": int(sum(r["engine_launches"] for r in rows)),
         "setup_s": time.perf_counter() - t_setup,
     }

@@ -39,6 +39,8 @@ namespace {
 #define BSW_NSLOT 4
 #define BSW_NLEVELS 6
 
+#define BSW_ARENA_PIECES 32
+
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -64,7 +66,7 @@ struct DevCtx {
     /* sequence arenas declared with bsw_arena_begin: device copies + the event that marks them uploaded */
     DevBuf arena_ref, arena_qer;
     cudaStream_t arena_stream = nullptr;
-    cudaEvent_t arena_ev = nullptr;
+    cudaEvent_t arena_ev[BSW_ARENA_PIECES] = {};     /* piece p of both arenas is on the device */
 };
 
 /* resident 2-bit reference (bsw_ref_upload), one copy per device */
@@ -171,7 +173,7 @@ DevCtx *ctx_acquire(DevRt &rt)
         sl.plan.reserve(sizeof(Plan));
     }
     CK(cudaStreamCreateWithFlags(&x->arena_stream, cudaStreamNonBlocking));
-    CK(cudaEventCreateWithFlags(&x->arena_ev, cudaEventDisableTiming));
+    for (cudaEvent_t &e : x->arena_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     x->cells.reserve(sizeof(unsigned long long));
     CK(cudaMemset(x->cells.p, 0, sizeof(unsigned long long)));
     return x;
@@ -206,6 +208,7 @@ struct Core {
     /* arenas declared with bsw_arena_begin */
     const uint8_t *arena_ref_h = nullptr, *arena_qer_h = nullptr;
     size_t arena_ref_n = 0, arena_qer_n = 0;
+    size_t arena_ref_piece = 0, arena_qer_piece = 0;     /* bytes per upload piece */
     bool arena_on = false;
 
     DevRt &rt(int i) { return devrt(devs[i]); }
@@ -595,10 +598,25 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
         DevCtx &x = *j.x;
         const bsw_seqpair_t *d_pairs = (const bsw_seqpair_t *)sl.pairs.p;
         /* query bases */
+        /* Arenas go up in BSW_ARENA_PIECES pieces behind the calls (bsw_arena_begin): the chunk waits for the piece that
+         * holds the last byte its (sampled) extents name, and tells prep_kernel that only the pieces up to there are valid,
+         * so a pair beyond them redoes the chunk with the exact extents instead of reading bytes still in flight. */
+        int piece = -1;
         if (in_arena_q) {
-            CK(cudaStreamWaitEvent(sl.stream, x.arena_ev, 0));
+            const long long hi = (qer - k.arena_qer_h) + std::max(qhi, 1ll) - 1;          /* arena offset of the last byte */
+            piece = std::max(piece, (int)std::min<long long>(BSW_ARENA_PIECES - 1, hi / (long long)k.arena_qer_piece));
+        }
+        if (in_arena_r) {
+            const long long hi = (ref - k.arena_ref_h) + std::max(rhi, 1ll) - 1;
+            piece = std::max(piece, (int)std::min<long long>(BSW_ARENA_PIECES - 1, hi / (long long)k.arena_ref_piece));
+        }
+        if (piece >= 0) CK(cudaStreamWaitEvent(sl.stream, x.arena_ev[piece], 0));
+        auto arena_valid = [&](size_t piece_bytes, size_t total) {
+            return (long long)std::min<unsigned long long>((unsigned long long)total, (unsigned long long)piece_bytes * (unsigned long long)(piece + 1));
+        };
+        if (in_arena_q) {
             j.d_qer = (const uint8_t *)x.arena_qer.p + (qer - k.arena_qer_h);
-            qlo = k.arena_qer_h - qer; qhi = qlo + (long long)k.arena_qer_n;
+            qlo = k.arena_qer_h - qer; qhi = qlo + (piece == BSW_ARENA_PIECES - 1 ? (long long)k.arena_qer_n : arena_valid(k.arena_qer_piece, k.arena_qer_n));
         } else {
             sl.qer.reserve((size_t)(qhi - qlo) + 64);
             if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
@@ -631,9 +649,8 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
             j.d_ref = (const uint8_t *)sl.reftmp.p;
             rlo = 0; rhi = cap;
         } else if (in_arena_r) {
-            CK(cudaStreamWaitEvent(sl.stream, x.arena_ev, 0));
             j.d_ref = (const uint8_t *)x.arena_ref.p + (ref - k.arena_ref_h);
-            rlo = k.arena_ref_h - ref; rhi = rlo + (long long)k.arena_ref_n;
+            rlo = k.arena_ref_h - ref; rhi = rlo + (piece == BSW_ARENA_PIECES - 1 ? (long long)k.arena_ref_n : arena_valid(k.arena_ref_piece, k.arena_ref_n));
         } else {
             sl.ref.reserve((size_t)(rhi - rlo) + 64);
             if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
@@ -947,15 +964,23 @@ void bsw_arena_begin(bsw_t *h, const uint8_t *seqBufRef, size_t refBytes, const 
     if (k.arena_on) die("bsw_arena_begin: an arena is already declared on this handle");
     k.arena_ref_h = seqBufRef; k.arena_ref_n = seqBufRef ? refBytes : 0;
     k.arena_qer_h = seqBufQer; k.arena_qer_n = seqBufQer ? qerBytes : 0;
+    /* pieces of at least 4 MB (a smaller copy does not reach the link's bandwidth), at most BSW_ARENA_PIECES of them */
+    k.arena_ref_piece = std::max<size_t>((size_t)4 << 20, ((k.arena_ref_n + BSW_ARENA_PIECES - 1) / BSW_ARENA_PIECES + 255) & ~(size_t)255);
+    k.arena_qer_piece = std::max<size_t>((size_t)4 << 20, ((k.arena_qer_n + BSW_ARENA_PIECES - 1) / BSW_ARENA_PIECES + 255) & ~(size_t)255);
     for (int i = 0; i < (int)k.devs.size(); ++i) {
         DevCtx &x = k.cx(i);
         CK(cudaSetDevice(x.dev));
         /* the slots may still read the previous arena's copies */
         for (Slot &sl : x.slot) slot_retire(x, sl);
         x.arena_ref.reserve(k.arena_ref_n + 64); x.arena_qer.reserve(k.arena_qer_n + 64);
-        if (k.arena_ref_n) CK(cudaMemcpyAsync(x.arena_ref.p, seqBufRef, k.arena_ref_n, cudaMemcpyHostToDevice, x.arena_stream));
-        if (k.arena_qer_n) CK(cudaMemcpyAsync(x.arena_qer.p, seqBufQer, k.arena_qer_n, cudaMemcpyHostToDevice, x.arena_stream));
-        CK(cudaEventRecord(x.arena_ev, x.arena_stream));
+        /* piece p of both arenas, then its event: the calls that follow start on the first pieces while the rest is in flight */
+        for (int pc = 0; pc < BSW_ARENA_PIECES; ++pc) {
+            const size_t r0 = std::min(k.arena_ref_n, k.arena_ref_piece * pc), r1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_ref_n : std::min(k.arena_ref_n, k.arena_ref_piece * (pc + 1));
+            const size_t q0 = std::min(k.arena_qer_n, k.arena_qer_piece * pc), q1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_qer_n : std::min(k.arena_qer_n, k.arena_qer_piece * (pc + 1));
+            if (r1 > r0) CK(cudaMemcpyAsync((char *)x.arena_ref.p + r0, seqBufRef + r0, r1 - r0, cudaMemcpyHostToDevice, x.arena_stream));
+            if (q1 > q0) CK(cudaMemcpyAsync((char *)x.arena_qer.p + q0, seqBufQer + q0, q1 - q0, cudaMemcpyHostToDevice, x.arena_stream));
+            CK(cudaEventRecord(x.arena_ev[pc], x.arena_stream));
+        }
         k.st.h2d_bytes += (long long)(k.arena_ref_n + k.arena_qer_n);
     }
     k.arena_on = true;

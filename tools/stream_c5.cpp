@@ -287,10 +287,10 @@ int main(int argc, char **argv)
     Tally sum;
     for (const Tally &t : tl) { sum.create_s += t.create_s; sum.call_s += t.call_s; sum.calls += t.calls; sum.creates += t.creates; sum.pairs += t.pairs; sum.retried += t.retried; }
     bsw_engine_stats_t es[8]; int nd = bsw_device_count(); if (nd > 8) nd = 8;
-    long long eb = 0, ep = 0, el = 0, emax = 0, ec = 0;
+    long long eb = 0, ep = 0, el = 0, emax = 0, ec = 0, eh2d = 0, ed2h = 0;
     double pf[8] = { 0 };
     for (int d = 0; d < nd; ++d) {
-        bsw_engine_get_stats(d, &es[d]); eb += es[d].batches; ep += es[d].pairs; el += es[d].kernel_launches; ec += es[d].calls;
+        bsw_engine_get_stats(d, &es[d]); eb += es[d].batches; ep += es[d].pairs; el += es[d].kernel_launches; ec += es[d].calls; eh2d += es[d].h2d_bytes; ed2h += es[d].d2h_bytes;
         emax = std::max<long long>(emax, es[d].max_batch_pairs);
         const int64_t v[8] = { es[d].scan_ns, es[d].reserve_ns, es[d].pack_ns, es[d].wait_ns, es[d].unpack_ns, es[d].packers_ns, es[d].submit_ns, es[d].flight_ns };
         for (int i = 0; i < 8; ++i) pf[i] += (double)v[i];
@@ -301,11 +301,12 @@ int main(int argc, char **argv)
            "\"handles_created\": %ld, \"us_per_create_destroy\": %.2f, \"engine_batches\": %lld, \"engine_pairs_per_batch\": %.1f, "
            "\"engine_max_batch\": %lld, \"engine_launches\": %lld, \"reps\": %d, "
            "\"us_per_call_scan_reserve_pack_wait_unpack\": [%.1f, %.1f, %.1f, %.1f, %.1f], "
-           "\"us_per_batch_packers_submit_flight\": [%.1f, %.1f, %.1f], \"devices\": %d}\n",
+           "\"us_per_batch_packers_submit_flight\": [%.1f, %.1f, %.1f], \"devices\": %d, "
+           "\"engine_h2d_bytes\": %lld, \"engine_d2h_bytes\": %lld}\n",
            W.mode == 1 ? "kswv" : "bsw", threads, pinned, per_task, (long long)W.nT, sum.pairs, sum.retried, best, sum.pairs / best,
            sum.calls, sum.calls ? sum.call_s / sum.calls * 1e6 : 0.0, sum.creates, sum.creates ? sum.create_s / sum.creates * 1e6 : 0.0,
            eb, eb ? (double)ep / eb : 0.0, emax, el, reps, pf[0] * pc, pf[1] * pc, pf[2] * pc, pf[3] * pc, pf[4] * pc,
-           pf[5] * pb, pf[6] * pb, pf[7] * pb, nd);
+           pf[5] * pb, pf[6] * pb, pf[7] * pb, nd, eh2d, ed2h);
     if (out) {
         FILE *f = fopen(out, "wb");
         if (!f) { perror(out); return 2; }
