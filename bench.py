@@ -31,6 +31,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -167,6 +168,10 @@ def oracle_sides(ora, d, tries, cores, simd=False):
     cells = [0]
 
     def side(P, r, q):
+        if tries == 1:                      # plain tier calls: one batch, in place on a copy
+            o = P.copy()
+            cells[0] += (ora.bsw_batch_avx2 if simd else ora.bsw_batch)(o, r, q, prm, W_BAND, cores)
+            return o, len(o)
         if not simd:
             o, n, c = ora.protocol_side(P, r, q, prm, W_BAND, tries, cores)
             cells[0] += c
@@ -187,7 +192,7 @@ def stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, task_reads, thre
     exe = os.path.join(ROOT, "tools", "bin", "stream_c5")
     if not os.path.exists(exe):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "tools"), "bin/stream_c5"])
-    tmp = os.path.join(ROOT, "gpurun_out", "stream_tmp"); os.makedirs(tmp, exist_ok=True)
+    tmp = os.path.join(tempfile.gettempdir(), "bsw_b200_stream"); os.makedirs(tmp, exist_ok=True)      # not under gpurun_out/: it is large
     w_in, w_out = os.path.join(tmp, f"w_{tag}.bin"), os.path.join(tmp, f"r_{tag}.bin")
     if not os.path.exists(w_in):
         ora.write_stream_workload(w_in, 0, L, R, lr, lq, rr, rq, ora.task_bounds(L["seqid"], n_reads, task_reads),
@@ -204,7 +209,7 @@ def stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, task_reads, thre
 
 def stream_cleanup(tag):
     try:
-        os.remove(os.path.join(ROOT, "gpurun_out", "stream_tmp", f"w_{tag}.bin"))
+        os.remove(os.path.join(tempfile.gettempdir(), "bsw_b200_stream", f"w_{tag}.bin"))
     except OSError:
         pass
 
@@ -521,6 +526,7 @@ def run_bsw(args):
         # the caller's protocol in C++: tools/stream_c5.cpp (worker threads over per-task slices, per-task shim objects, band retry)
         T = max(1, c.cores // max(1, c.world))
         info, raw = stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, args.task_reads, T, 0, 3, tag=f"c1_{c.rank}")
+        stream_cleanup(f"c1_{c.rank}")
         Ro2 = Ro.copy(); Ro2["h0"] = Rin["h0"]
         check("e2e left (C++ harness)", Lo, raw[:len(L)]); check("e2e right (C++ harness)", Ro2, raw[len(L):])
         e2e_ms = info["wall_s"] * 1e3 * args.steps

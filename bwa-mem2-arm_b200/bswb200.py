@@ -26,7 +26,7 @@ KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -87,6 +87,8 @@ def lib():
     L.bsw_dev_extendChained.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp]
     L.kswv_dev_getScores.restype = None
     L.kswv_dev_getScores.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, C.c_int, vp]
+    L.kswv_dev_align2.restype = None
+    L.kswv_dev_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, vp]
     L.bsw_host_alloc.restype = vp
     L.bsw_host_alloc.argtypes = [C.c_size_t]
     L.bsw_host_free.argtypes = [vp]
@@ -252,6 +254,10 @@ class kswv:
     def dev_getScores(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, phase=0, stream=0):
         self._L.kswv_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), _ptr(d_aln), numPairs,
                                    int(is8), int(phase), C.c_void_p(stream))
+
+    def dev_align2(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, stream=0):
+        """Forward pass, device-side hand-off and reverse pass of ksw_align2 in one submission (resident buffers)."""
+        self._L.kswv_dev_align2(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), _ptr(d_aln), numPairs, int(is8), C.c_void_p(stream))
 
     def stats(self):
         s = Stats()

@@ -46,6 +46,7 @@ struct Slot {
     cudaEvent_t done = nullptr;
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
     DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
+    DevBuf kx_off, kx_pairs, kx_ref, kx_qer;     /* device-side kswv hand-off (kswv_dev_align2) */
     DevBuf rpos, toff, reftmp;                    /* reference-resident calls: positions, target offsets, expanded targets */
     PinBuf h_res;                                 /* kswv phase 1: pinned landing area of a chunk's pass results */
     int *h_count = nullptr;                       /* pinned mailbox of the retry count */
@@ -169,7 +170,7 @@ DevCtx *ctx_acquire(DevRt &rt)
         CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&sl.dev_done, cudaEventDisableTiming));
         CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
-        CK(cudaHostAlloc((void **)&sl.h_count, sizeof(int), cudaHostAllocDefault));
+        CK(cudaHostAlloc((void **)&sl.h_count, 4 * sizeof(int), cudaHostAllocDefault));
         sl.plan.reserve(sizeof(Plan));
     }
     CK(cudaStreamCreateWithFlags(&x->arena_stream, cudaStreamNonBlocking));
@@ -1151,6 +1152,55 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
     launch_kswv(h->k, h->k.rt(0), x, sl, const_cast<bsw_seqpair_t *>(d_pairArray), d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase,
                 (cudaStream_t)stream);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
+}
+
+/* ksw_align2 for a resident batch in one submission: forward pass, hand-off on the device (which hits
+ * get a second pass, their reversed prefixes, the phase-1 records), reverse pass refining d_aln in place.  The pairs and
+ * the sequence buffers are not modified.  Two small read-backs (the hand-off totals, the second pass's histogram) on
+ * top of the first pass's histogram. */
+void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                     bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream)
+{
+    Core &k = h->k;
+    DevCtx &x = k.cx(0);
+    DevRt &rt = k.rt(0);
+    CK(cudaSetDevice(x.dev));
+    cudaStream_t s = (cudaStream_t)stream;
+    k.st.calls++;
+    const int n = numPairs;
+    if (n <= 0) return;
+    Slot &sl = dev_slot(x, s, false);
+    bsw_seqpair_t *d_pairs = const_cast<bsw_seqpair_t *>(d_pairArray);
+    launch_kswv(k, rt, x, sl, d_pairs, d_seqBufRef, d_seqBufQer, d_aln, n, is8, 0, s);
+    /* hand-off: three exclusive scans (slot, target bytes, query bytes), totals, fill */
+    sl.kx_off.reserve((size_t)n * 3 * sizeof(int) + 4 * sizeof(int));
+    int *off_k = (int *)sl.kx_off.p, *off_r = off_k + n, *off_q = off_r + n, *totals = off_q + n;
+    for (int which = 0; which < 3; ++which) {
+        auto it = thrust::make_transform_iterator(thrust::make_counting_iterator(0), HandoffLens{ d_pairs, d_aln, which });
+        size_t tmp_bytes = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, off_k + (size_t)which * n, n, s));
+        sl.cubtmp.reserve(tmp_bytes);
+        CK(cub::DeviceScan::ExclusiveSum(sl.cubtmp.p, tmp_bytes, it, off_k + (size_t)which * n, n, s));
+    }
+    /* the fill needs the scratch sizes: last offsets + last lengths */
+    kswv_handoff_totals_kernel<<<1, 32, 0, s>>>(d_pairs, d_aln, n, off_k, off_r, off_q, totals);
+    CK(cudaMemcpyAsync(sl.h_count, totals, 3 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s));
+    const int n1 = sl.h_count[0], tot_r = sl.h_count[1], tot_q = sl.h_count[2];
+    k.st.kernel_launches += 7;
+    if (n1 < 0 || tot_r < 0 || tot_q < 0) die("kswv_dev_align2: hand-off sizes overflow 31 bits (split the batch)");
+    if (n1 > 0) {
+        sl.kx_pairs.reserve((size_t)n1 * sizeof(bsw_seqpair_t));
+        sl.kx_ref.reserve((size_t)tot_r + 64); sl.kx_qer.reserve((size_t)tot_q + 64);
+        kswv_handoff_fill_kernel<<<(int)(((long long)n * 8 + 255) / 256), 256, 0, s>>>(d_pairs, d_aln, n, d_seqBufRef, d_seqBufQer, off_k, off_r, off_q,
+                                                                                  (bsw_seqpair_t *)sl.kx_pairs.p, (uint8_t *)sl.kx_ref.p,
+                                                                                  (uint8_t *)sl.kx_qer.p, totals);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+        launch_kswv(k, rt, x, sl, (bsw_seqpair_t *)sl.kx_pairs.p, (const uint8_t *)sl.kx_ref.p, (const uint8_t *)sl.kx_qer.p, d_aln, n1, is8, 1, s);
+    }
+    CK(cudaEventRecord(sl.dev_done, s));
 }
 
 void *bsw_host_alloc(size_t bytes)

@@ -515,6 +515,61 @@ __global__ void proto_chain_h0_kernel(const bsw_seqpair_t *__restrict__ left, in
 }
 
 
+/* ------------------------------------------------------------------ kswv hand-off on the device
+ * ksw_align2 between its two passes (mem_sam_pe_batch does it on the host between the getScores calls): a hit with
+ * KSW_XSTART and not (KSW_XSUBO and score < minsc) gets a second pass over the REVERSED prefixes target[0..te],
+ * query[0..qe] with xtra = KSW_XSTOP | score; its result refines aln[i] (kswv_store, phase 1).
+ * handoff_len: per pair the lengths of the two reversed prefixes (0: no second pass), rounded up to 4 for the scan;
+ * handoff_fill: 8 lanes per pair write the reversed bases and the phase-1 record (regid = seqid = i). */
+struct HandoffLens {
+    const bsw_seqpair_t *p; const bsw_kswr_t *a; int which;       /* 0: 1 per qualifying pair, 1: target bytes, 2: query bytes */
+    __host__ __device__ int operator()(int i) const
+    {
+        const int xtra = p[i].h0, sc = a[i].score;
+        const bool ok = (xtra & KSW_XSTART_) != 0 && !((xtra & KSW_XSUBO_) != 0 && sc < (xtra & 0xffff));
+        if (!ok) return 0;
+        if (which == 0) return 1;
+        const int l = (which == 1 ? a[i].te : a[i].qe) + 1;
+        return l > 0 ? (l + 3) & ~3 : 0;
+    }
+};
+
+__global__ void kswv_handoff_totals_kernel(const bsw_seqpair_t *__restrict__ pairs, const bsw_kswr_t *__restrict__ aln, int n,
+                                           const int *__restrict__ off_k, const int *__restrict__ off_r, const int *__restrict__ off_q,
+                                           int *__restrict__ totals)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const int g = n - 1;
+    const HandoffLens one{ pairs, aln, 0 }, lr{ pairs, aln, 1 }, lq{ pairs, aln, 2 };
+    totals[0] = off_k[g] + one(g); totals[1] = off_r[g] + lr(g); totals[2] = off_q[g] + lq(g);
+}
+
+__global__ void kswv_handoff_fill_kernel(const bsw_seqpair_t *__restrict__ pairs, const bsw_kswr_t *__restrict__ aln, int n,
+                                         const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                                         const int *__restrict__ off_k, const int *__restrict__ off_r, const int *__restrict__ off_q,
+                                         bsw_seqpair_t *__restrict__ out, uint8_t *__restrict__ rref, uint8_t *__restrict__ rqer,
+                                         int *__restrict__ totals)
+{
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3, lane = threadIdx.x & 7;
+    if (g >= n) return;
+    const HandoffLens one{ pairs, aln, 0 };
+    const bool ok = one(g) != 0;
+    (void)totals;
+    if (!ok) return;
+    const int l1 = aln[g].te + 1, l2 = aln[g].qe + 1, k = off_k[g];
+    const long long r0 = pairs[g].idr, q0 = pairs[g].idq;
+    uint8_t *dr = rref + off_r[g], *dq = rqer + off_q[g];
+    for (int j = lane; j < l1; j += 8) dr[j] = ref[r0 + (l1 - 1 - j)];
+    for (int j = lane; j < l2; j += 8) dq[j] = qer[q0 + (l2 - 1 - j)];
+    if (lane == 0) {
+        bsw_seqpair_t o;
+        o.idr = off_r[g]; o.idq = off_q[g]; o.id = k; o.len1 = l1 > 0 ? l1 : 0; o.len2 = l2 > 0 ? l2 : 0;
+        o.h0 = KSW_XSTOP_ | aln[g].score; o.seqid = g; o.regid = g;
+        o.score = o.tle = o.gtle = o.qle = o.gscore = o.max_off = 0;
+        out[k] = o;
+    }
+}
+
 /* ------------------------------------------------------------------ resident reference
  * The reference lives in HBM in bwa's .pac layout: base x of the forward strand in byte x >> 2, bits ((~x & 3) << 1).
  * Coordinates are bwa's doubled ones (bns_get_seq / bns_fetch_seq): 0 <= x < l_pac is the forward strand, l_pac <= x <

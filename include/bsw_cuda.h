@@ -194,6 +194,14 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
                         const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs,
                         int is8, int phase, void *stream);
 
+/* ksw_align2 for a resident batch in ONE submission (replaces mem_sam_pe_batch's sequence getScores(phase 0) -> host
+ * hand-off -> getScores(phase 1), bwa-mem2 src/bwamem_pair.cpp): forward pass into d_aln, hand-off on
+ * the device (hits with KSW_XSTART and not (KSW_XSUBO and score < minsc) get their prefixes target[0..te], query[0..qe]
+ * reversed and a KSW_XSTOP | score record), reverse pass refining d_aln[i].tb / .qb in place.  d_pairArray and the
+ * sequence buffers are read only.  Blocks the host for three small read-backs; returns with the last kernels queued. */
+void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
+                     const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream);
+
 /* pinned host arenas for the caller's SeqPair / sequence buffers (optional:
  * pageable memory works, pinned memory lets the copies run at link speed). */
 void *bsw_host_alloc(size_t bytes);

@@ -252,6 +252,38 @@ def test_kswv_c4(ora, ks, bsw):
         assert (ao["tb"] >= 0).mean() > 0.5
 
 
+def test_kswv_dev_align2(ora, bsw):
+    """kswv_dev_align2: forward pass, hand-off and reverse pass on the device in one submission equal
+    ksw_align2 per pair -- 8-bit and 16-bit batches, hits below minsc (no second pass), queries with N, the 32-bit general
+    kernel for long queries, a batch in which no hit qualifies, an empty batch."""
+    import torch
+    prm = ora.make_params()
+    ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    st = torch.cuda.current_stream().cuda_stream
+    cases = []
+    P, r, q = ora.gen_kswv(20000); cases.append((P, r, q, 1))
+    P, r, q = ora.gen_kswv(3000, qlen=250, tmin=400, tmax=700, seed=0xC5); cases.append((P, r, q, 0))
+    P, r, q = ora.gen_random(3000, 0, 120, 0, 250, sim=0.75, p_n=0.03, seed=31)
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 30; cases.append((P, r, q, 1))
+    P, r, q = ora.gen_kswv(200, qlen=400, tmin=600, tmax=900, seed=10, xtra=ora.KSW_XSUBO | ora.KSW_XSTART | 19); cases.append((P, r, q, 0))
+    P, r, q = ora.gen_kswv(500, seed=77, xtra=ora.KSW_XSUBO | ora.KSW_XBYTE | 19); cases.append((P, r, q, 1))       # no KSW_XSTART
+    for P, r, q, is8 in cases:
+        flag = P["h0"].copy()
+        if is8:
+            assert ((flag & ora.KSW_XBYTE) != 0).all()
+        ao, _ = ora.kswv_align2_batch(P, r, q, prm, 8)
+        dp = torch.from_numpy(P.view(np.uint8).reshape(-1).copy()).cuda()
+        dr, dq = torch.from_numpy(r).cuda(), torch.from_numpy(q).cuda()
+        da = torch.zeros(len(P) * 28, dtype=torch.uint8, device="cuda")
+        ks.dev_align2(dp, dr, dq, da, len(P), is8, st)
+        torch.cuda.synchronize()
+        ag = da.cpu().numpy().view(bsw.KSWR)
+        assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
+        assert (dp.cpu().numpy().view(bsw.SEQPAIR) == P).all()          # inputs untouched
+    ks.dev_align2(dp, dr, dq, da, 0, 1, st)
+    ks.close()
+
+
 def test_kswv_edge(ora, ks, bsw):
     prm = ora.make_params()
     P, r, q = ora.gen_random(2000, 0, 60, 0, 150, sim=0.7, p_n=0.05, seed=3)
