@@ -20,13 +20,14 @@ SEQPAIR = np.dtype([(n, "<i4") for n in (
     "idr", "idq", "id", "len1", "len2", "h0", "seqid", "regid",
     "score", "tle", "gtle", "qle", "gscore", "max_off")])
 KSWR = np.dtype([(n, "<i4") for n in ("score", "te", "qe", "score2", "te2", "tb", "qb")])
+GLOBALJOB = np.dtype([(n, "<i4") for n in ("idr", "idq", "tlen", "qlen", "w", "score", "n_cigar", "cigar_off")])
 KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 
 # every symbol include/bsw_cuda.h declares (tests check the .so exports all of them)
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -87,6 +88,10 @@ def lib():
     L.bsw_dev_extendChained.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp]
     L.kswv_dev_getScores.restype = None
     L.kswv_dev_getScores.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, C.c_int, vp]
+    L.bsw_global2.restype = C.c_int64
+    L.bsw_global2.argtypes = [vp, vp, i32, vp, vp, vp, C.c_int64]
+    L.bsw_dev_global2.restype = C.c_int64
+    L.bsw_dev_global2.argtypes = [vp, vp, i32, vp, vp, vp, C.c_int64, i32, vp]
     L.kswv_dev_align2.restype = None
     L.kswv_dev_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, vp]
     L.bsw_host_alloc.restype = vp
@@ -203,6 +208,20 @@ class BandedPairWiseSW:
 
     def set_wide_max(self, pairs):
         self._L.bsw_set_wide_max(self._h, int(pairs))
+
+    def global2(self, jobs, seqBufRef, seqBufQer, cigar=None):
+        """Batched ksw_global2 (CIGAR generation).  jobs: GLOBALJOB array, filled in place.  Returns the dense op array."""
+        assert jobs.dtype == GLOBALJOB and jobs.flags.c_contiguous
+        if cigar is None:
+            cigar = np.zeros(int((jobs["tlen"].astype(np.int64) + jobs["qlen"]).sum()) + 16, dtype=np.uint32)
+        tot = self._L.bsw_global2(self._h, _ptr(jobs), len(jobs), _ptr(seqBufRef), _ptr(seqBufQer), _ptr(cigar), len(cigar))
+        if tot < 0:
+            raise RuntimeError(f"cigar buffer too small: {-tot} ops needed")
+        return cigar[:tot]
+
+    def dev_global2(self, d_jobs, numJobs, d_ref, d_qer, d_cigar, cigarCap, maxBand, stream=0):
+        return self._L.bsw_dev_global2(self._h, _ptr(d_jobs), numJobs, _ptr(d_ref), _ptr(d_qer), _ptr(d_cigar), int(cigarCap),
+                                       int(maxBand), C.c_void_p(stream))
 
     def set_wide_policy(self, wide_max, wide_lat, wide_split):
         self._L.bsw_set_wide_policy(self._h, int(wide_max), int(wide_lat), int(wide_split))

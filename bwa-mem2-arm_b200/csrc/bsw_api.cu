@@ -47,9 +47,11 @@ struct Slot {
     DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
     DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
     DevBuf kx_off, kx_pairs, kx_ref, kx_qer;     /* device-side kswv hand-off (kswv_dev_align2) */
+    DevBuf gx_eh, gx_z, gx_zoff, gx_coff, gx_jobs, gx_cigar;   /* CIGAR generation (bsw_global2) */
     DevBuf rpos, toff, reftmp;                    /* reference-resident calls: positions, target offsets, expanded targets */
     PinBuf h_res;                                 /* kswv phase 1: pinned landing area of a chunk's pass results */
     int *h_count = nullptr;                       /* pinned mailbox of the retry count */
+    long long *h_tot = nullptr;                   /* pinned mailbox of 64-bit totals */
     Plan *h_plan = nullptr;                       /* pinned mailbox of the histogram */
     bool busy = false;                            /* a chunk is in flight on this slot */
     cudaEvent_t dev_done = nullptr;               /* end of the last device-resident call that used this slot's scratch */
@@ -68,6 +70,7 @@ struct DevCtx {
     DevBuf arena_ref, arena_qer;
     cudaStream_t arena_stream = nullptr;
     cudaEvent_t arena_ev[BSW_ARENA_PIECES] = {};     /* piece p of both arenas is on the device */
+    int arena_enq = 0;                               /* pieces whose copies have been enqueued */
 };
 
 /* resident 2-bit reference (bsw_ref_upload), one copy per device */
@@ -171,6 +174,7 @@ DevCtx *ctx_acquire(DevRt &rt)
         CK(cudaEventCreateWithFlags(&sl.dev_done, cudaEventDisableTiming));
         CK(cudaHostAlloc((void **)&sl.h_plan, sizeof(Plan), cudaHostAllocDefault));
         CK(cudaHostAlloc((void **)&sl.h_count, 4 * sizeof(int), cudaHostAllocDefault));
+        CK(cudaHostAlloc((void **)&sl.h_tot, 4 * sizeof(long long), cudaHostAllocDefault));
         sl.plan.reserve(sizeof(Plan));
     }
     CK(cudaStreamCreateWithFlags(&x->arena_stream, cudaStreamNonBlocking));
@@ -199,6 +203,7 @@ struct Core {
     bsw_stats_t st;
     int timing = 0;
     int count_cells = 0;
+    int trace = 0;                   /* BSW_CUDA_TRACE: host-side timing of every direct call on stderr */
     int chunk_pairs = 1 << 19;
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
@@ -255,6 +260,7 @@ void core_init(Core &k, int mode)
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
+    k.trace = env_int("BSW_CUDA_TRACE", 0);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
     k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 32768);
     k.wide_lat = env_int("BSW_CUDA_WIDE_LAT", 8192);
@@ -574,6 +580,20 @@ void slot_retire(DevCtx &x, Slot &sl)
     sl.busy = false;
 }
 
+/* enqueues the copies of the arena pieces [x.arena_enq, piece] on the device's arena stream, each followed by its event */
+void arena_pieces_upto(Core &k, DevCtx &x, int piece)
+{
+    for (; x.arena_enq <= piece; ++x.arena_enq) {
+        const int pc = x.arena_enq;
+        const size_t r0 = std::min(k.arena_ref_n, k.arena_ref_piece * pc), r1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_ref_n : std::min(k.arena_ref_n, k.arena_ref_piece * (pc + 1));
+        const size_t q0 = std::min(k.arena_qer_n, k.arena_qer_piece * pc), q1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_qer_n : std::min(k.arena_qer_n, k.arena_qer_piece * (pc + 1));
+        if (r1 > r0) CK(cudaMemcpyAsync((char *)x.arena_ref.p + r0, k.arena_ref_h + r0, r1 - r0, cudaMemcpyHostToDevice, x.arena_stream));
+        if (q1 > q0) CK(cudaMemcpyAsync((char *)x.arena_qer.p + q0, k.arena_qer_h + q0, q1 - q0, cudaMemcpyHostToDevice, x.arena_stream));
+        CK(cudaEventRecord(x.arena_ev[pc], x.arena_stream));
+        k.st.h2d_bytes += (long long)(r1 - r0) + (long long)(q1 - q0);
+    }
+}
+
 /* ---- direct BSW call: chunked, pipelined, sharded ---------------------------------------------
  * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
  * devices.  Each chunk uploads its 56-byte records and only the byte ranges of the sequence buffers its pairs
@@ -611,7 +631,7 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
             const long long hi = (ref - k.arena_ref_h) + std::max(rhi, 1ll) - 1;
             piece = std::max(piece, (int)std::min<long long>(BSW_ARENA_PIECES - 1, hi / (long long)k.arena_ref_piece));
         }
-        if (piece >= 0) CK(cudaStreamWaitEvent(sl.stream, x.arena_ev[piece], 0));
+        if (piece >= 0) { arena_pieces_upto(k, x, piece); CK(cudaStreamWaitEvent(sl.stream, x.arena_ev[piece], 0)); }
         auto arena_valid = [&](size_t piece_bytes, size_t total) {
             return (long long)std::min<unsigned long long>((unsigned long long)total, (unsigned long long)piece_bytes * (unsigned long long)(piece + 1));
         };
@@ -700,13 +720,24 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
     };
     /* chunk c+nd is uploading while chunk c waits for its histogram: the copy engine never idles */
     const int ahead = nd * std::max(1, std::min(BSW_NSLOT - 2, k.ahead));   /* chunks uploading ahead of the one waiting */
+    const bool trace = k.trace != 0;
+    long long t_a = 0, t_b = 0, t0 = trace ? now_ns() : 0;
     for (int ci = 0; ci < std::min(ahead, nchunks); ++ci) stage_a(ci);
+    if (trace) t_a += now_ns() - t0;
     for (int ci = 0; ci < nchunks; ++ci) {
+        long long t1 = trace ? now_ns() : 0;
         if (ci + ahead < nchunks) stage_a(ci + ahead);
+        long long t2 = trace ? now_ns() : 0;
         stage_b(ci);
+        if (trace) { t_a += t2 - t1; t_b += now_ns() - t2; }
     }
+    long long t3 = trace ? now_ns() : 0;
     for (size_t i = 0; i < k.ctx.size(); ++i)
         if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
+    if (trace)
+        fprintf(stderr, "[bsw-b200] direct call: %d pairs, %d chunks, total %.3f ms: stage A (retire slot + enqueue uploads, prep, sort) %.3f, "
+                        "stage B (wait histogram + launch DP + enqueue download) %.3f, final drain %.3f\n",
+                n, nchunks, (now_ns() - t0) * 1e-6, t_a * 1e-6, t_b * 1e-6, (now_ns() - t3) * 1e-6);
 }
 
 /* ---- direct kswv call: chunks of BSW_CUDA_KSWV_CHUNK pairs, pipelined over the slots like BSW -----
@@ -974,15 +1005,9 @@ void bsw_arena_begin(bsw_t *h, const uint8_t *seqBufRef, size_t refBytes, const 
         /* the slots may still read the previous arena's copies */
         for (Slot &sl : x.slot) slot_retire(x, sl);
         x.arena_ref.reserve(k.arena_ref_n + 64); x.arena_qer.reserve(k.arena_qer_n + 64);
-        /* piece p of both arenas, then its event: the calls that follow start on the first pieces while the rest is in flight */
-        for (int pc = 0; pc < BSW_ARENA_PIECES; ++pc) {
-            const size_t r0 = std::min(k.arena_ref_n, k.arena_ref_piece * pc), r1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_ref_n : std::min(k.arena_ref_n, k.arena_ref_piece * (pc + 1));
-            const size_t q0 = std::min(k.arena_qer_n, k.arena_qer_piece * pc), q1 = pc == BSW_ARENA_PIECES - 1 ? k.arena_qer_n : std::min(k.arena_qer_n, k.arena_qer_piece * (pc + 1));
-            if (r1 > r0) CK(cudaMemcpyAsync((char *)x.arena_ref.p + r0, seqBufRef + r0, r1 - r0, cudaMemcpyHostToDevice, x.arena_stream));
-            if (q1 > q0) CK(cudaMemcpyAsync((char *)x.arena_qer.p + q0, seqBufQer + q0, q1 - q0, cudaMemcpyHostToDevice, x.arena_stream));
-            CK(cudaEventRecord(x.arena_ev[pc], x.arena_stream));
-        }
-        k.st.h2d_bytes += (long long)(k.arena_ref_n + k.arena_qer_n);
+        /* the pieces go up lazily, each just before the first chunk that needs it (arena_pieces_upto): copies are served in
+         * submission order, so enqueueing the whole arena here would put every chunk's records behind it */
+        x.arena_enq = 0;
     }
     k.arena_on = true;
 }
@@ -1201,6 +1226,137 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
         launch_kswv(k, rt, x, sl, (bsw_seqpair_t *)sl.kx_pairs.p, (const uint8_t *)sl.kx_ref.p, (const uint8_t *)sl.kx_qer.p, d_aln, n1, is8, 1, s);
     }
     CK(cudaEventRecord(sl.dev_done, s));
+}
+
+/* ---- CIGAR generation ------------------------------------------------------ */
+__global__ void global2_last_kernel(const bswk::GJob *jobs, int count, const long long *zoff, long long *out)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    const bswk::GJob g = jobs[count - 1];
+    out[0] = zoff[count - 1] + bswk::global2_zwords(g.tlen, g.qlen, g.w);
+}
+__global__ void global2_last_cigar_kernel(const bswk::GJob *jobs, int count, const int *coff, long long *out)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    long long bad = 0;
+    out[1] = (long long)coff[count - 1] + (jobs[count - 1].n_cigar > 0 ? jobs[count - 1].n_cigar : 0);
+    (void)bad;
+}
+__global__ void global2_count_bad_kernel(const bswk::GJob *jobs, int count, int *bad)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < count && jobs[t].n_cigar < 0) atomicAdd(bad, 1);
+}
+
+/* resident jobs and sequences; ops to d_cigar (dense, job order).  Returns the total number of ops; the ops of the jobs
+ * that fit below cigarCap are written, the others only counted. */
+static long long dev_global2(Core &k, DevCtx &x, Slot &sl, bswk::GJob *d_jobs, int n, const uint8_t *d_ref, const uint8_t *d_qer,
+                             uint32_t *d_cigar, long long cap, int max_w, cudaStream_t s)
+{
+    const int M = 2 * std::max(0, max_w) + 2;
+    const int chunk_max = std::max(1024, env_int("BSW_CUDA_GLOBAL_CHUNK", 1 << 18));
+    long long total = 0;
+    for (int first = 0; first < n; first += chunk_max) {
+        const int cnt = std::min(chunk_max, n - first);
+        bswk::GJob *jb = d_jobs + first;
+        sl.gx_zoff.reserve((size_t)cnt * sizeof(long long));
+        sl.gx_coff.reserve((size_t)cnt * sizeof(int) + 16);
+        sl.gx_eh.reserve((size_t)cnt * (size_t)M * sizeof(int2));
+        sl.px_count.reserve(sizeof(int));
+        {
+            auto it = thrust::make_transform_iterator(thrust::make_counting_iterator(0), GlobalZWords{ jb });
+            size_t tmp = 0;
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, it, (long long *)sl.gx_zoff.p, cnt, s));
+            sl.cubtmp.reserve(tmp);
+            CK(cub::DeviceScan::ExclusiveSum(sl.cubtmp.p, tmp, it, (long long *)sl.gx_zoff.p, cnt, s));
+        }
+        global2_last_kernel<<<1, 32, 0, s>>>(jb, cnt, (const long long *)sl.gx_zoff.p, (long long *)sl.cubtmp.p);
+        CK(cudaMemcpyAsync(sl.h_tot, sl.cubtmp.p, sizeof(long long), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        const long long zwords = sl.h_tot[0];
+        sl.gx_z.reserve((size_t)(zwords + 4) * sizeof(uint32_t));
+        global2_dp_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(jb, cnt, d_ref, d_qer, k.c, (int2 *)sl.gx_eh.p, M, (uint32_t *)sl.gx_z.p,
+                                                         (const long long *)sl.gx_zoff.p, (unsigned long long *)x.cells.p);
+        CK(cudaGetLastError());
+        {
+            auto it = thrust::make_transform_iterator(thrust::make_counting_iterator(0), GlobalNCigar{ jb });
+            size_t tmp = 0;
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, it, (int *)sl.gx_coff.p, cnt, s));
+            sl.cubtmp.reserve(tmp + 64);
+            CK(cub::DeviceScan::ExclusiveSum(sl.cubtmp.p, tmp, it, (int *)sl.gx_coff.p, cnt, s));
+        }
+        CK(cudaMemsetAsync(sl.px_count.p, 0, sizeof(int), s));
+        global2_count_bad_kernel<<<(cnt + 255) / 256, 256, 0, s>>>(jb, cnt, (int *)sl.px_count.p);
+        global2_emit_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(jb, cnt, (const uint32_t *)sl.gx_z.p, (const long long *)sl.gx_zoff.p,
+                                                           (const int *)sl.gx_coff.p, total, d_cigar, cap);
+        global2_last_cigar_kernel<<<1, 32, 0, s>>>(jb, cnt, (const int *)sl.gx_coff.p, (long long *)sl.gx_zoff.p);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(sl.h_tot, (const long long *)sl.gx_zoff.p + 1, sizeof(long long), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(sl.h_count, sl.px_count.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if (*sl.h_count) die("bsw_global2: a job has a negative length or band, or a band above maxBand");
+        total += sl.h_tot[0];
+        if (total > 0x7fffffffll) die("bsw_global2: more than 2^31 CIGAR ops in one call (split the batch)");
+        k.st.kernel_launches += 9;
+        k.st.pairs += cnt;
+    }
+    return total;
+}
+
+int64_t bsw_dev_global2(bsw_t *h, bsw_global_job_t *d_jobs, int32_t numJobs, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                        uint32_t *d_cigar, int64_t cigarCap, int32_t maxBand, void *stream)
+{
+    Core &k = h->k;
+    DevCtx &x = k.cx(0);
+    CK(cudaSetDevice(x.dev));
+    k.st.calls++;
+    if (numJobs <= 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    Slot &sl = dev_slot(x, s, false);
+    const long long tot = dev_global2(k, x, sl, (bswk::GJob *)d_jobs, numJobs, d_seqBufRef, d_seqBufQer, d_cigar, cigarCap, maxBand, s);
+    CK(cudaEventRecord(sl.dev_done, s));
+    return tot;
+}
+
+int64_t bsw_global2(bsw_t *h, bsw_global_job_t *jobs, int32_t numJobs, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                    uint32_t *cigar, int64_t cigarCap)
+{
+    Core &k = h->k;
+    k.st.calls++;
+    if (numJobs <= 0) return 0;
+    if (!jobs || !seqBufRef || !seqBufQer || (!cigar && cigarCap > 0)) die("null buffer passed to bsw_global2");
+    DevCtx &x = k.cx(0);
+    CK(cudaSetDevice(x.dev));
+    Slot &sl = x.slot[0];
+    slot_retire(x, sl);
+    cudaStream_t s = sl.stream;
+    long long rlo = (long long)1 << 62, rhi = 0, qlo = (long long)1 << 62, qhi = 0;
+    int max_w = 0, bad = 0;
+    for (int i = 0; i < numJobs; ++i) {
+        const bsw_global_job_t &g = jobs[i];
+        if (g.tlen < 0 || g.qlen < 0 || g.w < 0) { ++bad; continue; }
+        rlo = std::min<long long>(rlo, g.idr); rhi = std::max<long long>(rhi, (long long)g.idr + g.tlen);
+        qlo = std::min<long long>(qlo, g.idq); qhi = std::max<long long>(qhi, (long long)g.idq + g.qlen);
+        max_w = std::max(max_w, g.w);
+    }
+    if (bad) die("bsw_global2: a job has a negative length or band");
+    if (rhi <= rlo) { rlo = 0; rhi = 0; }
+    if (qhi <= qlo) { qlo = 0; qhi = 0; }
+    sl.gx_jobs.reserve((size_t)numJobs * sizeof(bsw_global_job_t));
+    sl.ref.reserve((size_t)(rhi - rlo) + 64); sl.qer.reserve((size_t)(qhi - qlo) + 64);
+    sl.gx_cigar.reserve((size_t)std::max<long long>(cigarCap, 1) * sizeof(uint32_t));
+    CK(cudaMemcpyAsync(sl.gx_jobs.p, jobs, (size_t)numJobs * sizeof(bsw_global_job_t), cudaMemcpyHostToDevice, s));
+    if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, seqBufRef + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, s));
+    if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, seqBufQer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, s));
+    k.st.h2d_bytes += (long long)numJobs * sizeof(bsw_global_job_t) + (rhi - rlo) + (qhi - qlo);
+    const long long tot = dev_global2(k, x, sl, (bswk::GJob *)sl.gx_jobs.p, numJobs, (const uint8_t *)sl.ref.p - rlo, (const uint8_t *)sl.qer.p - qlo,
+                                      (uint32_t *)sl.gx_cigar.p, cigarCap, max_w, s);
+    CK(cudaMemcpyAsync(jobs, sl.gx_jobs.p, (size_t)numJobs * sizeof(bsw_global_job_t), cudaMemcpyDeviceToHost, s));
+    const long long fit = std::min<long long>(tot, cigarCap);
+    if (fit > 0) CK(cudaMemcpyAsync(cigar, sl.gx_cigar.p, (size_t)fit * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    k.st.d2h_bytes += (long long)numJobs * sizeof(bsw_global_job_t) + fit * 4;
+    return tot <= cigarCap ? tot : -tot;
 }
 
 void *bsw_host_alloc(size_t bytes)

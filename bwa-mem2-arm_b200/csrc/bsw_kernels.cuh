@@ -24,6 +24,7 @@
 #include "bsw_core2.cuh"
 #include "kswv_core.cuh"
 #include "bsw_wide.cuh"
+#include "global_core.cuh"
 
 namespace bswk {
 
@@ -568,6 +569,52 @@ __global__ void kswv_handoff_fill_kernel(const bsw_seqpair_t *__restrict__ pairs
         o.score = o.tle = o.gtle = o.qle = o.gscore = o.max_off = 0;
         out[k] = o;
     }
+}
+
+/* ------------------------------------------------------------------ CIGAR generation (global_core.cuh)
+ * global2_dp_kernel: DP + op count of jobs [first, first + count); thread t keeps its rolling row in eh[slot * count + t]
+ * and its direction words at z + zoff[t].  global2_emit_kernel: second backtrack, ops to cigar[base + coff[t] ...]. */
+struct GlobalZWords {
+    const GJob *j;
+    __host__ __device__ long long operator()(int i) const { return global2_zwords(j[i].tlen, j[i].qlen, j[i].w); }
+};
+struct GlobalNCigar {
+    const GJob *j;
+    __host__ __device__ int operator()(int i) const { return j[i].n_cigar > 0 ? j[i].n_cigar : 0; }
+};
+
+__global__ void global2_dp_kernel(GJob *__restrict__ jobs, int count, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                                  Const c, int2 *__restrict__ eh, int M, uint32_t *__restrict__ z, const long long *__restrict__ zoff,
+                                  unsigned long long *cells)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long my_cells = 0;
+    if (t < count) {
+        GJob g = jobs[t];
+        if (g.tlen < 0 || g.qlen < 0 || g.w < 0 || 2 * g.w + 2 > M) { jobs[t].score = 0; jobs[t].n_cigar = -1; }     /* contract: reported by the host */
+        else {
+            long long cl = 0;
+            uint32_t *zt = z + zoff[t];
+            g.score = global2_dp(c, g.tlen, g.qlen, g.w, ref + g.idr, qer + g.idq, eh + t, (long long)count, M, zt, cl);
+            g.n_cigar = global2_backtrack<false>(g.tlen, g.qlen, g.w, zt, nullptr, 0);
+            jobs[t].score = g.score; jobs[t].n_cigar = g.n_cigar;
+            my_cells = (unsigned long long)cl;
+        }
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if ((threadIdx.x & 31) == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+__global__ void global2_emit_kernel(GJob *__restrict__ jobs, int count, const uint32_t *__restrict__ z, const long long *__restrict__ zoff,
+                                    const int *__restrict__ coff, long long base, uint32_t *__restrict__ cigar, long long cap)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const GJob g = jobs[t];
+    if (g.n_cigar < 0) return;
+    const long long off = base + coff[t];
+    jobs[t].cigar_off = (int)off;
+    if (off + g.n_cigar <= cap) global2_backtrack<true>(g.tlen, g.qlen, g.w, z + zoff[t], cigar + off, g.n_cigar);
 }
 
 /* ------------------------------------------------------------------ resident reference

@@ -202,6 +202,28 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
 void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                      const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream);
 
+/* ---- CIGAR generation ------------------------------------------------------------
+ * Batched bwa ksw.c ksw_global2 (bwa-mem2 src/ksw.cpp), the banded global alignment with backtrack that mem_reg2aln
+ * reaches through bwa_gen_cigar2 once per reported alignment: one job per alignment, scoring from the handle
+ * (a / -b / ambiguous, gap open / extend; zdrop and end_bonus do not apply).  Outputs per job: the score, n_cigar, and
+ * its ops (len << 4 | op, op 0 = M, 1 = I, 2 = D, as bwa stores them) at cigar[cigar_off .. cigar_off + n_cigar):
+ * dense, in job order.  Contract: w >= |tlen - qlen| (bwa_gen_cigar2 guarantees + 3; below it ksw_global2's backtrack
+ * leaves its matrix and the result is unspecified there as here).  bwa_gen_cigar2's surroundings (the no-gap shortcut, the band rule, NM / MD) stay in the caller. */
+typedef struct bsw_global_job {
+    int32_t idr, idq;        /* target = seqBufRef + idr, query = seqBufQer + idq */
+    int32_t tlen, qlen, w;   /* lengths and band */
+    int32_t score;           /* out */
+    int32_t n_cigar;         /* out */
+    int32_t cigar_off;       /* out */
+} bsw_global_job_t;
+/* host buffers; synchronous.  Returns the total number of ops; if they exceed cigarCap returns minus the total (scores
+ * and n_cigar are valid, the ops of the jobs that end below cigarCap are written). */
+int64_t bsw_global2(bsw_t *h, bsw_global_job_t *jobs, int32_t numJobs, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                    uint32_t *cigar, int64_t cigarCap);
+/* resident buffers; maxBand >= every job's w.  Returns the total number of ops (the host blocks for the totals). */
+int64_t bsw_dev_global2(bsw_t *h, bsw_global_job_t *d_jobs, int32_t numJobs, const uint8_t *d_seqBufRef,
+                        const uint8_t *d_seqBufQer, uint32_t *d_cigar, int64_t cigarCap, int32_t maxBand, void *stream);
+
 /* pinned host arenas for the caller's SeqPair / sequence buffers (optional:
  * pageable memory works, pinned memory lets the copies run at link speed). */
 void *bsw_host_alloc(size_t bytes);

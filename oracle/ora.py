@@ -18,6 +18,8 @@ KSWR = np.dtype([(n, "<i4") for n in ("score", "te", "qe", "score2", "te2", "tb"
 assert SEQPAIR.itemsize == 56 and KSWR.itemsize == 28
 
 BSW_OUT = ("score", "tle", "gtle", "qle", "gscore", "max_off")
+GLOBALJOB = np.dtype([(n, "<i4") for n in ("idr", "idq", "tlen", "qlen", "w", "score", "n_cigar", "cigar_off")])
+assert GLOBALJOB.itemsize == 32
 KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 
 
@@ -87,6 +89,12 @@ def lib():
         L.ora_kswv_batch.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int, C.c_int, C.c_int, vp]
         L.ora_ksw_align2.restype = None
         L.ora_ksw_align2.argtypes = [C.c_int, vp, C.c_int, vp, C.POINTER(Params), C.c_int, vp, vp]
+        L.ora_ksw_global2.restype = C.c_int
+        L.ora_ksw_global2.argtypes = [C.c_int, vp, C.c_int, vp, C.POINTER(Params), C.c_int, vp, vp, vp]
+        L.ora_global2_batch.restype = C.c_int64
+        L.ora_global2_batch.argtypes = [vp, vp, vp, C.c_int32, C.POINTER(Params), vp, C.c_int64, C.c_int]
+        L.wl_global_fill.restype = None
+        L.wl_global_fill.argtypes = [C.c_uint64, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int32] + [C.c_int32] * 5 + [vp] * 3
         L.wl_bsw_sizes.restype = None
         L.wl_bsw_sizes.argtypes = [C.POINTER(BswCfg), vp, vp]
         L.wl_bsw_fill.restype = None
@@ -236,6 +244,32 @@ def kswv_phase1_inputs(pairs, ref, qer, aln, a=1):
     p1["h0"] = KSW_XSTOP | aln["score"][idx]
     p1["seqid"], p1["regid"] = idx, idx
     return p1, ref1, qer1
+
+
+# --------------------------------------------------------------------- CIGAR generation
+
+def global2_batch(jobs, ref, qer, params, nthreads=8):
+    """ksw_global2 over jobs (in place: score, n_cigar, cigar_off).  Returns (dense cigar array, cells)."""
+    assert jobs.dtype == GLOBALJOB and jobs.flags.c_contiguous
+    cap = int((jobs["tlen"].astype(np.int64) + jobs["qlen"]).sum()) + 16
+    cig = np.zeros(cap, dtype=np.uint32)
+    cells = lib().ora_global2_batch(_p(jobs), _p(ref), _p(qer), len(jobs), C.byref(params), _p(cig), cap, nthreads)
+    assert cells >= 0
+    tot = int(jobs["n_cigar"].astype(np.int64).sum())
+    return cig[:tot].copy(), cells
+
+
+def gen_global(n, qmin=30, qmax=150, div=0.03, p_n=1e-3, w_opt=100, seed=0xC6, a=1, o_del=6, e_del=1, o_ins=6, e_ins=1):
+    """CIGAR jobs shaped like bwa_gen_cigar2's calls (oracle/workload.c wl_global_fill).  Returns (jobs, ref, qer)."""
+    jobs = np.zeros(n, dtype=GLOBALJOB)
+    ref = np.zeros(n * (2 * qmax + 8) + 64, dtype=np.uint8)
+    qer = np.zeros(n * qmax + 64, dtype=np.uint8)
+    lib().wl_global_fill(seed, n, qmin, qmax, div, p_n, w_opt, a, o_del, e_del, o_ins, e_ins, _p(jobs), _p(ref), _p(qer))
+    return jobs, ref, qer
+
+
+def cigar_string(ops):
+    return "".join(f"{int(o) >> 4}{'MID'[int(o) & 15]}" for o in ops)
 
 
 # --------------------------------------------------------------------- caller protocol on the oracle (SURVEY.md row a9)

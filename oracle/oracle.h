@@ -91,6 +91,23 @@ int64_t ora_kswv_batch(const ora_seqpair_t *pairs, const uint8_t *ref, const uin
 void ora_ksw_align2(int qlen, const uint8_t *query, int tlen, const uint8_t *target,
                     const ora_bsw_params_t *p, int xtra, ora_kswr_t *r, int64_t *cells);
 
+/* ---- CIGAR generation: bwa ksw.c ksw_global2, oracle/global.c ---- */
+typedef struct {
+    int32_t idr, idq;        /* target = ref + idr, query = qer + idq */
+    int32_t tlen, qlen, w;   /* lengths and band (bwa_gen_cigar2 computes w per alignment) */
+    int32_t score;           /* out */
+    int32_t n_cigar;         /* out: number of ops */
+    int32_t cigar_off;       /* out: first op in the dense cigar array (sum of the n_cigar before this job) */
+} ora_global_job_t;
+
+int ora_ksw_global2(int qlen, const uint8_t *query, int tlen, const uint8_t *target, const ora_bsw_params_t *p, int w,
+                    int *n_cigar, uint32_t **cigar, int64_t *cells);
+void wl_global_fill(uint64_t seed, int32_t n, int32_t qmin, int32_t qmax, double div, double p_n, int32_t w_opt,
+                    int32_t a, int32_t o_del, int32_t e_del, int32_t o_ins, int32_t e_ins,
+                    ora_global_job_t *jobs, uint8_t *ref, uint8_t *qer);
+int64_t ora_global2_batch(ora_global_job_t *jobs, const uint8_t *ref, const uint8_t *qer, int32_t n,
+                          const ora_bsw_params_t *p, uint32_t *cigar, int64_t cigar_cap, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -240,3 +240,44 @@ void wl_random_pairs(uint64_t seed, int32_t n, int32_t qmin, int32_t qmax, int32
         sp->seqid = (int32_t)i; sp->regid = (int32_t)i;
     }
 }
+
+/* ------------------------------------------------------------------ CIGAR jobs
+ * One job per final alignment, shaped like bwa_gen_cigar2's calls from mem_reg2aln: query = the aligned part of a
+ * read (qmin..qmax bases), target = the query mutated at `div` (8:1:1 substitutions : insertions : deletions), its
+ * length whatever the mutations leave (both ends aligned: no padding), band by bwa_gen_cigar2's rule from the two
+ * lengths and opt->w.  Fixed strides: qer slot = qmax bytes, ref slot = 2 * qmax + 8 bytes per job. */
+void wl_global_fill(uint64_t seed, int32_t n, int32_t qmin, int32_t qmax, double div, double p_n, int32_t w_opt,
+                    int32_t a, int32_t o_del, int32_t e_del, int32_t o_ins, int32_t e_ins,
+                    ora_global_job_t *jobs, uint8_t *ref, uint8_t *qer)
+{
+    rng_t r; int64_t i; int k;
+    const int64_t tstride = 2 * (int64_t)qmax + 8;
+    for (i = 0; i < n; ++i) {
+        ora_global_job_t *g = &jobs[i];
+        uint8_t *q = qer + i * (int64_t)qmax, *t = ref + i * tstride;
+        int ql, tl = 0, qi = 0, w, max_ins, max_del, max_gap, min_w, dl;
+        rng_seed(&r, seed, (uint64_t)i);
+        ql = qmin + (int)rng_below(&r, (uint32_t)(qmax - qmin + 1));
+        for (k = 0; k < ql; ++k) q[k] = rng_base(&r, p_n);
+        while (qi < ql && tl < tstride - 1) {
+            if (rng_unif(&r) < div) {
+                uint32_t kind = rng_below(&r, 10);
+                if (kind < 8) { t[tl++] = q[qi] < 4 ? (uint8_t)((q[qi] + 1 + rng_below(&r, 3)) & 3) : (uint8_t)rng_below(&r, 4); ++qi; }
+                else if (kind == 8) { int gl = 1 + (int)rng_below(&r, 4); while (gl-- > 0 && tl < tstride - 1) t[tl++] = rng_base(&r, p_n); }
+                else qi += 1 + (int)rng_below(&r, 4);
+            } else t[tl++] = q[qi++];
+        }
+        /* bwa_gen_cigar2's band */
+        max_ins = (int)((double)(((ql + 1) >> 1) * a - o_ins) / e_ins + 1.);
+        max_del = (int)((double)(((ql + 1) >> 1) * a - o_del) / e_del + 1.);
+        max_gap = max_ins > max_del ? max_ins : max_del;
+        max_gap = max_gap > 1 ? max_gap : 1;
+        dl = tl > ql ? tl - ql : ql - tl;
+        w = (max_gap + dl + 1) >> 1;
+        w = w < w_opt ? w : w_opt;
+        min_w = dl + 3;
+        w = w > min_w ? w : min_w;
+        g->idr = (int32_t)(i * tstride); g->idq = (int32_t)(i * (int64_t)qmax);
+        g->tlen = tl; g->qlen = ql; g->w = w; g->score = 0; g->n_cigar = 0; g->cigar_off = 0;
+    }
+}

@@ -16,13 +16,14 @@ def lib():
         so = os.path.join(HERE, "emu", "libbswemu.so")
         src = os.path.join(HERE, "emu", "emu.cpp")
         deps = [src, os.path.join(HERE, "emu", "warp_emu.h")] + [os.path.join(ROOT, "bwa-mem2-arm_b200", "csrc", f)
-                                                                 for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh", "bsw_wide.cuh")]
+                                                                 for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh", "bsw_wide.cuh", "global_core.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
         _lib = C.CDLL(so)
         _lib.emu_bsw.restype = C.c_int
         _lib.emu_kswv.restype = C.c_int
         _lib.emu_bsw_wide.restype = C.c_int
+        _lib.emu_global2.restype = C.c_longlong
     return _lib
 
 
@@ -54,3 +55,12 @@ def bsw_wide(pairs, ref, qer, w=100, o_del=6, e_del=1, o_ins=6, e_ins=1, zdrop=1
     lib().emu_bsw_wide(_p(out), _p(ref), _p(qer), len(out), o_del, e_del, o_ins, e_ins, zdrop, end_bonus, a, b, -1, w,
                        min_cfg | (0x100 if latency else 0), _p(taken))
     return out, taken.astype(bool)
+
+
+def global2(jobs, ref, qer, o_del=6, e_del=1, o_ins=6, e_ins=1, a=1, b=4, nthreads=32):
+    """CIGAR generation (global_core.cuh) with the library's scratch layout.  Returns (jobs, dense op array)."""
+    out = jobs.copy()
+    cap = int((out["tlen"].astype(np.int64) + out["qlen"]).sum()) + 16
+    cig = np.zeros(cap, np.uint32)
+    tot = lib().emu_global2(_p(out), len(out), _p(ref), _p(qer), o_del, e_del, o_ins, e_ins, a, b, -1, _p(cig), C.c_longlong(cap), nthreads)
+    return out, cig[:tot]

@@ -11,6 +11,7 @@
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core2.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/kswv_core.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/bsw_wide.cuh"
+#include "../../bwa-mem2-arm_b200/csrc/global_core.cuh"
 #include "../../include/bsw_cuda.h"
 
 using namespace bswk;
@@ -173,6 +174,38 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         kput(aln, pairs[i], i, o, phase); if (cells_out) cells_out[i] = o.cells;
     }
     return (int)el.size();
+}
+
+
+// CIGAR generation (global_core.cuh): jobs as the library lays them out -- `nthreads` jobs per "launch" sharing an interleaved
+// rolling-row scratch of M = 2 * max_w + 2 slots, direction words per job, count pass, scan, emit pass.  Returns total ops.
+long long emu_global2(bsw_global_job_t *jobs, int n, const uint8_t *ref, const uint8_t *qer,
+                      int o_del, int e_del, int o_ins, int e_ins, int a, int b, int ambig, uint32_t *cigar, long long cap, int nthreads)
+{
+    Const c = mk(o_del, e_del, o_ins, e_ins, 0, 0, a, b, ambig);
+    long long total = 0;
+    for (int first = 0; first < n; first += nthreads) {
+        const int cnt = std::min(nthreads, n - first);
+        int max_w = 0;
+        for (int t = 0; t < cnt; ++t) max_w = std::max(max_w, jobs[first + t].w);
+        const int M = 2 * max_w + 2;
+        std::vector<int2> eh((size_t)M * cnt);
+        std::vector<std::vector<uint32_t>> z(cnt);
+        for (int t = 0; t < cnt; ++t) {
+            bsw_global_job_t &g = jobs[first + t];
+            z[t].assign((size_t)global2_zwords(g.tlen, g.qlen, g.w) + 1, 0xdeadbeefu);
+            long long cl = 0;
+            g.score = global2_dp(c, g.tlen, g.qlen, g.w, ref + g.idr, qer + g.idq, eh.data() + t, (long long)cnt, M, z[t].data(), cl);
+            g.n_cigar = global2_backtrack<false>(g.tlen, g.qlen, g.w, z[t].data(), nullptr, 0);
+        }
+        for (int t = 0; t < cnt; ++t) {
+            bsw_global_job_t &g = jobs[first + t];
+            g.cigar_off = (int)total;
+            if (total + g.n_cigar <= cap) global2_backtrack<true>(g.tlen, g.qlen, g.w, z[t].data(), cigar + total, g.n_cigar);
+            total += g.n_cigar;
+        }
+    }
+    return total;
 }
 
 }

@@ -121,3 +121,53 @@ def ksw_pass_py(query, target, mat, o_del, e_del, o_ins, e_ins, xtra, is8):
             if (row_i < te - d or row_i > te + d) and sc > r["score2"]:
                 r["score2"], r["te2"] = sc, row_i
     return r
+
+
+def global_full(query, target, mat, o_del, e_del, o_ins, e_ins, w):
+    """Independent full-matrix transcription of the recurrences ksw_global2 documents (bwa ksw.c): three (tlen+1) x (qlen+1)
+    tables, no rolling row, no backtrack bytes.  Cell (I, J) (1-based) exists iff |I - J| <= w; gaps open from M only.
+    Returns H[tlen][qlen]."""
+    NEG = -0x40000000
+    tl, ql = len(target), len(query)
+    H = [[NEG] * (ql + 1) for _ in range(tl + 1)]
+    E = [[NEG] * (ql + 1) for _ in range(tl + 2)]     # E[I][J]: gap in the query direction arriving at row I (deletion)
+    H[0][0] = 0
+    for J in range(1, ql + 1):
+        if J <= w:
+            H[0][J] = -(o_ins + e_ins * J)
+    for I in range(1, tl + 1):
+        if I <= w:
+            H[I][0] = -(o_del + e_del * I)
+    for I in range(1, tl + 1):
+        F = NEG
+        for J in range(1, ql + 1):
+            if abs(I - J) > w:
+                # ksw_global2 evaluates j in [i - w, i + w + 1) with i = I - 1, j = J - 1
+                continue
+            diag = H[I - 1][J - 1]
+            M = diag + mat[target[I - 1] * 5 + query[J - 1]]
+            e = E[I][J]
+            if J - 1 == max(I - 1 - w, 0):          # first cell of the row: F restarts
+                F = NEG
+            h = max(M, e, F)
+            H[I][J] = h
+            E[I + 1][J] = max(M - o_del, e) - e_del
+            F = max(M - o_ins, F) - e_ins
+    return H[tl][ql]
+
+
+def cigar_score(ops, query, target, mat, o_del, e_del, o_ins, e_ins):
+    """Score of an alignment given as bwa ops (len << 4 | op; 0 = M, 1 = I, 2 = D) under affine gaps."""
+    i = j = 0
+    s = 0
+    for o in ops:
+        ln, op = int(o) >> 4, int(o) & 15
+        if op == 0:
+            for _ in range(ln):
+                s += mat[target[i] * 5 + query[j]]; i += 1; j += 1
+        elif op == 1:
+            s -= o_ins + e_ins * ln; j += ln
+        else:
+            s -= o_del + e_del * ln; i += ln
+    assert i == len(target) and j == len(query)
+    return s

@@ -284,6 +284,42 @@ def test_kswv_dev_align2(ora, bsw):
     ks.close()
 
 
+def test_global2_cigar_generation(ora, bsw, monkeypatch):
+    """Row f.4: bsw_global2 / bsw_dev_global2 (batched ksw_global2 with backtrack) == the oracle: score, n_cigar, cigar_off
+    and every op -- bwa_gen_cigar2-shaped jobs at three divergences, two scoring sets, corner jobs, a call cut into
+    several launches, a too-small op buffer."""
+    import torch
+    from test_kernel_logic_cpu import _global_cases
+    for kw, sc in ((dict(), (6, 1, 6, 1, 100, 5, None, 1, 4, 1)), (dict(o_del=4, e_del=2, o_ins=7, e_ins=1, a=2, b=3), (4, 2, 7, 1, 100, 5, None, 2, 3, 1))):
+        prm = ora.make_params(**kw)
+        h = bsw.BandedPairWiseSW(*sc)
+        for J, r, q in _global_cases(ora) + [ora.gen_global(30000, div=0.04, seed=0xD1)]:
+            o = J.copy(); oc, _ = ora.global2_batch(o, r, q, prm, 8)
+            g = J.view(bsw.GLOBALJOB).copy()
+            gc = h.global2(g, r, q)
+            assert (g == o.view(bsw.GLOBALJOB)).all() and len(gc) == len(oc) and (gc == oc).all()
+        h.close()
+    # resident buffers, several launches per call
+    monkeypatch.setenv("BSW_CUDA_GLOBAL_CHUNK", "4096")
+    h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    J, r, q = ora.gen_global(20000, div=0.06, seed=0xD2)
+    prm = ora.make_params()
+    o = J.copy(); oc, _ = ora.global2_batch(o, r, q, prm, 8)
+    dj = torch.from_numpy(J.view(np.uint8).reshape(-1).copy()).cuda()
+    dr, dq = torch.from_numpy(r).cuda(), torch.from_numpy(q).cuda()
+    dc = torch.zeros(len(oc) + 8, dtype=torch.int32, device="cuda")
+    tot = h.dev_global2(dj, len(J), dr, dq, dc, len(oc) + 8, int(J["w"].max()), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert tot == len(oc)
+    assert (dj.cpu().numpy().view(bsw.GLOBALJOB) == o.view(bsw.GLOBALJOB)).all()
+    assert (dc.cpu().numpy().view(np.uint32)[:tot] == oc).all()
+    # op buffer too small: the call reports the size it needs
+    small = np.zeros(100, np.uint32)
+    with pytest.raises(RuntimeError, match=str(len(oc))):
+        h.global2(J.view(bsw.GLOBALJOB).copy(), r, q, small)
+    h.close()
+
+
 def test_kswv_edge(ora, ks, bsw):
     prm = ora.make_params()
     P, r, q = ora.gen_random(2000, 0, 60, 0, 150, sim=0.7, p_n=0.05, seed=3)

@@ -154,3 +154,39 @@ def test_bsw_wide_16bit_tier(ora):
     _check_wide(ora, L, lr, lq, w=10, zdrop=20)
     P, r, q = ora.gen_random(4, 1100, 1200, 1100, 1200, h0min=10, h0max=20, sim=0.9, seed=14)       # too long: not admitted
     assert not _check_wide(ora, P, r, q).any()
+
+
+def _global_cases(ora):
+    """CIGAR jobs: bwa_gen_cigar2-shaped ones at three divergences, plus hand-made corners (empty sides, band 0, band
+    equal to the length difference, all-N, a band wider than the query).  w >= |tlen - qlen| throughout: below that the
+    reference's backtrack leaves its matrix (bwa_gen_cigar2 never asks for it)."""
+    cases = [ora.gen_global(400, div=0.03, seed=0xC6), ora.gen_global(300, qmin=1, qmax=60, div=0.15, seed=0xC7),
+             ora.gen_global(100, qmin=200, qmax=400, div=0.08, seed=0xC8, w_opt=100)]
+    rng = np.random.default_rng(3)
+    q = rng.integers(0, 4, 400, dtype=np.uint8); r = rng.integers(0, 4, 400, dtype=np.uint8)
+    r[100:160] = q[100:160]; q[300:310] = 4
+    J = np.zeros(9, dtype=ora.GLOBALJOB)
+    rows = [(0, 0, 0, 0, 3), (0, 0, 10, 0, 10), (0, 0, 0, 10, 12), (100, 100, 60, 60, 0), (100, 100, 60, 40, 20), (100, 100, 30, 60, 31),
+            (0, 0, 50, 50, 100), (300, 300, 10, 10, 4), (90, 100, 80, 60, 25)]
+    for k, (a, b, tl, ql, w) in enumerate(rows):
+        J[k]["idr"], J[k]["idq"], J[k]["tlen"], J[k]["qlen"], J[k]["w"] = a, b, tl, ql, w
+    cases.append((J, r, q))
+    return cases
+
+
+def test_global2_cigar_generation(ora):
+    """global_core.cuh (row f.4: ksw_global2 with backtrack) on the host with the library's scratch layout (interleaved
+    rolling rows modulo 2 w_max + 2, packed direction words, count + emit passes) == the oracle: scores, op counts, ops."""
+    for kw in (dict(), dict(o_del=4, e_del=2, o_ins=7, e_ins=1, a=2, b=3)):
+        prm = ora.make_params(**kw)
+        for J, r, q in _global_cases(ora):
+            o = J.copy(); oc, _ = ora.global2_batch(o, r, q, prm, 4)
+            g, gc = emu.global2(J, r, q, **kw)
+            for f in ("score", "n_cigar", "cigar_off"):
+                assert (o[f] == g[f]).all(), (f, np.nonzero(o[f] != g[f])[0][:5])
+            assert len(oc) == len(gc) and (oc == gc).all()
+            # every CIGAR consumes exactly its query and target
+            for i in range(len(o)):
+                ops = oc[o["cigar_off"][i]:o["cigar_off"][i] + o["n_cigar"][i]]
+                assert sum(int(x) >> 4 for x in ops if int(x) & 15 in (0, 1)) == o["qlen"][i]
+                assert sum(int(x) >> 4 for x in ops if int(x) & 15 in (0, 2)) == o["tlen"][i]
