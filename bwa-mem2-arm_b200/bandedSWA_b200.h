@@ -59,6 +59,20 @@ public:
                                int32_t w, int32_t maxBandTry, void *stream)
     { bsw_dev_extendChained(h_, d_left, d_leftRef, d_leftQer, numLeft, d_right, d_rightRef, d_rightQer, numRight, w, maxBandTry, stream); }
 
+    /* ---- optional additions next to the unchanged signatures (include/bsw_cuda.h) ---- */
+    /* the sequence buffers both tier calls of a batch share go up once: declare them around the calls */
+    void arenaBegin(const uint8_t *seqBufRef, size_t refBytes, const uint8_t *seqBufQer, size_t qerBytes)
+    { bsw_arena_begin(h_, seqBufRef, refBytes, seqBufQer, qerBytes); }
+    void arenaEnd() { bsw_arena_end(h_); }
+    /* targets from the reference resident on the GPU (bsw_ref_upload of the .pac): rpos[i] as bns_fetch_seq counts
+     * (doubled-strand coordinate; ~x = read downwards from x, the reversed slices of left extensions) */
+    void getScoresRef(SeqPair *pairArray, const bsw_ref_t *ref, const int64_t *rpos, uint8_t *seqBufQer, int32_t numPairs, int32_t w)
+    { bsw_getScoresRef(h_, pairArray, ref, rpos, seqBufQer, numPairs, w); }
+    /* CIGAR generation after the extension: a batch of bwa_gen_cigar2's ksw_global2 calls */
+    int64_t global2(bsw_global_job_t *jobs, int32_t numJobs, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                    uint32_t *cigar, int64_t cigarCap)
+    { return bsw_global2(h_, jobs, numJobs, seqBufRef, seqBufQer, cigar, cigarCap); }
+
     int64_t getTicks() { return 0; }          /* the reference's rdtsc counter; device time is in bsw_get_stats */
     bsw_t *handle() { return h_; }
 
@@ -82,6 +96,11 @@ public:
     void getScores16(SeqPair *pairArray, uint8_t *seqBufRef, uint8_t *seqBufQer, kswr_t *aln, int32_t numPairs,
                      uint16_t numThreads, int phase)
     { kswv_getScores16(h_, pairArray, seqBufRef, seqBufQer, reinterpret_cast<bsw_kswr_t *>(aln), numPairs, numThreads, phase); }
+
+    /* device-resident pairs: ksw_align2 (forward pass, hand-off, reverse pass) in one submission; see kswv_dev_align2 */
+    void align2Resident(const SeqPair *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer, kswr_t *d_aln,
+                        int32_t numPairs, int is8, void *stream)
+    { kswv_dev_align2(h_, d_pairArray, d_seqBufRef, d_seqBufQer, reinterpret_cast<bsw_kswr_t *>(d_aln), numPairs, is8, stream); }
 
     kswv_t *handle() { return h_; }
 

@@ -1,7 +1,7 @@
 /*
  * global_core.cuh -- CIGAR generation: banded global alignment with backtrack, one thread per alignment
  * (semantics = bwa ksw.c ksw_global2, which bwa-mem2's mem_reg2aln reaches through
- * bwa_gen_cigar2 once per reported alignment; restated in oracle/global.c).
+ * bwa_gen_cigar2 once per reported alignment).
  *
  * Differences from the extension kernels: the DP is Needleman-Wunsch (negative scores, -inf outside the band, 32-bit
  * state), every cell leaves a direction byte, and the product is the op list, not a score.  A job is ~3 k cells
