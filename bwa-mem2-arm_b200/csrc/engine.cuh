@@ -209,6 +209,7 @@ public:
         for (int spin = 0; spin < spin_iters; ++spin) {    /* short spin: a wake-up through the futex costs more than a small batch */
             if (done_gen(s) >= r.gen) return;
             cpu_relax();
+            if ((spin & 63) == 63) std::this_thread::yield();
         }
         std::unique_lock<std::mutex> lk(s->done_mu);       /* per slot: a landing batch wakes its own callers only */
         s->done_cv.wait(lk, [&] { return done_gen(s) >= r.gen; });
@@ -350,6 +351,9 @@ private:
             if (pending || std::chrono::steady_clock::now() - last_activity < std::chrono::microseconds(300)) {
                 lk.unlock();                               /* busy period: poll (events + new arrivals) */
                 for (int k = 0; k < 32; ++k) cpu_relax();
+                /* give the core to a runnable caller if there is one (returns at once otherwise): with more worker threads than
+                 * cores -- or one engine per GPU on an 8-GPU host -- a polling engine would otherwise starve the packers */
+                std::this_thread::yield();
                 lk.lock();
             } else {
                 engine_sleeping.store(1, std::memory_order_release);

@@ -61,7 +61,7 @@ class KswvCfg(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("oracle.c", "workload.c", "bsw_avx2.c", "oracle.h", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("oracle.c", "workload.c", "bsw_avx2.c", "global.c", "striped.c", "oracle.h", "Makefile")]
     stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
@@ -89,6 +89,8 @@ def lib():
         L.ora_kswv_batch.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int, C.c_int, C.c_int, vp]
         L.ora_ksw_align2.restype = None
         L.ora_ksw_align2.argtypes = [C.c_int, vp, C.c_int, vp, C.POINTER(Params), C.c_int, vp, vp]
+        L.ora_kswv_batch_striped.restype = None
+        L.ora_kswv_batch_striped.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int]
         L.ora_ksw_global2.restype = C.c_int
         L.ora_ksw_global2.argtypes = [C.c_int, vp, C.c_int, vp, C.POINTER(Params), C.c_int, vp, vp, vp]
         L.ora_global2_batch.restype = C.c_int64
@@ -132,6 +134,12 @@ def kswv_batch(pairs, ref, qer, aln, params, is8, phase, nthreads=1, want_cells=
     tot = lib().ora_kswv_batch(_p(pairs), _p(ref), _p(qer), _p(aln), len(pairs), C.byref(params),
                                int(is8), int(phase), nthreads, _p(cells))
     return (tot, cells) if want_cells else tot
+
+
+def kswv_batch_striped(pairs, ref, qer, aln, params, is8):
+    """Phase 0 through the lane-by-lane emulation of bwa's striped ksw_u8 / ksw_i16 (oracle/striped.c; analysis only)."""
+    assert pairs.dtype == SEQPAIR and aln.dtype == KSWR
+    lib().ora_kswv_batch_striped(_p(pairs), _p(ref), _p(qer), _p(aln), len(pairs), C.byref(params), int(is8))
 
 
 def ksw_align2(query, target, params, xtra):

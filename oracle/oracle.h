@@ -91,6 +91,12 @@ int64_t ora_kswv_batch(const ora_seqpair_t *pairs, const uint8_t *ref, const uin
 void ora_ksw_align2(int qlen, const uint8_t *query, int tlen, const uint8_t *target,
                     const ora_bsw_params_t *p, int xtra, ora_kswr_t *r, int64_t *cells);
 
+/* lane-by-lane emulation of bwa's striped ksw_u8 / ksw_i16 (oracle/striped.c): analysis tool, see its header */
+void ora_ksw_pass_striped(int qlen, const uint8_t *query, int tlen, const uint8_t *target, const ora_bsw_params_t *p, int xtra,
+                          int is8, ora_kswr_t *r);
+void ora_kswv_batch_striped(const ora_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, ora_kswr_t *aln, int32_t n,
+                            const ora_bsw_params_t *p, int is8);
+
 /* ---- CIGAR generation: bwa ksw.c ksw_global2, oracle/global.c ---- */
 typedef struct {
     int32_t idr, idq;        /* target = ref + idr, query = qer + idq */

@@ -295,6 +295,7 @@ int main(int argc, char **argv)
         const int64_t v[8] = { es[d].scan_ns, es[d].reserve_ns, es[d].pack_ns, es[d].wait_ns, es[d].unpack_ns, es[d].packers_ns, es[d].submit_ns, es[d].flight_ns };
         for (int i = 0; i < 8; ++i) pf[i] += (double)v[i];
     }
+    int used = 0; for (int d = 0; d < nd; ++d) used += es[d].batches > 0;      /* devices whose engine ran a batch */
     const double pc = ec ? 1e-3 / (double)ec : 0.0, pb = eb ? 1e-3 / (double)eb : 0.0;
     printf("{\"mode\": \"%s\", \"threads\": %d, \"pinned\": %d, \"per_task_handles\": %d, \"tasks\": %lld, \"pairs_submitted\": %ld, "
            "\"pairs_retried_or_phase1\": %ld, \"wall_s\": %.6f, \"pairs_per_s\": %.1f, \"calls\": %ld, \"us_per_call\": %.2f, "
@@ -306,7 +307,7 @@ int main(int argc, char **argv)
            W.mode == 1 ? "kswv" : "bsw", threads, pinned, per_task, (long long)W.nT, sum.pairs, sum.retried, best, sum.pairs / best,
            sum.calls, sum.calls ? sum.call_s / sum.calls * 1e6 : 0.0, sum.creates, sum.creates ? sum.create_s / sum.creates * 1e6 : 0.0,
            eb, eb ? (double)ep / eb : 0.0, emax, el, reps, pf[0] * pc, pf[1] * pc, pf[2] * pc, pf[3] * pc, pf[4] * pc,
-           pf[5] * pb, pf[6] * pb, pf[7] * pb, nd, eh2d, ed2h);
+           pf[5] * pb, pf[6] * pb, pf[7] * pb, used, eh2d, ed2h);
     if (out) {
         FILE *f = fopen(out, "wb");
         if (!f) { perror(out); return 2; }
