@@ -749,9 +749,10 @@ void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const u
     const int nd = (int)k.devs.size();
     const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
     const int nchunks = (n + chunk - 1) / chunk;
-    struct Job { int first, cnt, di; DevCtx *x; Slot *sl; bsw_kswr_t *h_res; };
+    struct Job { int first, cnt, di; long long rlo, qlo; DevCtx *x; Slot *sl; bsw_kswr_t *h_res; bool landed; };
     std::vector<Job> jobs(nchunks);
     auto finish = [&](Job &j) {              /* chunk landed: phase 1 applies the refinement rule on the host */
+        if (j.landed) return;
         slot_retire(*j.x, *j.sl);
         if (phase == 1)
             for (int i = 0; i < j.cnt; ++i) {
@@ -759,43 +760,61 @@ void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const u
                 bsw_kswr_t *a = &aln[pairs[j.first + i].regid];
                 if (a->score == rr.score) { a->tb = a->te - rr.te; a->qb = a->qe - rr.qe; }
             }
-        j.h_res = nullptr;
+        j.landed = true;
     };
-    auto stage = [&](int ci) {
+    auto upload = [&](Job &j, bool exact) {
+        Slot &sl = *j.sl;
+        long long rlo, rhi, qlo, qhi;
+        if (exact) extents(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
+        else extents_sampled(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
+        sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
+        sl.ref.reserve((size_t)(rhi - rlo) + 64); sl.qer.reserve((size_t)(qhi - qlo) + 64);
+        sl.aln.reserve((size_t)j.cnt * sizeof(bsw_kswr_t));
+        CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
+        if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
+        if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
+        k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
+        j.rlo = rlo; j.qlo = qlo;
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - qlo, j.cnt, sl.stream, 0, rlo, rhi, qlo, qhi);
+    };
+    /* stage A: the slot's previous chunk lands, then uploads + prep + sort + histogram read-back are enqueued */
+    auto stage_a = [&](int ci) {
         Job &j = jobs[ci];
         j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
-        j.di = ci % nd;
+        j.di = ci % nd; j.landed = false;
         j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
-        if (ci >= nd * BSW_NSLOT) finish(jobs[ci - nd * BSW_NSLOT]);      /* the slot's previous chunk */
+        if (ci >= nd * BSW_NSLOT) finish(jobs[ci - nd * BSW_NSLOT]);
+        CK(cudaSetDevice(j.x->dev));
+        upload(j, false);
+        j.sl->busy = true;
+    };
+    /* stage B: histogram in, DP kernels, results on their way home */
+    auto stage_b = [&](int ci) {
+        Job &j = jobs[ci];
         Slot &sl = *j.sl;
         CK(cudaSetDevice(j.x->dev));
-        long long rlo, rhi, qlo, qhi;
-        extents_sampled(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
-        for (int attempt = 0; attempt < 2; ++attempt) {
-            if (attempt == 1) extents(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi);
-            sl.pairs.reserve((size_t)j.cnt * sizeof(bsw_seqpair_t));
-            sl.ref.reserve((size_t)(rhi - rlo) + 64); sl.qer.reserve((size_t)(qhi - qlo) + 64);
-            sl.aln.reserve((size_t)j.cnt * sizeof(bsw_kswr_t));
-            CK(cudaMemcpyAsync(sl.pairs.p, pairs + j.first, (size_t)j.cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, sl.stream));
-            if (rhi > rlo) CK(cudaMemcpyAsync(sl.ref.p, ref + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, sl.stream));
-            if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
-            k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
-            plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - qlo, j.cnt, sl.stream, 0, rlo, rhi, qlo, qhi);
-            const Plan *pl = plan_wait(sl, sl.stream);
-            if (!pl->oob_pairs) break;
-            if (attempt == 1) die("a pair names bases outside its sequence buffer");
+        const Plan *pl = plan_wait(sl, sl.stream);
+        if (pl->oob_pairs) {
+            upload(j, true);
+            pl = plan_wait(sl, sl.stream);
+            if (pl->oob_pairs) die("a pair names bases outside its sequence buffer");
         }
         /* the device always stores the raw pass result of pair i at chunk-local index i (phase-0 store rule) */
-        launch_kswv_dp(k, k.rt(j.di), *j.x, sl, sl.h_plan, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - rlo,
-                       (const uint8_t *)sl.qer.p - qlo, (bsw_kswr_t *)sl.aln.p, j.cnt, is8, 0, sl.stream);
+        launch_kswv_dp(k, k.rt(j.di), *j.x, sl, pl, (bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.ref.p - j.rlo,
+                       (const uint8_t *)sl.qer.p - j.qlo, (bsw_kswr_t *)sl.aln.p, j.cnt, is8, 0, sl.stream);
         if (phase == 0) j.h_res = aln + j.first;
         else { sl.h_res.reserve((size_t)chunk * sizeof(bsw_kswr_t)); j.h_res = (bsw_kswr_t *)sl.h_res.p; }
         CK(cudaMemcpyAsync(j.h_res, sl.aln.p, (size_t)j.cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, sl.stream));
         CK(cudaEventRecord(sl.done, sl.stream));
-        sl.busy = true;
         k.st.d2h_bytes += (int64_t)j.cnt * sizeof(bsw_kswr_t);
     };
-    for (int ci = 0; ci < nchunks; ++ci) stage(ci);
+    /* like the BSW path: chunk c + ahead is uploading while chunk c waits for its histogram */
+    const int ahead = nd * std::max(1, std::min(BSW_NSLOT - 2, k.ahead));
+    for (int ci = 0; ci < std::min(ahead, nchunks); ++ci) stage_a(ci);
+    for (int ci = 0; ci < nchunks; ++ci) {
+        if (ci + ahead < nchunks) stage_a(ci + ahead);
+        stage_b(ci);
+    }
     for (int ci = std::max(0, nchunks - nd * BSW_NSLOT); ci < nchunks; ++ci) finish(jobs[ci]);
 }
 

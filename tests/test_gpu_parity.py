@@ -320,6 +320,58 @@ def test_global2_cigar_generation(ora, bsw, monkeypatch):
     h.close()
 
 
+def test_guard_bands_untouched(ora, bsw):
+    """No resident entry point writes outside the caller's buffers: every buffer sits between two 4 KiB guard bands that
+    must come back unchanged (compute-sanitizer is closed on this pool; this covers the caller-visible side of memcheck)."""
+    import torch
+    G = 4096
+
+    def guarded(a):
+        raw = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+        t = torch.full((len(raw) + 2 * G,), 0xA5, dtype=torch.uint8, device="cuda")
+        t[G:G + len(raw)] = torch.from_numpy(raw.copy()).cuda()
+        return t, t[G:G + len(raw)]
+
+    def intact(*ts):
+        for t, body in ts:
+            assert bool((t[:G] == 0xA5).all()) and bool((t[G + len(body):] == 0xA5).all())
+
+    st = torch.cuda.current_stream().cuda_stream
+    prm = ora.make_params()
+    # BSW: thread kernel (large call), lanes-per-pair kernel (small call, 16-bit tier), general kernel
+    for P, r, q in (ora.gen_bsw(60000, seed=0x91)["left"], ora.gen_bsw(700, seed=0x92)["left"],
+                    ora.gen_bsw(600, read_len=300, seed=0x93, div=0.02, seed_max=150)["right"],
+                    ora.gen_random(40, 1100, 1300, 1100, 1300, h0min=10, h0max=20, sim=0.9, seed=14)):
+        o, _ = _oracle_bsw(ora, P, r, q)
+        tp, tr, tq = guarded(P), guarded(r), guarded(q)
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+        h.dev_getScores(tp[1], tr[1], tq[1], len(P), 100, st)
+        torch.cuda.synchronize()
+        _assert_same(o, tp[1].cpu().numpy().view(bsw.SEQPAIR))
+        intact(tp, tr, tq)
+        h.close()
+    # kswv: both passes and the hand-off
+    K, kr, kq = ora.gen_kswv(5000, seed=0x94)
+    ao, _ = ora.kswv_align2_batch(K, kr, kq, prm, 8)
+    tp, tr, tq, ta = guarded(K), guarded(kr), guarded(kq), guarded(np.zeros(len(K), bsw.KSWR))
+    ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    ks.dev_align2(tp[1], tr[1], tq[1], ta[1], len(K), 1, st)
+    torch.cuda.synchronize()
+    assert (ta[1].cpu().numpy().view(bsw.KSWR) == ao).all()
+    intact(tp, tr, tq, ta)
+    ks.close()
+    # CIGAR generation
+    J, jr, jq = ora.gen_global(5000, seed=0x95)
+    jo = J.copy(); oc, _ = ora.global2_batch(jo, jr, jq, prm, 8)
+    tj, tr, tq, tc = guarded(J), guarded(jr), guarded(jq), guarded(np.zeros(len(oc), np.uint32))
+    h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    tot = h.dev_global2(tj[1], len(J), tr[1], tq[1], tc[1], len(oc), int(J["w"].max()), st)
+    torch.cuda.synchronize()
+    assert tot == len(oc) and (tc[1].cpu().numpy().view(np.uint32) == oc).all()
+    intact(tj, tr, tq, tc)
+    h.close()
+
+
 def test_kswv_edge(ora, ks, bsw):
     prm = ora.make_params()
     P, r, q = ora.gen_random(2000, 0, 60, 0, 150, sim=0.7, p_n=0.05, seed=3)
