@@ -66,7 +66,7 @@ __device__ __forceinline__ bool query_has_n(const uint8_t *__restrict__ qer, lon
 }
 
 #define BSW_KEY_BITS 26         /* packed pairs: (has-N flag) << 25 | (len2 + 1) << 16 | (len1 / 2) << 8 | h0  (>= 0x10000);
-                                 * wide-only pairs: (configuration + 1) << 13 | len1 / 2  (< 0x10000); general pairs: 0 */
+                                 * wide-only pairs: (configuration + 1) << 12 | len1 / 2  (< 0x10000); general pairs: 0 */
 
 __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ qer, int n, Const c, int mode,
                             int max_elems, int tier8_check, int allow_wide, long long rlo, long long rhi, long long qlo, long long qhi,
@@ -103,8 +103,8 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
         } else if (mode == MODE_BSW && allow_wide && wide_eligible(c, len1, len2, h0)) {
             /* too long or too high-scoring for the byte-packed rows: the 16-bit lanes-per-pair kernel takes it */
             const int cfg = wide_cfg_for(len2);
-            const uint32_t l1 = (uint32_t)(len1 >> 1) > 8191u ? 8191u : (uint32_t)(len1 >> 1);
-            key = ((uint32_t)(cfg + 1) << 13) | l1;
+            const uint32_t l1 = (uint32_t)(len1 >> 1) > 4095u ? 4095u : (uint32_t)(len1 >> 1);
+            key = ((uint32_t)(cfg + 1) << 12) | l1;
             atomicAdd(&s_wide[cfg], 1);
         } else {
             atomicAdd(&s_misc[0], 1);
@@ -200,7 +200,7 @@ __device__ __forceinline__ void bintable_lookup(const BinTable &t, int block, in
 /* staged batches: pair i's compact record carries (class << 24 | position within the class) in its `id` word
  * (written by the host thread that packed it); class_start[] is known once the batch is closed.  Deterministic
  * inverse: sorted[class_start[class] + position] = i. */
-#define BSW_NCLASS 40
+#define BSW_NCLASS 48
 struct ClassStart { int start[BSW_NCLASS]; };
 __global__ void class_scatter_kernel(const char *__restrict__ rec24, int n, ClassStart cs, uint32_t *__restrict__ sorted)
 {
@@ -250,25 +250,14 @@ bsw_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
 
 /* ------------------------------------------------------------------ 4c. BSW wide (lanes per pair, bsw_wide.cuh)
  * G lanes per pair, 128 threads per block; pair of group g = sorted slot first + g. */
-template <int G, int R, bool SYM>
-__global__ void __launch_bounds__(128)
-bsw_wide_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
-                const uint32_t *__restrict__ sorted_idx, int first, int count, Const c, int w)
-{
-    const int gid = (blockIdx.x * 128 + threadIdx.x) / G, gl = threadIdx.x % G;
-    const int pi = gid < count ? (int)sorted_idx[first + gid] : -1;
-    const PairIn P = load_pair(io, pi);
-    PairOut o;
-    bsw_wide_lane<G, R, SYM>(c, w, P, ref, qer, gl, o);
-    if (pi >= 0 && gl == 0) store_bsw(io, pi, o);
-}
-
-/* Kernel shapes (G lanes x R registers x 2 halves).  0..4 are the configurations of bsw_wide.cuh (smallest that holds a
- * query: the throughput choice); 5 and 6 are their latency alternates: the same columns on twice / four times the lanes,
- * i.e. a shorter chain per row, for batches too small to fill the device anyway. */
-#define BSW_WIDE_NSHAPE 7
-static inline int wide_shape_lanes(int sh) { return sh <= 1 ? 8 : (sh == 2 || sh == 5) ? 16 : 32; }
-static inline int wide_latency_shape(int cfg) { return cfg == 1 ? 5 : cfg == 2 ? 6 : cfg; }   /* (8,9) -> (16,5); (16,9) -> (32,5) */
+/* Kernel shapes (G lanes x R registers x 2 halves).  0..7 are the configurations of bsw_wide.cuh (the throughput choice);
+ * 8..10 are the latency alternates: the same columns on more lanes, i.e. a shorter chain per row, for batches too
+ * small to fill the device anyway. */
+#define BSW_WIDE_NSHAPE 11
+static inline int wide_shape_lanes(int sh) { return sh <= 7 ? wide_cfg_lanes(sh) : sh == 8 ? 8 : sh == 9 ? 16 : 32; }
+static inline int wide_shape_regs(int sh) { return sh <= 7 ? wide_cfg_regs(sh) : 5; }
+/* (4,10) -> (8,5); (4,16), (8,9) -> (16,5) = 160 columns; (8,16), (16,9) -> (32,5) = 320 columns; larger: unchanged */
+static inline int wide_latency_shape(int cfg) { return cfg == 0 ? 8 : cfg <= 2 ? 9 : cfg <= 4 ? 10 : cfg; }
 
 #define BSW_WIDE_MAXSEG 8
 struct WideTable {
@@ -290,7 +279,8 @@ __device__ __forceinline__ void wide_block(const PairIO &io, const uint8_t *__re
 }
 
 /* several shapes in ONE launch: a small batch is two or three short segments, and launching them one after another
- * on a stream adds their latencies (each 50-150 us) */
+ * on a stream adds their latencies (each 50-150 us).  Two kernels by register need: R <= 10 (96 registers, 20 warps/SM)
+ * and R = 16 (<= 168 registers, 12 warps/SM). */
 template <bool SYM>
 __global__ void __launch_bounds__(128)
 bsw_wide_multi_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
@@ -300,12 +290,29 @@ bsw_wide_multi_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t 
     while (s + 1 < t.nseg && (int)blockIdx.x >= t.first_block[s + 1]) ++s;
     const int block = (int)blockIdx.x - t.first_block[s], first = t.first_pair[s], count = t.count[s];
     switch (t.shape[s]) {
-    case 0: wide_block<8, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
-    case 1: wide_block<8, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
-    case 2: wide_block<16, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
-    case 3: wide_block<32, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
-    case 5: wide_block<16, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 0: wide_block<4, 10, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 2: wide_block<8, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 4: wide_block<16, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 6: wide_block<32, 9, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 8: wide_block<8, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 9: wide_block<16, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
     default: wide_block<32, 5, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    }
+}
+
+template <bool SYM>
+__global__ void __launch_bounds__(128, 3)
+bsw_wide_multi16_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                        const uint32_t *__restrict__ sorted_idx, const __grid_constant__ WideTable t, Const c, int w)
+{
+    int s = 0;
+    while (s + 1 < t.nseg && (int)blockIdx.x >= t.first_block[s + 1]) ++s;
+    const int block = (int)blockIdx.x - t.first_block[s], first = t.first_pair[s], count = t.count[s];
+    switch (t.shape[s]) {
+    case 1: wide_block<4, 16, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 3: wide_block<8, 16, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    case 5: wide_block<16, 16, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
+    default: wide_block<32, 16, SYM>(io, ref, qer, sorted_idx, first, count, c, w, block); break;
     }
 }
 
@@ -317,33 +324,36 @@ struct WideSeg { int cfg, first, count; };
 static inline int launch_wide_segs(const WideSeg *segs, int nseg, bool latency, bool sym, PairIO io, const uint8_t *ref,
                                    const uint8_t *qer, const uint32_t *sorted, const Const &c, int w, cudaStream_t s)
 {
-    WideTable t; memset(&t, 0, sizeof t);
-    int launches = 0, blocks = 0;
-    auto flush = [&] {
-        t.first_block[t.nseg] = blocks;
-        if (blocks > 0) {
-            if (sym) bsw_wide_multi_kernel<true><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
-            else bsw_wide_multi_kernel<false><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
-            ++launches;
+    int launches = 0;
+    for (int pass = 0; pass < 2; ++pass) {                  /* pass 0: the R <= 10 shapes, pass 1: the R = 16 shapes */
+        WideTable t; memset(&t, 0, sizeof t);
+        int blocks = 0;
+        auto flush = [&] {
+            t.first_block[t.nseg] = blocks;
+            if (blocks > 0) {
+                if (pass == 0) {
+                    if (sym) bsw_wide_multi_kernel<true><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+                    else bsw_wide_multi_kernel<false><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+                } else {
+                    if (sym) bsw_wide_multi16_kernel<true><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+                    else bsw_wide_multi16_kernel<false><<<blocks, 128, 0, s>>>(io, ref, qer, sorted, t, c, w);
+                }
+                ++launches;
+            }
+            memset(&t, 0, sizeof t); blocks = 0;
+        };
+        for (int k = 0; k < nseg; ++k) {
+            if (segs[k].count <= 0) continue;
+            const int sh = latency ? wide_latency_shape(segs[k].cfg) : segs[k].cfg;
+            if ((wide_shape_regs(sh) == 16) != (pass == 1)) continue;
+            if (t.nseg == BSW_WIDE_MAXSEG) flush();
+            const int per_block = 128 / wide_shape_lanes(sh);
+            t.first_block[t.nseg] = blocks; t.first_pair[t.nseg] = segs[k].first; t.count[t.nseg] = segs[k].count; t.shape[t.nseg] = sh;
+            blocks += (segs[k].count + per_block - 1) / per_block;
+            t.nseg++;
         }
-        memset(&t, 0, sizeof t); blocks = 0;
-    };
-    for (int k = 0; k < nseg; ++k) {
-        if (segs[k].count <= 0) continue;
-        if (segs[k].cfg >= 4) {               /* (32, 16): 128 registers, its own kernel */
-            const int grid = (segs[k].count + 3) / 4;
-            if (sym) bsw_wide_kernel<32, 16, true><<<grid, 128, 0, s>>>(io, ref, qer, sorted, segs[k].first, segs[k].count, c, w);
-            else bsw_wide_kernel<32, 16, false><<<grid, 128, 0, s>>>(io, ref, qer, sorted, segs[k].first, segs[k].count, c, w);
-            ++launches;
-            continue;
-        }
-        if (t.nseg == BSW_WIDE_MAXSEG) flush();
-        const int sh = latency ? wide_latency_shape(segs[k].cfg) : segs[k].cfg, per_block = 128 / wide_shape_lanes(sh);
-        t.first_block[t.nseg] = blocks; t.first_pair[t.nseg] = segs[k].first; t.count[t.nseg] = segs[k].count; t.shape[t.nseg] = sh;
-        blocks += (segs[k].count + per_block - 1) / per_block;
-        t.nseg++;
+        flush();
     }
-    flush();
     return launches;
 }
 

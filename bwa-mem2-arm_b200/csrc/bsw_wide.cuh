@@ -72,13 +72,14 @@ static inline int ctz32(uint32_t v) { return __builtin_ctz(v); }
 
 #define BSW_WIDE_MAX_COLS 1024
 
-/* the (G, R) configurations instantiated by the library, smallest first; columns = G * 2R */
-#define BSW_WIDE_NCFG 5
-BSW_HD int wide_cfg_cols(int cfg)
-{
-    return cfg == 0 ? 8 * 10 : cfg == 1 ? 8 * 18 : cfg == 2 ? 16 * 18 : cfg == 3 ? 32 * 18 : 32 * 32;
-}
-BSW_HD int wide_cfg_lanes(int cfg) { return cfg <= 1 ? 8 : cfg == 2 ? 16 : 32; }
+/* the (G, R) configurations a pair is classified into, smallest first; columns = G * 2R.  These are the THROUGHPUT
+ * shapes: as few lanes per pair as the registers allow (the per-row bookkeeping -- masks, scan, shift, reductions -- costs
+ * ~320 instructions per warp whatever G is, so it is shared by 8 pairs at G = 4 and by one at G = 32).  Small batches
+ * run the same columns on more lanes (bsw_kernels.cuh wide_latency_shape). */
+#define BSW_WIDE_NCFG 8
+BSW_HD int wide_cfg_lanes(int cfg) { return cfg <= 1 ? 4 : cfg <= 3 ? 8 : cfg <= 5 ? 16 : 32; }
+BSW_HD int wide_cfg_regs(int cfg) { return cfg == 0 ? 10 : (cfg & 1) ? 16 : 9; }
+BSW_HD int wide_cfg_cols(int cfg) { return wide_cfg_lanes(cfg) * 2 * wide_cfg_regs(cfg); }   /* 80 128 144 256 288 512 576 1024 */
 
 /* smallest configuration that holds columns 0 .. len2, or -1 */
 BSW_HD int wide_cfg_for(int len2)

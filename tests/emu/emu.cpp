@@ -65,18 +65,24 @@ int emu_bsw_wide_impl(bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *q
     }
     for (int k = 0; k < BSW_WIDE_NCFG; ++k) {
         const std::vector<int> &v = by_cfg[k];
-        const int shape = latency ? (k == 1 ? 5 : k == 2 ? 6 : k) : k;
-        const int per = 32 / (shape <= 1 ? 8 : (shape == 2 || shape == 5) ? 16 : 32);
+        // the library's shape table (bsw_kernels.cuh): 0..7 = the configurations, 8..10 = their latency alternates
+        const int shape = latency ? (k == 0 ? 8 : k <= 2 ? 9 : k <= 4 ? 10 : k) : k;
+        const int lanes = shape <= 7 ? wide_cfg_lanes(shape) : shape == 8 ? 8 : shape == 9 ? 16 : 32;
+        const int per = 32 / lanes;
         for (size_t f = 0; f < v.size(); f += per) {
             const int cnt = (int)std::min<size_t>(per, v.size() - f);
             switch (shape) {
-            case 5: wide_warp<16, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            case 6: wide_warp<32, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            case 0: wide_warp<8, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            case 1: wide_warp<8, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            case 2: wide_warp<16, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            case 3: wide_warp<32, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
-            default: wide_warp<32, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 0: wide_warp<4, 10>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 1: wide_warp<4, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 2: wide_warp<8, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 3: wide_warp<8, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 4: wide_warp<16, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 5: wide_warp<16, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 6: wide_warp<32, 9>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 7: wide_warp<32, 16>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 8: wide_warp<8, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            case 9: wide_warp<16, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
+            default: wide_warp<32, 5>(c, w, pairs, v.data() + f, cnt, ref, qer, pairs); break;
             }
         }
     }

@@ -131,9 +131,11 @@ def test_bsw_wide_lanes_per_pair(ora):
     _check_wide(ora, P, r, q, w=5, zdrop=10)
     _check_wide(ora, P, r, q, w=1, zdrop=0, end_bonus=0)
     _check_wide(ora, P, r, q, w=30, min_cfg=2)
+    _check_wide(ora, P, r, q, w=60, min_cfg=3)
+    _check_wide(ora, P, r, q, w=3, zdrop=12, min_cfg=5)
     _check_wide(ora, P, r, q, w=37, o_del=4, e_del=2, o_ins=7, e_ins=1, zdrop=30, end_bonus=0, a=2, b=3)
     _check_wide(ora, P, r, q, w=2, o_del=0, o_ins=0)
-    # the shapes small batches run on: (16, 5) for up to 160 and (32, 5) for up to 320 columns
+    # the shapes small batches run on: (8, 5) for up to 80, (16, 5) for up to 160 and (32, 5) for up to 320 columns
     assert _check_wide(ora, P, r, q, latency=True).all()
     _check_wide(ora, P, r, q, w=9, zdrop=15, latency=True)
     P, r, q = ora.gen_random(60, 100, 300, 100, 400, h0min=1, h0max=200, sim=0.9, p_n=0.01, seed=15)
