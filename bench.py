@@ -524,7 +524,7 @@ def run_bsw(args):
             Rf.close()
     else:
         # the caller's protocol in C++: tools/stream_c5.cpp (worker threads over per-task slices, per-task shim objects, band retry)
-        T = max(1, c.cores // max(1, c.world))
+        T = max(1, 2 * c.cores // max(1, c.world))      # callers mostly sleep on their batch: two per core
         info, raw = stream_harness(ora, bswb200, L, R, lr, lq, rr, rq, n_reads, args.task_reads, T, 0, 3, tag=f"c1_{c.rank}")
         stream_cleanup(f"c1_{c.rank}")
         Ro2 = Ro.copy(); Ro2["h0"] = Rin["h0"]

@@ -208,7 +208,7 @@ struct Core {
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
     int wide_max = 32768;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
-    int wide_lat = 8192;             /* ... and up to this many on its shapes with more lanes per pair (latency) */
+    int wide_lat = 32768;             /* ... and up to this many on its shapes with more lanes per pair (latency) */
     int wide_split = 0;              /* staged batches in between: bins up to this index stay on the thread kernel */
     int mode = MODE_BSW;
     /* arenas declared with bsw_arena_begin */
@@ -263,7 +263,7 @@ void core_init(Core &k, int mode)
     k.trace = env_int("BSW_CUDA_TRACE", 0);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
     k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 32768);
-    k.wide_lat = env_int("BSW_CUDA_WIDE_LAT", 8192);
+    k.wide_lat = env_int("BSW_CUDA_WIDE_LAT", 32768);
     k.wide_split = env_int("BSW_CUDA_WIDE_SPLIT", 0);
 }
 

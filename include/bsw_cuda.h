@@ -260,7 +260,7 @@ void bsw_set_direct_min(bsw_t *h, int pairs);
  * kernel admits still use it). */
 void bsw_set_wide_max(bsw_t *h, int pairs);
 /* the whole kernel-choice policy of a handle: wide_max as above; calls / batches of up to wide_lat pairs (default
- * BSW_CUDA_WIDE_LAT = 8192) use the kernel's shapes with more lanes per pair (lowest latency); staged batches between
+ * BSW_CUDA_WIDE_LAT = 32768) use the kernel's shapes with more lanes per pair (lowest latency); staged batches between
  * wide_lat and wide_max keep the bins of up to wide_split x 16 columns on the thread kernel (default
  * BSW_CUDA_WIDE_SPLIT = 0: none).  Results never depend on it. */
 void bsw_set_wide_policy(bsw_t *h, int wide_max, int wide_lat, int wide_split);

@@ -661,7 +661,7 @@ def test_staged_batch_size_regimes(ora, bsw):
     d = ora.gen_bsw(60000, seed=0x7A1)
     P, r, q = d["left"]
     o, _ = _oracle_bsw(ora, P, r, q)
-    for n, wide_max, wide_lat, wide_split in ((1500, 32768, 8192, 0), (9000, 32768, 4096, 5), (9000, 32768, 4096, 0),
+    for n, wide_max, wide_lat, wide_split in ((1500, 32768, 32768, 0), (9000, 32768, 4096, 5), (9000, 32768, 4096, 0),
                                               (40000, 1 << 30, 8192, 9), (40000, 16384, 8192, 0)):
         h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
         h.set_direct_min(1 << 30); h.set_wide_policy(wide_max, wide_lat, wide_split)
