@@ -459,9 +459,9 @@ void launch_bsw(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs,
     launch_bsw_dp(k, rt, x, sl, pl, d_pairs, d_ref, d_qer, n, w, s);
 }
 
-/* kswv row-maximum scratch (kswv_core.cuh): rows x packed pairs x 2 B, rows = longest target among the PACKED pairs.
- * Launches are cut so that one launch's scratch stays below BSW_CUDA_ROWMAX_MB (default 2048 MB): sorted order is
- * longest query first, so a part is a contiguous range of sorted slots inside one bin. */
+/* kswv DP launches of a planned call: one registers-and-shuffles launch (kswv_sys.cuh) per non-empty query-length bin on
+ * the bin's stream -- queries with an N first (key bit 25; the general score table), each longest query first -- then
+ * the general 32-bit kernel for what prep did not admit. */
 void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref,
                     const uint8_t *d_qer, bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
 {
@@ -469,47 +469,27 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
     const PairIO io = pairio_records(d_pairs);
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
-    for (int qb = 1; qb <= BSW_NBINS; ++qb) n_packed += pl->hist[qb];
-    if (n_packed > 0) {
-        const size_t rows = (size_t)std::max(1, pl->max_len1_packed);
-        const size_t budget = (size_t)std::max(16, env_int("BSW_CUDA_ROWMAX_MB", 2048)) << 20;
-        /* slots per part, a multiple of 64 (one block = 64 slots) */
-        const size_t part = std::max<size_t>(64, (budget / (rows * sizeof(uint16_t))) & ~(size_t)63);
-        const long long stride = (long long)std::min<size_t>((size_t)n_packed, part);
-        sl.rowmax.reserve(rows * (size_t)stride * sizeof(uint16_t));
-        const bool one_part = (size_t)n_packed <= part;
-        int first = 0;
-        if (one_part) CK(cudaEventRecord(x.fork_ev, s));
+    const bool sym = k.c.oe_del == k.c.oe_ins;
+    unsigned used = 0;
+    CK(cudaEventRecord(x.fork_ev, s));
+    for (int pass = 0; pass < 2; ++pass)
         for (int qb = BSW_NBINS; qb >= 1; --qb) {
-            const int cnt = pl->hist[qb];
+            const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
             if (cnt <= 0) continue;
-            const int NE = qb * 16;
-            /* SYM=false on purpose: sharing h - oe puts a third op on kswv's f -> h -> f chain (measured 3 % slower) */
-            auto kern = kswv_packed_kernel<false>;
-            if (one_part) {
-                cudaStream_t bs = rt.bin_stream[qb];
-                CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
-                kern<<<(cnt + 63) / 64, 32, NE * BSW_WARP_ELEM_BYTES, bs>>>(io, d_ref, d_qer, d_aln, sorted, bintable_single(first, cnt, NE),
-                                                                          k.c, is8, phase, (uint16_t *)sl.rowmax.p, stride,
-                                                                          (unsigned long long *)x.cells.p);
-                CK(cudaGetLastError());
-                CK(cudaEventRecord(x.bin_ev[qb], bs));
-                CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
-                k.st.kernel_launches++;
-            } else {
-                /* budgeted: parts one after another on the call's stream, each indexing the scratch from its own first slot */
-                for (int off = 0; off < cnt; off += (int)part) {
-                    const int c2 = std::min<int>((int)part, cnt - off);
-                    kern<<<(c2 + 63) / 64, 32, NE * BSW_WARP_ELEM_BYTES, s>>>(io, d_ref, d_qer, d_aln, sorted, bintable_single(first + off, c2, NE),
-                                                                            k.c, is8, phase, (uint16_t *)sl.rowmax.p - (first + off), stride,
-                                                                            (unsigned long long *)x.cells.p);
-                    CK(cudaGetLastError());
-                    k.st.kernel_launches++;
-                }
-            }
-            first += cnt;
+            cudaStream_t bs = rt.bin_stream[qb];
+            if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+            used |= 1u << qb;
+            launch_kswv_sys(qb, sym, pass == 0, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
+                            k.c, is8, phase, (unsigned long long *)x.cells.p, bs);
+            CK(cudaGetLastError());
+            k.st.kernel_launches++;
+            n_packed += cnt;
         }
-    }
+    for (int qb = BSW_NBINS; qb >= 1; --qb)
+        if (used & (1u << qb)) {
+            CK(cudaEventRecord(x.bin_ev[qb], rt.bin_stream[qb]));
+            CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
+        }
     if (pl->n_general > 0) {
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
         int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));

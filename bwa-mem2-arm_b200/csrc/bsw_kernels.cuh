@@ -23,6 +23,7 @@
 #include "bsw_core.cuh"
 #include "bsw_core2.cuh"
 #include "kswv_core.cuh"
+#include "kswv_sys.cuh"
 #include "bsw_wide.cuh"
 #include "global_core.cuh"
 
@@ -82,9 +83,10 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         const int len1 = pairs[i].len1, len2 = pairs[i].len2, h0 = pairs[i].h0;
-        bool ok = (mode == MODE_BSW) ? packed_eligible(c, len1, len2, h0) : kswv_packed_eligible(c, len1, len2);
-        /* columns a thread needs: len2 + 1 (kswv), len2 + 4 (BSW: the sweep's slack, bsw_core2.cuh) */
-        const int qb = (len2 + (mode == MODE_BSW ? BSW_SWEEP_SLACK : 1) + 15) >> 4;
+        bool ok = (mode == MODE_BSW) ? packed_eligible(c, len1, len2, h0) : kswv_sys_eligible(c, len1, len2);
+        /* BSW: columns a thread needs = len2 + 4 (the sweep's slack, bsw_core2.cuh); kswv: the query's columns (kswv_sys.cuh) */
+        int qb = (len2 + (mode == MODE_BSW ? BSW_SWEEP_SLACK : 0) + 15) >> 4;
+        qb = qb < 1 ? 1 : qb;
         if (ok && qb * 16 > max_elems) ok = false;
         uint32_t key = 0;
         if (ok) {
@@ -92,11 +94,12 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
              * thread carries terminate, trim and widen alike */
             const uint32_t l1 = (uint32_t)(len1 >> 1) > 255u ? 255u : (uint32_t)(len1 >> 1);
             const uint32_t hh = mode == MODE_BSW ? ((uint32_t)h0 > 255u ? 255u : (uint32_t)h0) : 0u;
-            key = ((uint32_t)(len2 + 1) << 16) | (l1 << 8) | hh;
-            /* BSW: queries with an N go to the kernel variant with the general score table (bsw_core2.cuh, QN).  Only
-             * pairs inside the uploaded byte ranges are read here (the others make the host redo the chunk). */
+            key = mode == MODE_BSW ? ((uint32_t)(len2 + 1) << 16) | (l1 << 8) | hh
+                                   : ((uint32_t)(len2 + 1) << 16) | ((uint32_t)len1 << 5);     /* len1 <= KSWV_SYS_MAX_ROWS < 2048 */
+            /* queries with an N go to the kernel variant with the general score table (bsw_core2.cuh / kswv_sys.cuh, QN).
+             * Only pairs inside the uploaded byte ranges are read here (the others make the host redo the chunk). */
             const long long iq0 = pairs[i].idq;
-            const bool qn = mode == MODE_BSW && len2 > 0 && iq0 >= qlo && iq0 + len2 <= qhi && query_has_n(qer, iq0, len2);
+            const bool qn = len2 > 0 && iq0 >= qlo && iq0 + len2 <= qhi && query_has_n(qer, iq0, len2);
             if (qn) key |= 1u << 25;
             atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
             atomicMax(&s_misc[4], len1);
@@ -423,6 +426,75 @@ kswv_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
     }
     for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
     if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+/* ------------------------------------------------------------------ 4d. kswv in registers (kswv_sys.cuh)
+ * One warp per block = 32 / G groups of two pairs; group g of block b serves the sorted slots first + (b * 32 / G + g) * 2
+ * and + 1.  Dynamic shared memory: the `b` lists, cap words per pair. */
+template <int G, int C, bool SYM, bool QN>
+__global__ void __launch_bounds__(32)
+kswv_sys_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
+                const uint32_t *__restrict__ sorted_idx, int first, int count, Const c, int is8, int phase, int cap,
+                unsigned long long *cells)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint32_t *bl = reinterpret_cast<uint32_t *>(smem);
+    constexpr int NG = 32 / G;
+    const int lane = threadIdx.x, g = lane / G, gl = lane % G;
+    const int rel = ((int)blockIdx.x * NG + g) * 2;
+    const int pa = rel < count ? (int)sorted_idx[first + rel] : -1;
+    const int pb = rel + 1 < count ? (int)sorted_idx[first + rel + 1] : -1;
+    const PairIn A = load_pair(io, pa), B = load_pair(io, pb);
+    KswOut oa, ob;
+    kswv_sys_lane<G, C, SYM, QN>(c, is8, A, B, ref, qer, gl, bl + (size_t)(g * 2) * cap, bl + (size_t)(g * 2 + 1) * cap, oa, ob);
+    unsigned long long my_cells = 0;
+    if (gl == G - 1) {
+        if (pa >= 0) { kswv_store(aln, io, pa, oa, phase); my_cells += (unsigned long long)oa.cells; }
+        if (pb >= 0) { kswv_store(aln, io, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
+    }
+    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
+    if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
+}
+
+#define KSWV_SYS_G 8
+/* columns per lane the launch of bin qb (queries of up to qb * 16 bases) uses.  The common variant (symmetric gap sums, no
+ * N in the query) has one instantiation per bin; the three others share four shapes. */
+static inline int kswv_sys_cols(int qb, bool sym, bool qn)
+{
+    const int c = 2 * qb;
+    return (sym && !qn) ? c : (c + 7) & ~7;
+}
+
+static inline void launch_kswv_sys(int qb, bool sym, bool qn, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
+                                   const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
+                                   unsigned long long *cells, cudaStream_t s)
+{
+    constexpr int G = KSWV_SYS_G, NG = 32 / G;
+    const int cap = kswv_sys_list_cap(max_rows);
+    const int grid = (count + 2 * NG - 1) / (2 * NG);
+    const size_t smem = (size_t)NG * 2 * cap * sizeof(uint32_t);
+#define KSWV_SYS_LAUNCH(CC, SYM, QN) \
+    kswv_sys_kernel<G, CC, SYM, QN><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells)
+#define KSWV_SYS_COARSE(SYM, QN) \
+    switch (kswv_sys_cols(qb, SYM, QN)) { \
+    case 8: KSWV_SYS_LAUNCH(8, SYM, QN); break; case 16: KSWV_SYS_LAUNCH(16, SYM, QN); break; \
+    case 24: KSWV_SYS_LAUNCH(24, SYM, QN); break; default: KSWV_SYS_LAUNCH(32, SYM, QN); break; }
+    if (sym && !qn) {
+        switch (qb) {
+        case 1: KSWV_SYS_LAUNCH(2, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, true, false); break;
+        case 3: KSWV_SYS_LAUNCH(6, true, false); break;   case 4: KSWV_SYS_LAUNCH(8, true, false); break;
+        case 5: KSWV_SYS_LAUNCH(10, true, false); break;  case 6: KSWV_SYS_LAUNCH(12, true, false); break;
+        case 7: KSWV_SYS_LAUNCH(14, true, false); break;  case 8: KSWV_SYS_LAUNCH(16, true, false); break;
+        case 9: KSWV_SYS_LAUNCH(18, true, false); break;  case 10: KSWV_SYS_LAUNCH(20, true, false); break;
+        case 11: KSWV_SYS_LAUNCH(22, true, false); break; case 12: KSWV_SYS_LAUNCH(24, true, false); break;
+        case 13: KSWV_SYS_LAUNCH(26, true, false); break; case 14: KSWV_SYS_LAUNCH(28, true, false); break;
+        case 15: KSWV_SYS_LAUNCH(30, true, false); break; default: KSWV_SYS_LAUNCH(32, true, false); break;
+        }
+    } else if (sym) { KSWV_SYS_COARSE(true, true) }
+    else if (qn) { KSWV_SYS_COARSE(false, true) }
+    else { KSWV_SYS_COARSE(false, false) }
+#undef KSWV_SYS_COARSE
+#undef KSWV_SYS_LAUNCH
 }
 
 /* ------------------------------------------------------------------ 5b. kswv general */

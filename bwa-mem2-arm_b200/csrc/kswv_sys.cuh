@@ -1,0 +1,201 @@
+/*
+ * kswv_sys.cuh -- batched mate-rescue local alignment with the DP state in REGISTERS: G lanes of a warp form a
+ * systolic pipeline over the query columns of TWO pairs (kswv::getScores8/16, bwa-mem2 src/kswv.cpp; semantics =
+ * bwa ksw_u8 / ksw_i16 in exact arithmetic, SURVEY.md Appendix A.2 -- the same statement kswv_core.cuh implements).
+ *
+ * Why a second mapping next to the thread-owns-two-pairs kernel (kswv_core.cuh): that kernel keeps 6 bytes per
+ * column and thread in shared memory, which caps a 150-column launch at 7 warps per SM (ncu: 57 % of the issue slots
+ * used, three LSU instructions per cell vector).  ksw_u8 has no band and no trimming -- row i + 1 needs nothing from
+ * row i but the cells above it -- so the rows can be skewed over the lanes:
+ *
+ *   lane t of the group owns the padded columns [t*C, (t+1)*C): Hs[k] = H(i-1, c-1), E[k] = E(i, c), Q[k] = PRMT
+ *   selector of the query bases of both pairs (pair A in the low, pair B in the high 16 bits of every register, as
+ *   everywhere in this library).  In step s lane t sweeps its C columns of row i = s - t; what crosses a lane
+ *   boundary -- H(i, tC-1), F(i, tC), the row's running (max << 8 | 255 - column) key and the per-row score tables
+ *   (or the target bases, QN) -- travels by five one-lane shuffles per step.  No shared memory for the state, no
+ *   loads or stores in the cell loop, occupancy set by registers only.
+ *
+ * Exactness:
+ *   - the query is RIGHT-aligned in the G*C columns: column c holds query base c - pad (pad = G*C - qlen, per pair).
+ *     The pad columns come first and use a selector whose score is <= 0 for every target base (sign bytes of the row
+ *     table: 0 or -1; the N code when QN), so they evaluate to H = E = F = 0 exactly like the j = -1 boundary;
+ *     nothing needs a mask and the two pairs of a group may have different lengths;
+ *   - lanes that have no row yet (s < t) see all-zero score tables, so their state stays zero; rows past a pair's
+ *     target are fed the N base (scores <= 0: no value grows, the 16-bit halves cannot carry into each other) and are
+ *     ignored by the bookkeeping, which the LAST lane of the group does in row order: row maximum and its first
+ *     column from the key, (gmax, te, qe), the stop conditions (KSW_XSTOP score, 8-bit overflow), and ksw_u8's
+ *     `b` list -- kept as a list ((score << 16 | row) entries in shared memory, at most rows / 2 + 1 of them) and
+ *     resolved once te and score are final, as ksw_u8 does.  A pair that stops early only shortens the loop.
+ * Admission (kswv_sys_eligible): the byte-key limits of kswv_core.cuh (scores and columns < 256) and at most
+ * KSWV_SYS_MAX_ROWS target bases (sizes the list).  Everything else goes to the general 32-bit kernel.
+ *
+ * __host__ __device__: tests/emu/warp_emu.h runs the same source on an emulated warp.
+ */
+#pragma once
+#include "bsw_core.cuh"
+#include "bsw_core2.cuh"
+#include "kswv_core.cuh"
+#include "bsw_wide.cuh"
+
+namespace bswk {
+
+#define KSWV_SYS_MAX_ROWS 2046
+#define KSWV_SYS_MAX_COLS 256
+
+BSW_HD bool kswv_sys_eligible(const Const &c, int len1, int len2)
+{
+    return kswv_packed_eligible(c, len1, len2) && len1 <= KSWV_SYS_MAX_ROWS && c.a <= 120 && c.b <= 120 && c.ambig <= 0;
+}
+/* `b`-list entries a pair of `rows` target bases can produce, plus the open one */
+BSW_HD int kswv_sys_list_cap(int rows) { return (rows >> 1) + 2; }
+
+/*
+ * One lane of a G-lane group; gl = its index.  Every lane of the warp must call this together.  blA / blB: the
+ * group's `b`-list storage for pair A / B (kswv_sys_list_cap(max rows) words each; only the last lane touches it).
+ * Results are valid in lane G - 1 only.
+ */
+template <int G, int C, bool SYM, bool QN>
+BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn &B,
+                          const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, int gl,
+                          uint32_t *blA, uint32_t *blB, KswOut &oa, KswOut &ob)
+{
+    static_assert(G * C <= KSWV_SYS_MAX_COLS, "column index must fit the key's byte");
+    const PairIn *in[2] = { &A, &B };
+    uint32_t *bl[2] = { blA, blB };
+    const int shift = c.b > -c.ambig ? c.b : -c.ambig;       /* |min(mat)| */
+    int qlen[2], tlen[2], pad[2], lim[2], minsc[2], endsc[2], gmax[2], te[2], qk[2], bsc[2], brow[2], bn[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const PairIn &x = *in[p];
+        qlen[p] = x.valid ? x.len2 : 0;
+        tlen[p] = x.valid ? x.len1 : 0;
+        pad[p] = G * C - qlen[p];
+        lim[p] = tlen[p] > 0 ? tlen[p] : 0;                  /* rows the bookkeeping still wants */
+        minsc[p] = (x.h0 & KSW_XSUBO_) ? (x.h0 & 0xffff) : 0x10000;
+        endsc[p] = (x.h0 & KSW_XSTOP_) ? (x.h0 & 0xffff) : 0x10000;
+        gmax[p] = 0; te[p] = -1; qk[p] = 0; bsc[p] = 0; brow[p] = -2; bn[p] = 0;
+    }
+
+    /* ---- query selectors of this lane's columns; state = 0 ---- */
+    uint32_t Hs[C], E[C], Q[C];
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        const int col = gl * C + k;
+        uint32_t qv[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const int j = col - pad[p];
+            uint32_t q = 4u;                                 /* pad column */
+            if (j >= 0) { q = qer[(*in[p]).idq + j]; q = q > 4u ? 4u : q; }
+            qv[p] = q;
+        }
+        if (QN) Q[k] = bsw_selector<true>(qv[0], qv[1]);
+        else {
+            /* in-range: byte q of the pair's row table and its sign; pad: the sign of byte 0 twice (0 or -1) */
+            const uint32_t sa = qv[0] > 3u ? 0x88u : (((8u | qv[0]) << 4) | qv[0]);
+            const uint32_t sb = qv[1] > 3u ? 0xCCu : (((12u | qv[1]) << 4) | (4u | qv[1]));
+            Q[k] = (sb << 8) | sa;
+        }
+        Hs[k] = 0u; E[k] = 0u;
+    }
+
+    const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
+    const uint32_t LUTLO = launder(lut_lo(c)), LUTHI = launder(AMBW);
+    const uint32_t NOD = pack2(-c.oe_del, -c.oe_del), NOI = pack2(-c.oe_ins, -c.oe_ins);
+    const uint32_t NED = pack2(-c.e_del, -c.e_del), NEI = pack2(-c.e_ins, -c.e_ins);
+    const uint32_t KOFF = (uint32_t)(gl * C) * 0x00010001u;
+
+    /* target bases: lane 0 of the group reads them (aligned words, four rows per refill) */
+    TWin tw[2];
+    twin_init(tw[0], ref, A.idr, tlen[0], gl == 0 && tlen[0] > 0);
+    twin_init(tw[1], ref, B.idr, tlen[1], gl == 0 && tlen[1] > 0);
+    uint32_t win[2] = { 0u, 0u };
+
+    const int rows_all = mx(lim[0], lim[1]);
+    /* row tables of the step (QN: LA = target selector T, LB unused).  A lane without a row yet: all-zero tables / the N code */
+    uint32_t LA = QN ? 0x4444u : 0u, LB = 0u;
+    uint32_t hout = 0u, fout = 0u, kout = 0u;
+    int s = 0;
+    while (w_any(gl == G - 1 && rows_all > 0 && s - (G - 1) < mx(lim[0], lim[1]))) {
+        /* ---- what the left neighbour produced in the previous step ---- */
+        uint32_t nLA = w_shfl_up(LA, 1, G), nLB = 0u;
+        if (!QN) nLB = w_shfl_up(LB, 1, G);
+        uint32_t hin = w_shfl_up(hout, 1, G), f = w_shfl_up(fout, 1, G), kin = w_shfl_up(kout, 1, G);
+        if (gl == 0) {
+            if ((s & 3) == 0) { win[0] = twin_refill(tw[0], s >> 2); win[1] = twin_refill(tw[1], s >> 2); }
+            const uint32_t ta = s < tlen[0] ? (win[0] & 0xffu) : 4u, tb = s < tlen[1] ? (win[1] & 0xffu) : 4u;
+            win[0] >>= 8; win[1] >>= 8;
+            if (QN) nLA = ta * 0x0011u | tb * 0x1100u;
+            else { nLA = bsw_lutrow(MISW, XW, AMBW, ta * 8u); nLB = bsw_lutrow(MISW, XW, AMBW, tb * 8u); }
+            hin = 0u; f = 0u; kin = 0u;
+        }
+        LA = nLA; LB = nLB;
+
+        /* ---- this lane's C cells of row s - gl (A.2) ---- */
+        uint32_t carry = hin, key = 0u, kprev = 0u;
+#pragma unroll
+        for (int k = 0; k < C; ++k) {
+            const uint32_t sc = QN ? p_perm(LUTLO, LUTHI, p_xsel(Q[k], LA)) : p_perm(LA, LB, Q[k]);
+            const uint32_t h = p_max3_relu(p_add(Hs[k], sc), E[k], f);
+            if (SYM) {
+                const uint32_t u = p_add(h, NOD);
+                E[k] = p_addmax_relu(E[k], NED, u);
+                f = p_addmax_relu(f, NEI, u);
+            } else {
+                E[k] = p_addmax_relu(h, NOD, p_add(E[k], NED));
+                f = p_addmax_relu(h, NOI, p_add(f, NEI));
+            }
+            Hs[k] = carry; carry = h;
+            const uint32_t kc = (h << 8) + (0x00ff00ffu - (uint32_t)k * 0x00010001u);
+            if (k & 1) key = p_max3u(key, kprev, kc); else kprev = kc;
+        }
+        if (C & 1) key = p_maxu(key, kprev);
+        hout = carry; fout = f;
+        kout = p_maxu(kin, key - KOFF);              /* column byte 255 - (gl*C + k): ties keep the smaller column */
+
+        /* ---- bookkeeping of row s - (G-1), in the last lane (A.2) ---- */
+        const int row = s - (G - 1);
+        if (gl == G - 1 && row >= 0) {
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                if (row < lim[p]) {
+                    const int kp = half_u(kout, p), imax = kp >> 8;
+                    if (imax >= minsc[p]) {
+                        if (brow[p] + 1 != row) {            /* new entry (brow = -2: none yet) */
+                            if (brow[p] >= 0) bl[p][bn[p]++] = ((uint32_t)bsc[p] << 16) | (uint32_t)brow[p];
+                            bsc[p] = imax; brow[p] = row;
+                        } else if (bsc[p] < imax) { bsc[p] = imax; brow[p] = row; }
+                    }
+                    if (imax > gmax[p]) {
+                        gmax[p] = imax; te[p] = row; qk[p] = kp & 0xff;
+                        if ((is8 && imax + shift >= 255) || imax >= endsc[p]) lim[p] = row + 1;
+                    }
+                }
+            }
+        }
+        ++s;
+    }
+
+    KswOut *out[2] = { &oa, &ob };
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        KswOut &o = *out[p];
+        const bool ovf = is8 && gmax[p] + shift >= 255;
+        o.score = ovf ? 255 : gmax[p]; o.te = te[p]; o.qe = -1; o.score2 = -1; o.te2 = -1;
+        o.cells = (long long)lim[p] * qlen[p];
+        if (gl == G - 1 && !ovf) {
+            /* ksw_u8: qe = smallest j attaining the maximum of row te; Hmax stays all-zero when gmax == 0 */
+            o.qe = qlen[p] > 0 ? (gmax[p] > 0 ? 255 - qk[p] - pad[p] : 0) : -1;
+            if (minsc[p] < 0x10000) {
+                const int d = (o.score + c.maxsc - 1) / c.maxsc, low = te[p] - d, high = te[p] + d;
+                if (brow[p] >= 0) bl[p][bn[p]++] = ((uint32_t)bsc[p] << 16) | (uint32_t)brow[p];
+                for (int k = 0; k < bn[p]; ++k) {
+                    const int e = (int)(bl[p][k] & 0xffffu), sc2 = (int)(bl[p][k] >> 16);
+                    if ((e < low || e > high) && sc2 > o.score2) { o.score2 = sc2; o.te2 = e; }
+                }
+            }
+        }
+    }
+}
+
+} /* namespace bswk */

@@ -16,7 +16,7 @@ def lib():
         so = os.path.join(HERE, "emu", "libbswemu.so")
         src = os.path.join(HERE, "emu", "emu.cpp")
         deps = [src, os.path.join(HERE, "emu", "warp_emu.h")] + [os.path.join(ROOT, "bwa-mem2-arm_b200", "csrc", f)
-                                                                 for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh", "bsw_wide.cuh", "global_core.cuh")]
+                                                                 for f in ("bsw_core.cuh", "bsw_core2.cuh", "kswv_core.cuh", "kswv_sys.cuh", "bsw_wide.cuh", "global_core.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src])
         _lib = C.CDLL(so)

@@ -11,6 +11,7 @@
 #include "../../bwa-mem2-arm_b200/csrc/bsw_core2.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/kswv_core.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/bsw_wide.cuh"
+#include "../../bwa-mem2-arm_b200/csrc/kswv_sys.cuh"
 #include "../../bwa-mem2-arm_b200/csrc/global_core.cuh"
 #include "../../include/bsw_cuda.h"
 
@@ -151,12 +152,94 @@ static void kput(bsw_kswr_t *aln, const bsw_seqpair_t &sp, int i, const KswOut &
     else { bsw_kswr_t *a = &aln[sp.regid]; if (a->score == o.score) { a->tb = a->te - o.te; a->qb = a->qe - o.qe; } }
 }
 
+}   // extern "C"
+
+// registers-and-shuffles kernel (kswv_sys.cuh): one emulated warp per 32 / G groups of two pairs
+template <int G, int C, bool SYM, bool QN>
+static void sys_warp(const Const &c, int is8, const bsw_seqpair_t *pairs, const int *ids, int cnt, const uint8_t *ref,
+                     const uint8_t *qer, KswOut *res)
+{
+    constexpr int NG = 32 / G;
+    int maxrows = 0;
+    for (int k = 0; k < cnt; ++k) maxrows = std::max(maxrows, pairs[ids[k]].len1);
+    const int cap = kswv_sys_list_cap(maxrows);
+    std::vector<uint32_t> bl((size_t)NG * 2 * cap, 0xdeadbeefu);
+    warp_emu::run([&](int lane) {
+        const int g = lane / G, gl = lane % G;
+        PairIn P[2];
+        for (int u = 0; u < 2; ++u) {
+            const int k = g * 2 + u;
+            if (k < cnt) { const bsw_seqpair_t &p = pairs[ids[k]]; P[u] = { p.idr, p.idq, p.len1, p.len2, p.h0, 1 }; }
+            else P[u] = { 0, 0, 0, 0, 0, 0 };
+        }
+        KswOut oa, ob;
+        kswv_sys_lane<G, C, SYM, QN>(c, is8, P[0], P[1], ref, qer, gl, bl.data() + (size_t)(g * 2) * cap, bl.data() + (size_t)(g * 2 + 1) * cap, oa, ob);
+        if (gl == G - 1) { if (g * 2 < cnt) res[g * 2] = oa; if (g * 2 + 1 < cnt) res[g * 2 + 1] = ob; }
+    });
+}
+
+template <int G, int C>
+static void sys_warp_v(const Const &c, int is8, bool qn, const bsw_seqpair_t *pairs, const int *ids, int cnt, const uint8_t *ref,
+                       const uint8_t *qer, KswOut *res)
+{
+    const bool sym = c.oe_del == c.oe_ins;
+    if (sym) { if (qn) sys_warp<G, C, true, true>(c, is8, pairs, ids, cnt, ref, qer, res); else sys_warp<G, C, true, false>(c, is8, pairs, ids, cnt, ref, qer, res); }
+    else { if (qn) sys_warp<G, C, false, true>(c, is8, pairs, ids, cnt, ref, qer, res); else sys_warp<G, C, false, false>(c, is8, pairs, ids, cnt, ref, qer, res); }
+}
+
+extern "C" {
+
 int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln, int n,
              int o_del, int e_del, int o_ins, int e_ins, int a, int b, int ambig,
              int is8, int phase, int force_general, long long *cells_out)
 {
     Const c = mk(o_del, e_del, o_ins, e_ins, 0, 0, a, b, ambig);
     std::vector<int> el, ge;
+    if ((force_general & 0xff) == 2) {
+        // mode 2: the registers-and-shuffles kernel for every pair it admits, the general kernel for the rest.  Bits 8..15:
+        // minimum columns per lane (a larger shape than the query needs: more pad columns, same results); bit 16: run
+        // every group through the QN variant.  Pairs are taken in input order, two per group, like the sorted order
+        // of the library only that neighbouring lengths differ more.
+        const int min_c = (force_general >> 8) & 0xff;
+        const bool all_qn = (force_general >> 16) & 1;
+        std::vector<int> by[2][17];
+        for (int i = 0; i < n; ++i) {
+            if (!kswv_sys_eligible(c, pairs[i].len1, pairs[i].len2)) { ge.push_back(i); continue; }
+            bool qn = all_qn;
+            for (int j = 0; j < pairs[i].len2; ++j) qn |= qer[pairs[i].idq + j] > 3;
+            int qb = (pairs[i].len2 + 15) >> 4; qb = qb < 1 ? 1 : qb;
+            while (2 * qb < min_c && qb < 16) ++qb;
+            by[qn][qb].push_back(i);
+        }
+        int tot = 0;
+        for (int qn = 0; qn < 2; ++qn)
+            for (int qb = 1; qb <= 16; ++qb) {
+                const std::vector<int> &v = by[qn][qb];
+                for (size_t f = 0; f < v.size(); f += 8) {
+                    const int cnt = (int)std::min<size_t>(8, v.size() - f);
+                    KswOut res[8];
+                    switch (qb) {
+#define SYS_CASE(QB) case QB: sys_warp_v<8, 2 * QB>(c, is8, qn != 0, pairs, v.data() + f, cnt, ref, qer, res); break;
+                    SYS_CASE(1) SYS_CASE(2) SYS_CASE(3) SYS_CASE(4) SYS_CASE(5) SYS_CASE(6) SYS_CASE(7) SYS_CASE(8)
+                    SYS_CASE(9) SYS_CASE(10) SYS_CASE(11) SYS_CASE(12) SYS_CASE(13) SYS_CASE(14) SYS_CASE(15) SYS_CASE(16)
+#undef SYS_CASE
+                    }
+                    for (int k = 0; k < cnt; ++k) {
+                        const int i = v[f + k];
+                        kput(aln, pairs[i], i, res[k], phase); if (cells_out) cells_out[i] = res[k].cells;
+                    }
+                    tot += cnt;
+                }
+            }
+        for (int i : ge) {
+            PairIn P = { pairs[i].idr, pairs[i].idq, pairs[i].len1, pairs[i].len2, pairs[i].h0, 1 };
+            KswOut o;
+            std::vector<int2> he(P.len2 + 2); std::vector<int> rm(P.len1 + 2);
+            kswv_general_thread<int>(c, is8, P, ref, qer, he.data(), 1, rm.data(), 1, o);
+            kput(aln, pairs[i], i, o, phase); if (cells_out) cells_out[i] = o.cells;
+        }
+        return tot;
+    }
     for (int i = 0; i < n; ++i)
         (!force_general && kswv_packed_eligible(c, pairs[i].len1, pairs[i].len2) ? el : ge).push_back(i);
     for (size_t k = 0; k < el.size(); k += 2) {

@@ -77,6 +77,53 @@ def _check_kswv(ora, pairs, ref, qer, is8):
         assert (ao == ae).all()
 
 
+def _check_kswv_sys(ora, pairs, ref, qer, is8, mode=2, **sc):
+    """kswv_sys.cuh (DP state in registers, rows skewed over the 8 lanes of a group) on an emulated warp."""
+    prm = ora.make_params(**sc) if sc else ora.make_params()
+    ao = np.zeros(len(pairs), ora.KSWR)
+    ae = np.zeros(len(pairs), ora.KSWR)
+    _, oc = ora.kswv_batch(pairs, ref, qer, ao, prm, is8, 0, 4, True)
+    ec, npk = emu.kswv(pairs, ref, qer, ae, is8, 0, force_general=mode, **sc)
+    assert (ao == ae).all() and (oc == ec).all()
+    p1, r1, q1 = ora.kswv_phase1_inputs(pairs, ref, qer, ao)
+    ora.kswv_batch(p1, r1, q1, ao, prm, is8, 1, 4)
+    emu.kswv(p1, r1, q1, ae, is8, 1, force_general=mode, **sc)
+    assert (ao == ae).all()
+    return npk
+
+
+def test_kswv_sys_kernel(ora):
+    P, r, q = ora.gen_kswv(240)
+    assert _check_kswv_sys(ora, P, r, q, 1) == len(P)
+    _check_kswv_sys(ora, P, r, q, 1, mode=2 | (1 << 16))          # every group through the general score table (QN)
+    _check_kswv_sys(ora, P, r, q, 1, mode=2 | (26 << 8))          # a larger shape than needed: more pad columns
+    P, r, q = ora.gen_kswv(100, qlen=250, tmin=400, tmax=700, seed=5)
+    _check_kswv_sys(ora, P, r, q, 0)
+    # ragged lengths (neighbouring pairs of one group differ), empty sequences, N in queries and targets, early stops
+    P, r, q = ora.gen_random(800, 0, 40, 0, 80, sim=0.7, p_n=0.05, seed=3)
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 5
+    _check_kswv_sys(ora, P, r, q, 1)
+    P, r, q = ora.gen_random(400, 0, 200, 0, 300, sim=0.8, p_n=0.002, seed=4)
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | 9
+    _check_kswv_sys(ora, P, r, q, 0)
+    _check_kswv_sys(ora, P, r, q, 1)
+    # 8-bit overflow rule, tandem repeats (second-best list), scoring variants (asymmetric gap sums: the non-SYM variants)
+    P, r, q = ora.gen_kswv(80, qlen=255, tmin=300, tmax=400, seed=9, div=0.0,
+                           xtra=ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 19)
+    _check_kswv_sys(ora, P, r, q, 1)
+    P, r, q = ora.gen_kswv(200, qlen=60, tmin=200, tmax=400, seed=11, p_contain=0.9, div=0.05)
+    for i in range(len(P)):
+        o, l = int(P["idr"][i]), int(P["len1"][i])
+        h = l // 2
+        r[o + h:o + 2 * h] = r[o:o + h]
+    _check_kswv_sys(ora, P, r, q, 1)
+    P, r, q = ora.gen_random(300, 0, 120, 0, 300, sim=0.85, p_n=0.004, seed=14)
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | 9
+    for sc in (dict(o_del=4, e_del=2, o_ins=7, e_ins=1, a=2, b=3), dict(o_del=1, e_del=1, o_ins=1, e_ins=1, a=1, b=9),
+               dict(o_del=12, e_del=3, o_ins=5, e_ins=2, a=1, b=1)):
+        _check_kswv_sys(ora, P, r, q, 0, **sc)
+
+
 def test_kswv_c4_shape(ora):
     P, r, q = ora.gen_kswv(1200)
     _check_kswv(ora, P, r, q, 1)
