@@ -205,6 +205,7 @@ struct Core {
     int count_cells = 0;
     int trace = 0;                   /* BSW_CUDA_TRACE: host-side timing of every direct call on stderr */
     int chunk_pairs = 1 << 19;
+    bool kswv_lanes4 = false;                     /* kswv_sys.cuh: four lanes per group for bins of up to 160 columns */
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
     int wide_max = 32768;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
@@ -259,6 +260,7 @@ void core_init(Core &k, int mode)
     for (size_t i = 0; i < k.devs.size(); ++i) (void)devrt(k.devs[i]);       /* first handle on a device builds its runtime */
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
+    k.kswv_lanes4 = env_int("BSW_CUDA_KSWV_LANES4", 0) != 0;
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.trace = env_int("BSW_CUDA_TRACE", 0);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
@@ -479,7 +481,7 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
             cudaStream_t bs = rt.bin_stream[qb];
             if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             used |= 1u << qb;
-            launch_kswv_sys(qb, sym, pass == 0, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
+            launch_kswv_sys(qb, sym, pass == 0, k.kswv_lanes4, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
                             k.c, is8, phase, (unsigned long long *)x.cells.p, bs);
             CK(cudaGetLastError());
             k.st.kernel_launches++;

@@ -456,39 +456,58 @@ kswv_sys_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__res
     if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
 }
 
-#define KSWV_SYS_G 8
-/* columns per lane the launch of bin qb (queries of up to qb * 16 bases) uses.  The common variant (symmetric gap sums, no
- * N in the query) has one instantiation per bin; the three others share four shapes. */
-static inline int kswv_sys_cols(int qb, bool sym, bool qn)
+/* columns per lane the launch of bin qb (queries of up to qb * 16 bases) uses with G lanes per group.  The common variant
+ * (symmetric gap sums, no N in the query) has one instantiation per bin; the three others share four shapes. */
+static inline int kswv_sys_cols(int qb, int G, bool sym, bool qn)
 {
-    const int c = 2 * qb;
+    const int c = 16 * qb / G;
     return (sym && !qn) ? c : (c + 7) & ~7;
 }
 
-static inline void launch_kswv_sys(int qb, bool sym, bool qn, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
-                                   const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
-                                   unsigned long long *cells, cudaStream_t s)
+template <int G, int C, bool SYM, bool QN>
+static inline void launch_kswv_sys_shape(int first, int count, int max_rows, PairIO io, const uint8_t *ref, const uint8_t *qer,
+                                         bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
+                                         unsigned long long *cells, cudaStream_t s)
 {
-    constexpr int G = KSWV_SYS_G, NG = 32 / G;
+    constexpr int NG = 32 / G;
     const int cap = kswv_sys_list_cap(max_rows);
     const int grid = (count + 2 * NG - 1) / (2 * NG);
     const size_t smem = (size_t)NG * 2 * cap * sizeof(uint32_t);
-#define KSWV_SYS_LAUNCH(CC, SYM, QN) \
-    kswv_sys_kernel<G, CC, SYM, QN><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells)
+    kswv_sys_kernel<G, C, SYM, QN><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells);
+}
+
+/* lanes4: four lanes per group for the bins of up to 160 columns (twice the cells per step and lane: the per-step
+ * shuffles and bookkeeping weigh half as much; 40 columns per lane is what the register file takes) */
+static inline void launch_kswv_sys(int qb, bool sym, bool qn, bool lanes4, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
+                                   const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
+                                   unsigned long long *cells, cudaStream_t s)
+{
+#define KSWV_SYS_LAUNCH(G, CC, SYM, QN) \
+    launch_kswv_sys_shape<G, CC, SYM, QN>(first, count, max_rows, io, ref, qer, aln, sorted, c, is8, phase, cells, s)
 #define KSWV_SYS_COARSE(SYM, QN) \
-    switch (kswv_sys_cols(qb, SYM, QN)) { \
-    case 8: KSWV_SYS_LAUNCH(8, SYM, QN); break; case 16: KSWV_SYS_LAUNCH(16, SYM, QN); break; \
-    case 24: KSWV_SYS_LAUNCH(24, SYM, QN); break; default: KSWV_SYS_LAUNCH(32, SYM, QN); break; }
+    switch (kswv_sys_cols(qb, 8, SYM, QN)) { \
+    case 8: KSWV_SYS_LAUNCH(8, 8, SYM, QN); break; case 16: KSWV_SYS_LAUNCH(8, 16, SYM, QN); break; \
+    case 24: KSWV_SYS_LAUNCH(8, 24, SYM, QN); break; default: KSWV_SYS_LAUNCH(8, 32, SYM, QN); break; }
     if (sym && !qn) {
+        if (lanes4 && qb <= 10) {
+            switch (qb) {
+            case 1: KSWV_SYS_LAUNCH(4, 4, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, 8, true, false); break;
+            case 3: KSWV_SYS_LAUNCH(4, 12, true, false); break;  case 4: KSWV_SYS_LAUNCH(4, 16, true, false); break;
+            case 5: KSWV_SYS_LAUNCH(4, 20, true, false); break;  case 6: KSWV_SYS_LAUNCH(4, 24, true, false); break;
+            case 7: KSWV_SYS_LAUNCH(4, 28, true, false); break;  case 8: KSWV_SYS_LAUNCH(4, 32, true, false); break;
+            case 9: KSWV_SYS_LAUNCH(4, 36, true, false); break;  default: KSWV_SYS_LAUNCH(4, 40, true, false); break;
+            }
+            return;
+        }
         switch (qb) {
-        case 1: KSWV_SYS_LAUNCH(2, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, true, false); break;
-        case 3: KSWV_SYS_LAUNCH(6, true, false); break;   case 4: KSWV_SYS_LAUNCH(8, true, false); break;
-        case 5: KSWV_SYS_LAUNCH(10, true, false); break;  case 6: KSWV_SYS_LAUNCH(12, true, false); break;
-        case 7: KSWV_SYS_LAUNCH(14, true, false); break;  case 8: KSWV_SYS_LAUNCH(16, true, false); break;
-        case 9: KSWV_SYS_LAUNCH(18, true, false); break;  case 10: KSWV_SYS_LAUNCH(20, true, false); break;
-        case 11: KSWV_SYS_LAUNCH(22, true, false); break; case 12: KSWV_SYS_LAUNCH(24, true, false); break;
-        case 13: KSWV_SYS_LAUNCH(26, true, false); break; case 14: KSWV_SYS_LAUNCH(28, true, false); break;
-        case 15: KSWV_SYS_LAUNCH(30, true, false); break; default: KSWV_SYS_LAUNCH(32, true, false); break;
+        case 1: KSWV_SYS_LAUNCH(8, 2, true, false); break;   case 2: KSWV_SYS_LAUNCH(8, 4, true, false); break;
+        case 3: KSWV_SYS_LAUNCH(8, 6, true, false); break;   case 4: KSWV_SYS_LAUNCH(8, 8, true, false); break;
+        case 5: KSWV_SYS_LAUNCH(8, 10, true, false); break;  case 6: KSWV_SYS_LAUNCH(8, 12, true, false); break;
+        case 7: KSWV_SYS_LAUNCH(8, 14, true, false); break;  case 8: KSWV_SYS_LAUNCH(8, 16, true, false); break;
+        case 9: KSWV_SYS_LAUNCH(8, 18, true, false); break;  case 10: KSWV_SYS_LAUNCH(8, 20, true, false); break;
+        case 11: KSWV_SYS_LAUNCH(8, 22, true, false); break; case 12: KSWV_SYS_LAUNCH(8, 24, true, false); break;
+        case 13: KSWV_SYS_LAUNCH(8, 26, true, false); break; case 14: KSWV_SYS_LAUNCH(8, 28, true, false); break;
+        case 15: KSWV_SYS_LAUNCH(8, 30, true, false); break; default: KSWV_SYS_LAUNCH(8, 32, true, false); break;
         }
     } else if (sym) { KSWV_SYS_COARSE(true, true) }
     else if (qn) { KSWV_SYS_COARSE(false, true) }

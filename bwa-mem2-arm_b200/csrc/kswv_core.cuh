@@ -33,7 +33,10 @@ BSW_HD bool kswv_packed_eligible(const Const &c, int len1, int len2)
 
 #if defined(__CUDA_ARCH__)
 __device__ __forceinline__ uint32_t p_max3_relu(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_s16x2_relu(a, b, c); }
+__device__ __forceinline__ uint32_t p_max_relu(uint32_t a, uint32_t b) { return __vimax_s16x2_relu(a, b); }
 #else
+static inline uint32_t p_max_relu(uint32_t a, uint32_t b)
+{ return pk(imax(imax(lo16(a), lo16(b)), 0), imax(imax(hi16(a), hi16(b)), 0)); }
 static inline uint32_t p_max3_relu(uint32_t a, uint32_t b, uint32_t c)
 { return pk(imax(imax(imax(lo16(a), lo16(b)), lo16(c)), 0), imax(imax(imax(hi16(a), hi16(b)), hi16(c)), 0)); }
 #endif

@@ -8,7 +8,7 @@
  * used, three LSU instructions per cell vector).  ksw_u8 has no band and no trimming -- row i + 1 needs nothing from
  * row i but the cells above it -- so the rows can be skewed over the lanes:
  *
- *   lane t of the group owns the padded columns [t*C, (t+1)*C): Hs[k] = H(i-1, c-1), E[k] = E(i, c), Q[k] = PRMT
+ *   lane t of the group owns the padded columns [t*C, (t+1)*C): Hc[k] = H(i-1, c), E[k] = E(i, c), Q[k] = PRMT
  *   selector of the query bases of both pairs (pair A in the low, pair B in the high 16 bits of every register, as
  *   everywhere in this library).  In step s lane t sweeps its C columns of row i = s - t; what crosses a lane
  *   boundary -- H(i, tC-1), F(i, tC), the row's running (max << 8 | 255 - column) key and the per-row score tables
@@ -77,7 +77,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
     }
 
     /* ---- query selectors of this lane's columns; state = 0 ---- */
-    uint32_t Hs[C], E[C], Q[C];
+    uint32_t Hc[C], E[C], Q[C];
 #pragma unroll
     for (int k = 0; k < C; ++k) {
         const int col = gl * C + k;
@@ -96,7 +96,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
             const uint32_t sb = qv[1] > 3u ? 0xCCu : (((12u | qv[1]) << 4) | (4u | qv[1]));
             Q[k] = (sb << 8) | sa;
         }
-        Hs[k] = 0u; E[k] = 0u;
+        Hc[k] = 0u; E[k] = 0u;
     }
 
     const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
@@ -104,39 +104,65 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
     const uint32_t NOD = pack2(-c.oe_del, -c.oe_del), NOI = pack2(-c.oe_ins, -c.oe_ins);
     const uint32_t NED = pack2(-c.e_del, -c.e_del), NEI = pack2(-c.e_ins, -c.e_ins);
     const uint32_t KOFF = (uint32_t)(gl * C) * 0x00010001u;
+    /* h * 256 + column as an IMAD (the FMA pipe idles, the ALU pipe is the bound): the multiplier must be a value ptxas
+     * cannot fold, or it emits an ALU-pipe LEA */
+    const uint32_t K256 = 256u + ((uint32_t)is8 & 2u);
 
-    /* target bases: lane 0 of the group reads them (aligned words, four rows per refill) */
-    TWin tw[2];
-    twin_init(tw[0], ref, A.idr, tlen[0], gl == 0 && tlen[0] > 0);
-    twin_init(tw[1], ref, B.idr, tlen[1], gl == 0 && tlen[1] > 0);
-    uint32_t win[2] = { 0u, 0u };
+    /* target bases, G rows at a time: in the steps with s % G == 0 lane l of the group turns the bases of row s + l (fetched
+     * one batch ahead) into that row's score tables; lane 0 picks row s's up with one indexed shuffle per table.  Rows
+     * past a pair's target read as N. */
+    uint32_t TA = 0u, TB = 0u, nb[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) nb[p] = gl < tlen[p] ? (uint32_t)ref[(*in[p]).idr + gl] : 4u;
 
-    const int rows_all = mx(lim[0], lim[1]);
+    /* bookkeeping state of the last lane, both pairs packed: rows left, best (max << 8 | 255 - column) key and its max, te */
+    uint32_t R = pack2(lim[0], lim[1]), GM = 0u, BK = 0u, TE = 0xffffffffu;
+    const uint32_t ONE2 = 0x00010001u, NEG1 = 0xffffffffu;
+    uint32_t NTH, NMS;
+    {
+        int th[2], ms[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            th[p] = mn(mn(endsc[p], is8 ? 255 - shift : 0x7fff), 0x7fff);     /* stop: gmax >= endsc or the 8-bit overflow */
+            ms[p] = mn(minsc[p], 0x7fff);
+        }
+        NTH = pack2(-th[0], -th[1]); NMS = pack2(-ms[0], -ms[1]);
+    }
+
     /* row tables of the step (QN: LA = target selector T, LB unused).  A lane without a row yet: all-zero tables / the N code */
     uint32_t LA = QN ? 0x4444u : 0u, LB = 0u;
-    uint32_t hout = 0u, fout = 0u, kout = 0u;
+    uint32_t hout = 0u, fout = 0u, kout = 0u, dprev = 0u;
     int s = 0;
-    while (w_any(gl == G - 1 && rows_all > 0 && s - (G - 1) < mx(lim[0], lim[1]))) {
-        /* ---- what the left neighbour produced in the previous step ---- */
-        uint32_t nLA = w_shfl_up(LA, 1, G), nLB = 0u;
-        if (!QN) nLB = w_shfl_up(LB, 1, G);
-        uint32_t hin = w_shfl_up(hout, 1, G), f = w_shfl_up(fout, 1, G), kin = w_shfl_up(kout, 1, G);
-        if (gl == 0) {
-            if ((s & 3) == 0) { win[0] = twin_refill(tw[0], s >> 2); win[1] = twin_refill(tw[1], s >> 2); }
-            const uint32_t ta = s < tlen[0] ? (win[0] & 0xffu) : 4u, tb = s < tlen[1] ? (win[1] & 0xffu) : 4u;
-            win[0] >>= 8; win[1] >>= 8;
-            if (QN) nLA = ta * 0x0011u | tb * 0x1100u;
-            else { nLA = bsw_lutrow(MISW, XW, AMBW, ta * 8u); nLB = bsw_lutrow(MISW, XW, AMBW, tb * 8u); }
-            hin = 0u; f = 0u; kin = 0u;
+    while (w_any(gl == G - 1 && R != 0u)) {
+        if ((s & (G - 1)) == 0) {
+            const uint32_t ta = nb[0] > 4u ? 4u : nb[0], tb = nb[1] > 4u ? 4u : nb[1];
+            if (QN) TA = ta * 0x0011u | tb * 0x1100u;
+            else { TA = bsw_lutrow(MISW, XW, AMBW, ta * 8u); TB = bsw_lutrow(MISW, XW, AMBW, tb * 8u); }
+#pragma unroll
+            for (int p = 0; p < 2; ++p) { const int rn = s + G + gl; nb[p] = rn < tlen[p] ? (uint32_t)ref[(*in[p]).idr + rn] : 4u; }
         }
+        /* ---- row s's tables (lane 0) / what the left neighbour produced in the previous step (the others) ---- */
+        const uint32_t fA = w_shfl(TA, s & (G - 1), G);
+        uint32_t nLA = w_shfl_up(LA, 1, G), nLB = 0u, fB = 0u;
+        if (!QN) { fB = w_shfl(TB, s & (G - 1), G); nLB = w_shfl_up(LB, 1, G); }
+        uint32_t hin = w_shfl_up(hout, 1, G), f = w_shfl_up(fout, 1, G), kin = w_shfl_up(kout, 1, G);
+        if (gl == 0) { nLA = fA; nLB = fB; hin = 0u; f = 0u; kin = 0u; }
         LA = nLA; LB = nLB;
 
-        /* ---- this lane's C cells of row s - gl (A.2) ---- */
-        uint32_t carry = hin, key = 0u, kprev = 0u;
+        /* ---- this lane's C cells of row s - gl (A.2) ----
+         * Hc[k] = H(i-1, c) is updated in place: the first operation of cell k + 1 -- t = max(H(i-1, c) + s, E, 0), all
+         * of the cell that does not hang on the f chain -- is issued before cell k overwrites Hc[k] with H(i, c). */
+        uint32_t key = 0u, kprev = 0u;
+        uint32_t t = p_addmax_relu(dprev, QN ? p_perm(LUTLO, LUTHI, p_xsel(Q[0], LA)) : p_perm(LA, LB, Q[0]), E[0]);
+        dprev = hin;                                     /* H(i, c0 - 1): the diagonal of the next row's first cell */
 #pragma unroll
         for (int k = 0; k < C; ++k) {
-            const uint32_t sc = QN ? p_perm(LUTLO, LUTHI, p_xsel(Q[k], LA)) : p_perm(LA, LB, Q[k]);
-            const uint32_t h = p_max3_relu(p_add(Hs[k], sc), E[k], f);
+            uint32_t tn = 0u;
+            if (k + 1 < C) {
+                const uint32_t sc = QN ? p_perm(LUTLO, LUTHI, p_xsel(Q[k + 1], LA)) : p_perm(LA, LB, Q[k + 1]);
+                tn = p_addmax_relu(Hc[k], sc, E[k + 1]);
+            }
+            const uint32_t h = p_max_relu(t, f);
             if (SYM) {
                 const uint32_t u = p_add(h, NOD);
                 E[k] = p_addmax_relu(E[k], NED, u);
@@ -145,36 +171,49 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
                 E[k] = p_addmax_relu(h, NOD, p_add(E[k], NED));
                 f = p_addmax_relu(h, NOI, p_add(f, NEI));
             }
-            Hs[k] = carry; carry = h;
-            const uint32_t kc = (h << 8) + (0x00ff00ffu - (uint32_t)k * 0x00010001u);
+            Hc[k] = h;
+            const uint32_t kc = h * K256 + (0x00ff00ffu - (uint32_t)k * 0x00010001u);     /* IMAD: the FMA pipe idles here */
             if (k & 1) key = p_max3u(key, kprev, kc); else kprev = kc;
+            t = tn;
         }
         if (C & 1) key = p_maxu(key, kprev);
-        hout = carry; fout = f;
+        hout = Hc[C - 1]; fout = f;
         kout = p_maxu(kin, key - KOFF);              /* column byte 255 - (gl*C + k): ties keep the smaller column */
 
-        /* ---- bookkeeping of row s - (G-1), in the last lane (A.2) ---- */
-        const int row = s - (G - 1);
-        if (gl == G - 1 && row >= 0) {
+        /* ---- bookkeeping of row s - (G-1), in the last lane (A.2), both pairs at once ---- */
+        if (gl == G - 1 && s >= G - 1) {
+            const int row = s - (G - 1);
+            const uint32_t LM = p_minu(R, ONE2) * 0xffffu;           /* 0xffff per pair that still wants this row */
+            const uint32_t IM = st_e(kout) & LM;                     /* row maxima */
+            const uint32_t nGM = p_maxu(GM, IM);
+            const uint32_t chg = nGM ^ GM;
+            if (chg) {                                               /* imax > gmax: new (gmax, te, qe); stop conditions */
+                const uint32_t CM = p_minu(chg, ONE2) * 0xffffu;
+                TE = (TE & ~CM) | (((uint32_t)row * ONE2) & CM);
+                BK = (BK & ~CM) | (kout & CM);
+                GM = nGM;
+                const uint32_t stopb = ~p_add(nGM, NTH) & CM & 0x80008000u;
+                if (stopb & 0x00008000u) { lim[0] = row + 1; R &= 0xffff0000u; }
+                if (stopb & 0x80000000u) { lim[1] = row + 1; R &= 0x0000ffffu; }
+            }
+            const uint32_t qb = ~p_add(IM, NMS) & LM & 0x80008000u;  /* imax >= minsc: ksw_u8's `b` list */
+            if (qb) {
 #pragma unroll
-            for (int p = 0; p < 2; ++p) {
-                if (row < lim[p]) {
-                    const int kp = half_u(kout, p), imax = kp >> 8;
-                    if (imax >= minsc[p]) {
+                for (int p = 0; p < 2; ++p)
+                    if (qb & (p ? 0x80000000u : 0x00008000u)) {
+                        const int imax = half_u(IM, p);
                         if (brow[p] + 1 != row) {            /* new entry (brow = -2: none yet) */
                             if (brow[p] >= 0) bl[p][bn[p]++] = ((uint32_t)bsc[p] << 16) | (uint32_t)brow[p];
                             bsc[p] = imax; brow[p] = row;
                         } else if (bsc[p] < imax) { bsc[p] = imax; brow[p] = row; }
                     }
-                    if (imax > gmax[p]) {
-                        gmax[p] = imax; te[p] = row; qk[p] = kp & 0xff;
-                        if ((is8 && imax + shift >= 255) || imax >= endsc[p]) lim[p] = row + 1;
-                    }
-                }
             }
+            R = p_addmax_relu(R, NEG1, 0u);
         }
         ++s;
     }
+#pragma unroll
+    for (int p = 0; p < 2; ++p) { gmax[p] = half_u(GM, p); te[p] = half_s(TE, p); qk[p] = half_u(BK, p) & 0xff; }
 
     KswOut *out[2] = { &oa, &ob };
 #pragma unroll
