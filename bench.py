@@ -685,7 +685,7 @@ def run_kswv(args):
                     "h2d_bytes_per_step": est["h2d_bytes"] // args.steps, "d2h_bytes_per_step": est["d2h_bytes"] // args.steps,
                     "api": "kswv_getScores8/16 phase 0 then phase 1 on pinned host buffers (the caller's reversed-prefix hand-off between them is host work and not in the time)"},
             "gpu_launches": int(launches),
-            "roofline": roofline(bswb200, c, 7, cells_step, kms, ms_step, "kswv_packed_kernel", "kswv_packed_kernel"),
+            "roofline": roofline(bswb200, c, 7, cells_step, kms, ms_step, "kswv_sys_kernel", "kswv_sys_kernel"),
             "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "setup_s": time.perf_counter() - t_setup, "oracle_full_config_s": oracle_s,
         }
     reduce_and_print(c, args, line, [ms_total, e2e_ms, kernel_ms_step], [float(cells_step), float(npairs)])

@@ -44,7 +44,7 @@ namespace {
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
-    DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch, rowmax;
+    DevBuf pairs, ref, qer, aln, keys_a, keys_b, idx_a, idx_b, cubtmp, plan, scratch;
     DevBuf px_prev, px_list, px_sub, px_count;   /* device-side caller protocol (bsw_dev_extendChained) */
     DevBuf kx_off, kx_pairs, kx_ref, kx_qer;     /* device-side kswv hand-off (kswv_dev_align2) */
     DevBuf gx_eh, gx_z, gx_zoff, gx_coff, gx_jobs, gx_cigar;   /* CIGAR generation (bsw_global2) */
@@ -146,8 +146,7 @@ DevRt &devrt(int dev)
     if (max_smem > r->smem_optin) die("device shared memory too small for the packed kernels");
     const void *fns[] = { (const void *)bsw_packed_kernel<false, false, false>, (const void *)bsw_packed_kernel<false, true, false>,
                           (const void *)bsw_packed_kernel<false, false, true>, (const void *)bsw_packed_kernel<false, true, true>,
-                          (const void *)bsw_packed_kernel<true, false, true>, (const void *)bsw_packed_kernel<true, true, true>,
-                          (const void *)kswv_packed_kernel<false> };
+                          (const void *)bsw_packed_kernel<true, false, true>, (const void *)bsw_packed_kernel<true, true, true> };
     for (const void *fn : fns) {
         CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
         CK(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
@@ -208,6 +207,7 @@ struct Core {
     bool kswv_lanes4 = false;                     /* kswv_sys.cuh: four lanes per group for bins of up to 160 columns */
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
+    long long direct_bytes = 8ll << 20;  /* ... unless they carry at least this many bases (call_is_heavy) */
     int wide_max = 32768;            /* calls / batches up to this many pairs run on the lanes-per-pair kernel */
     int wide_lat = 32768;             /* ... and up to this many on its shapes with more lanes per pair (latency) */
     int wide_split = 0;              /* staged batches in between: bins up to this index stay on the thread kernel */
@@ -264,6 +264,7 @@ void core_init(Core &k, int mode)
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.trace = env_int("BSW_CUDA_TRACE", 0);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
+    k.direct_bytes = (long long)std::max(1, env_int("BSW_CUDA_DIRECT_MB", 8)) << 20;
     k.wide_max = env_int("BSW_CUDA_WIDE_MAX", 32768);
     k.wide_lat = env_int("BSW_CUDA_WIDE_LAT", 32768);
     k.wide_split = env_int("BSW_CUDA_WIDE_SPLIT", 0);
@@ -823,13 +824,14 @@ inline bool bytes_have_n(const uint8_t *p, int len)
 /* class of one pair: the same rules prep_kernel applies on the device (bsw_kernels.cuh) */
 inline int classify(const Core &k, const bsw_seqpair_t &p, const uint8_t *qer)
 {
-    const bool ok = k.mode == MODE_BSW ? packed_eligible(k.c, p.len1, p.len2, p.h0) : kswv_packed_eligible(k.c, p.len1, p.len2);
-    const int qb = (p.len2 + (k.mode == MODE_BSW ? BSW_SWEEP_SLACK : 1) + 15) >> 4;
+    const bool ok = k.mode == MODE_BSW ? packed_eligible(k.c, p.len1, p.len2, p.h0) : kswv_sys_eligible(k.c, p.len1, p.len2);
+    int qb = (p.len2 + (k.mode == MODE_BSW ? BSW_SWEEP_SLACK : 0) + 15) >> 4;
+    qb = qb < 1 ? 1 : qb;
     if (!ok || qb > BSW_NBINS) {
         if (k.mode == MODE_BSW && wide_eligible(k.c, p.len1, p.len2, p.h0)) return CLS_WIDE0 + wide_cfg_for(p.len2);
         return CLS_GENERAL;
     }
-    if (k.mode == MODE_BSW && p.len2 > 0 && bytes_have_n(qer + p.idq, p.len2)) return BSW_NBINS + qb;
+    if (p.len2 > 0 && bytes_have_n(qer + p.idq, p.len2)) return BSW_NBINS + qb;
     return qb;
 }
 
@@ -920,12 +922,24 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
     }
 }
 
+/* The staged route exists to MERGE the small calls of many host threads; its callers pack every base themselves.  A single
+ * call that already carries a device batch worth of work -- at least BSW_CUDA_DIRECT_MB of bases (default 8), estimated
+ * from 16 evenly spaced pairs -- takes the direct route however few pairs it has (50 k mate-rescue pairs of 250 x 550 bp:
+ * 31 ms staged, 3.4 ms direct). */
+bool call_is_heavy(const Core &k, const bsw_seqpair_t *pairs, int n)
+{
+    if (n < 2048) return false;
+    long long sum = 0;
+    for (int t = 0; t < 16; ++t) { const bsw_seqpair_t &p = pairs[(long long)t * (n - 1) / 15]; sum += std::max(p.len1, 0) + std::max(p.len2, 0); }
+    return sum * (long long)n / 16 >= k.direct_bytes;
+}
+
 void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check)
 {
     k.st.calls++;
     if (n <= 0) return;
     if (!pairs || !ref || !qer) die("null buffer passed to getScores");
-    if (n >= k.direct_min || k.count_cells || k.timing) direct_call_bsw(k, pairs, ref, qer, n, w, tier8_check);
+    if (n >= k.direct_min || k.count_cells || k.timing || call_is_heavy(k, pairs, n)) direct_call_bsw(k, pairs, ref, qer, n, w, tier8_check);
     else staged_call(k, pairs, ref, qer, nullptr, n, w, tier8_check, 0, 0);
 }
 
@@ -937,7 +951,7 @@ void host_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uin
     if (!pairs || !ref || !qer || !aln) die("null buffer passed to kswv getScores");
     if (phase == 1)
         for (int i = 0; i < n; ++i) if (pairs[i].regid < 0) die("kswv phase 1: negative regid");
-    if (n >= k.direct_min || k.timing) direct_call_kswv(k, pairs, ref, qer, aln, n, is8, phase);
+    if (n >= k.direct_min || k.timing || call_is_heavy(k, pairs, n)) direct_call_kswv(k, pairs, ref, qer, aln, n, is8, phase);
     else staged_call(k, pairs, ref, qer, aln, n, 0, 0, is8, phase);
 }
 

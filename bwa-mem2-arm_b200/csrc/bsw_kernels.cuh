@@ -8,10 +8,12 @@
  *   2. cub radix sort   descending: longest queries first (heavy tiles first),
  *                       pairs the packed kernel does not admit last (key 0).
  *   3. histogram read-back (one 200-byte D2H): the host derives each bin's sorted range.
- *   4. *_packed_kernel  one launch per non-empty bin, longest queries first.  A block is ONE
+ *   4. bsw_packed_kernel one launch per non-empty bin, longest queries first.  A block is ONE
  *                       warp = 64 pairs (2 per thread); its dynamic shared memory holds exactly
  *                       that bin's DP rows (NE x 192 B), so the number of resident warps per SM
  *                       is set by the query length, with no block-level barrier anywhere.
+ *      kswv_sys_kernel  one launch per non-empty bin: a warp = 4 groups of 8 lanes, two pairs per group,
+ *                       DP state in registers (kswv_sys.cuh).
  *   5. *_general_kernel 32-bit path for the (rare) pairs step 1 did not admit.
  */
 #pragma once
@@ -41,7 +43,7 @@ struct Plan {
     int hist_w[BSW_WIDE_NCFG + 1]; /* BSW: pairs only the lanes-per-pair kernel admits (16-bit state), by configuration */
     int n_general;                 /* pairs routed to the general kernel */
     int max_len1;                  /* over all pairs                      */
-    int max_len1_packed;           /* over the pairs the packed kernels take (sizes kswv's row-maximum scratch) */
+    int max_len1_packed;           /* over the pairs the packed kernels take (sizes kswv's `b` lists in shared memory) */
     int max_len2_general;
     int bad_pairs;                 /* contract violations seen by prep    */
     int oob_pairs;                 /* pairs whose bases fall outside the uploaded byte ranges */
@@ -398,37 +400,7 @@ __device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const P
     }
 }
 
-/* ------------------------------------------------------------------ 4b. kswv packed */
-template <bool SYM>   /* only <false> is instantiated: sharing h - oe puts a third op on kswv's f -> h -> f chain (3 % slower) */
-__global__ void __launch_bounds__(32)
-kswv_packed_kernel(PairIO io, const uint8_t *__restrict__ ref,
-                   const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
-                   const uint32_t *__restrict__ sorted_idx, const __grid_constant__ BinTable tbl, Const c, int is8, int phase,
-                   uint16_t *rowmax, long long rm_stride, unsigned long long *cells)
-{
-    extern __shared__ __align__(16) uint8_t smem[];
-    const int lane = threadIdx.x;
-    int slot0, bin_end, NE;
-    bintable_lookup(tbl, blockIdx.x, slot0, bin_end, NE);
-    uint32_t *he = reinterpret_cast<uint32_t *>(smem) + lane;
-    uint16_t *qs = reinterpret_cast<uint16_t *>(smem + (size_t)NE * 128) + lane;
-    const int slot = slot0 + lane * 2;
-    const int pa = slot < bin_end ? (int)sorted_idx[slot] : -1;
-    const int pb = slot + 1 < bin_end ? (int)sorted_idx[slot + 1] : -1;
-    unsigned long long my_cells = 0;
-    if (pa >= 0) {
-        PairIn A = load_pair(io, pa), B = load_pair(io, pb);
-        KswOut oa, ob;
-        kswv_packed_thread<32, SYM>(c, is8, A, B, ref, qer, he, qs, rowmax + slot, rm_stride, oa, ob);
-        kswv_store(aln, io, pa, oa, phase);
-        my_cells += (unsigned long long)oa.cells;
-        if (pb >= 0) { kswv_store(aln, io, pb, ob, phase); my_cells += (unsigned long long)ob.cells; }
-    }
-    for (int o = 16; o; o >>= 1) my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o);
-    if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
-}
-
-/* ------------------------------------------------------------------ 4d. kswv in registers (kswv_sys.cuh)
+/* ------------------------------------------------------------------ 4b. kswv in registers (kswv_sys.cuh)
  * One warp per block = 32 / G groups of two pairs; group g of block b serves the sorted slots first + (b * 32 / G + g) * 2
  * and + 1.  Dynamic shared memory: the `b` lists, cap words per pair. */
 template <int G, int C, bool SYM, bool QN>

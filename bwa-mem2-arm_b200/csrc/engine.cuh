@@ -110,7 +110,7 @@ struct StagedSlot {
     char *h_rec = nullptr, *h_seq = nullptr, *h_res = nullptr;
     char *d_rec = nullptr, *d_seq = nullptr, *d_res = nullptr;
     uint32_t *d_sorted = nullptr;
-    DevBuf scratch, rowmax;
+    DevBuf scratch;
     cudaStream_t stream = nullptr, stream2 = nullptr;
     cudaEvent_t done_ev = nullptr, fork_ev = nullptr, join_ev = nullptr;
     long long t_submit = 0;
@@ -456,11 +456,16 @@ inline void Engine::submit(StagedSlot &s)
     } else {
         bsw_kswr_t *d_aln = (bsw_kswr_t *)s.d_res;
         if (n_packed > 0) {
-            const BinTable &t = tb[1];
-            s.rowmax.reserve((size_t)std::max(1, s.max_len1_packed) * (size_t)n_packed * sizeof(uint16_t));
-            kswv_packed_kernel<false><<<t.first_block[t.nbins], 32, maxne[1] * BSW_WARP_ELEM_BYTES, q>>>(
-                io, seq, seq, d_aln, s.d_sorted, t, key.c, key.is8, 0, (uint16_t *)s.rowmax.p, (long long)n_packed, d_cells);
-            ++launches;
+            /* one registers-and-shuffles launch per non-empty bin (kswv_sys.cuh): queries with an N first, longest bin first */
+            const bool sym = key.c.oe_del == key.c.oe_ins;
+            for (int pass = 0; pass < 2; ++pass) {
+                const BinTable &t = tb[pass];
+                for (int b = 0; b < t.nbins; ++b) {
+                    launch_kswv_sys(t.ne[b] / 16, sym, pass == 0, false, t.first_pair[b], t.first_pair[b + 1] - t.first_pair[b],
+                                    std::max(1, s.max_len1_packed), io, seq, seq, d_aln, s.d_sorted, key.c, key.is8, 0, d_cells, q);
+                    ++launches;
+                }
+            }
         }
         if (n_general > 0) {
             const size_t he_b = (size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2);

@@ -1,19 +1,20 @@
 /*
  * kswv_sys.cuh -- batched mate-rescue local alignment with the DP state in REGISTERS: G lanes of a warp form a
  * systolic pipeline over the query columns of TWO pairs (kswv::getScores8/16, bwa-mem2 src/kswv.cpp; semantics =
- * bwa ksw_u8 / ksw_i16 in exact arithmetic, SURVEY.md Appendix A.2 -- the same statement kswv_core.cuh implements).
+ * bwa ksw_u8 / ksw_i16 in exact arithmetic).
  *
- * Why a second mapping next to the thread-owns-two-pairs kernel (kswv_core.cuh): that kernel keeps 6 bytes per
- * column and thread in shared memory, which caps a 150-column launch at 7 warps per SM (ncu: 57 % of the issue slots
- * used, three LSU instructions per cell vector).  ksw_u8 has no band and no trimming -- row i + 1 needs nothing from
- * row i but the cells above it -- so the rows can be skewed over the lanes:
+ * Why not the thread-owns-two-pairs mapping of the BSW kernel (rounds 1-2 shipped one, kswv_packed_kernel): its rows cost
+ * 6 bytes per column and thread of shared memory, which capped a 150-column launch at 7 warps per SM (ncu: 57 % of the
+ * issue slots used, three LSU instructions per cell vector, 0.40 of the DPX peak), and it kept a row-maximum scratch of
+ * rows x pairs x 2 B in HBM.  ksw_u8 has no band and no trimming -- row i + 1 needs nothing from row i but the cells
+ * above it -- so the rows can be skewed over the lanes:
  *
  *   lane t of the group owns the padded columns [t*C, (t+1)*C): Hc[k] = H(i-1, c), E[k] = E(i, c), Q[k] = PRMT
  *   selector of the query bases of both pairs (pair A in the low, pair B in the high 16 bits of every register, as
  *   everywhere in this library).  In step s lane t sweeps its C columns of row i = s - t; what crosses a lane
  *   boundary -- H(i, tC-1), F(i, tC), the row's running (max << 8 | 255 - column) key and the per-row score tables
- *   (or the target bases, QN) -- travels by five one-lane shuffles per step.  No shared memory for the state, no
- *   loads or stores in the cell loop, occupancy set by registers only.
+ *   (or the target bases, QN) -- travels by one-lane shuffles (five to seven per step).  No shared memory for the
+ *   state, no loads or stores in the cell loop, occupancy set by registers only.  ncu: ALU pipe 85 % busy.
  *
  * Exactness:
  *   - the query is RIGHT-aligned in the G*C columns: column c holds query base c - pad (pad = G*C - qlen, per pair).
@@ -26,7 +27,7 @@
  *     column from the key, (gmax, te, qe), the stop conditions (KSW_XSTOP score, 8-bit overflow), and ksw_u8's
  *     `b` list -- kept as a list ((score << 16 | row) entries in shared memory, at most rows / 2 + 1 of them) and
  *     resolved once te and score are final, as ksw_u8 does.  A pair that stops early only shortens the loop.
- * Admission (kswv_sys_eligible): the byte-key limits of kswv_core.cuh (scores and columns < 256) and at most
+ * Admission (kswv_sys_eligible): scores and columns < 256 (the key is max << 8 | column in 16 bits) and at most
  * KSWV_SYS_MAX_ROWS target bases (sizes the list).  Everything else goes to the general 32-bit kernel.
  *
  * __host__ __device__: tests/emu/warp_emu.h runs the same source on an emulated warp.

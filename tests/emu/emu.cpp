@@ -194,9 +194,10 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
              int is8, int phase, int force_general, long long *cells_out)
 {
     Const c = mk(o_del, e_del, o_ins, e_ins, 0, 0, a, b, ambig);
-    std::vector<int> el, ge;
-    if ((force_general & 0xff) == 2) {
-        // mode 2: the registers-and-shuffles kernel for every pair it admits, the general kernel for the rest.  Bits 8..15:
+    std::vector<int> ge;
+    if ((force_general & 0xff) != 1) {
+        // the library's routing: the registers-and-shuffles kernel (kswv_sys.cuh) for every pair it admits, the general kernel
+        // for the rest (force_general = 1: the general kernel for all).  Bits 8..15:
         // minimum columns per lane (a larger shape than the query needs: more pad columns, same results); bit 16: run
         // every group through the QN variant.  Pairs are taken in input order, two per group, like the sorted order
         // of the library only that neighbouring lengths differ more.
@@ -240,21 +241,7 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         }
         return tot;
     }
-    for (int i = 0; i < n; ++i)
-        (!force_general && kswv_packed_eligible(c, pairs[i].len1, pairs[i].len2) ? el : ge).push_back(i);
-    for (size_t k = 0; k < el.size(); k += 2) {
-        PairIn A, B; KswOut oa, ob;
-        int ia = el[k], ib = k + 1 < el.size() ? el[k + 1] : -1;
-        A = { pairs[ia].idr, pairs[ia].idq, pairs[ia].len1, pairs[ia].len2, pairs[ia].h0, 1 };
-        if (ib >= 0) B = { pairs[ib].idr, pairs[ib].idq, pairs[ib].len1, pairs[ib].len2, pairs[ib].h0, 1 };
-        else B = { 0, 0, 0, 0, 0, 0 };
-        int qm = A.len2 > B.len2 ? A.len2 : B.len2, tm = A.len1 > B.len1 ? A.len1 : B.len1;
-        std::vector<uint32_t> he(qm + 2); std::vector<uint16_t> qs(qm + 2), rm(tm + 2);
-        // the library always launches kswv_packed_kernel<false> (bsw_api.cu launch_kswv_dp): that is what runs here
-        kswv_packed_thread<1, false>(c, is8, A, B, ref, qer, he.data(), qs.data(), rm.data(), 1, oa, ob);
-        kput(aln, pairs[ia], ia, oa, phase); if (cells_out) cells_out[ia] = oa.cells;
-        if (ib >= 0) { kput(aln, pairs[ib], ib, ob, phase); if (cells_out) cells_out[ib] = ob.cells; }
-    }
+    for (int i = 0; i < n; ++i) ge.push_back(i);
     for (int i : ge) {
         PairIn P = { pairs[i].idr, pairs[i].idq, pairs[i].len1, pairs[i].len2, pairs[i].h0, 1 };
         KswOut o;
@@ -262,7 +249,7 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         kswv_general_thread<int>(c, is8, P, ref, qer, he.data(), 1, rm.data(), 1, o);
         kput(aln, pairs[i], i, o, phase); if (cells_out) cells_out[i] = o.cells;
     }
-    return (int)el.size();
+    return 0;
 }
 
 

@@ -77,7 +77,7 @@ def _check_kswv(ora, pairs, ref, qer, is8):
         assert (ao == ae).all()
 
 
-def _check_kswv_sys(ora, pairs, ref, qer, is8, mode=2, **sc):
+def _check_kswv_sys(ora, pairs, ref, qer, is8, mode=0, **sc):
     """kswv_sys.cuh (DP state in registers, rows skewed over the 8 lanes of a group) on an emulated warp."""
     prm = ora.make_params(**sc) if sc else ora.make_params()
     ao = np.zeros(len(pairs), ora.KSWR)
@@ -95,8 +95,8 @@ def _check_kswv_sys(ora, pairs, ref, qer, is8, mode=2, **sc):
 def test_kswv_sys_kernel(ora):
     P, r, q = ora.gen_kswv(240)
     assert _check_kswv_sys(ora, P, r, q, 1) == len(P)
-    _check_kswv_sys(ora, P, r, q, 1, mode=2 | (1 << 16))          # every group through the general score table (QN)
-    _check_kswv_sys(ora, P, r, q, 1, mode=2 | (26 << 8))          # a larger shape than needed: more pad columns
+    _check_kswv_sys(ora, P, r, q, 1, mode=1 << 16)          # every group through the general score table (QN)
+    _check_kswv_sys(ora, P, r, q, 1, mode=26 << 8)          # a larger shape than needed: more pad columns
     P, r, q = ora.gen_kswv(100, qlen=250, tmin=400, tmax=700, seed=5)
     _check_kswv_sys(ora, P, r, q, 0)
     # ragged lengths (neighbouring pairs of one group differ), empty sequences, N in queries and targets, early stops
