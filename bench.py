@@ -480,7 +480,8 @@ def run_bsw(args):
     if tries == 1:
         hcalls = [(pin(x[0]), (h_lr, h_lq) if x[3] is lr else (h_rr, h_rq), x[5]) for x in calls]
 
-        def step_e2e(arena=True):
+        def step_e2e(arena=True, defer=False):
+            sw.arena_defer(arena and defer)
             cur = None
             for hp, (hr, hq), tier in hcalls:
                 if arena and cur is not hr:
@@ -497,6 +498,10 @@ def run_bsw(args):
             check(f"e2e {'left' if x[3] is lr else 'right'} tier{tier}", side_o[tiers == 0] if tier == 8 else side_o[tiers != 0], hp)
         e2e_api = "bsw_getScores8/bsw_getScores16 on pinned host SeqPair/sequence buffers; the two sequence arenas of each side declared once (bsw_arena_begin/end)"
         if wl == "c2":
+            sw.reset_stats(); ms = time_host(c, args, lambda: step_e2e(True, True)); s2 = sw.stats()
+            variants["arena_deferred"] = {"ms_per_step": ms / args.steps, "h2d_bytes_per_step": s2["h2d_bytes"] // (args.steps + 2),
+                                          "api": "arenas declared + bsw_arena_defer: a tier call may return before its last chunks are home, "
+                                                 "bsw_arena_end completes the bracket (measured: no gain, the step is bound by PCIe bytes)"}
             sw.reset_stats(); ms = time_host(c, args, lambda: step_e2e(False)); s2 = sw.stats()
             variants["strict"] = {"ms_per_step": ms / args.steps, "h2d_bytes_per_step": s2["h2d_bytes"] // (args.steps + 2),
                                   "api": "bsw_getScores8/16 only: each tier call uploads the byte range of the shared arenas it touches"}

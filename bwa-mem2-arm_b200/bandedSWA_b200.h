@@ -64,6 +64,7 @@ public:
     void arenaBegin(const uint8_t *seqBufRef, size_t refBytes, const uint8_t *seqBufQer, size_t qerBytes)
     { bsw_arena_begin(h_, seqBufRef, refBytes, seqBufQer, qerBytes); }
     void arenaEnd() { bsw_arena_end(h_); }
+    void arenaDefer(bool on) { bsw_arena_defer(h_, on ? 1 : 0); }
     /* targets from the reference resident on the GPU (bsw_ref_upload of the .pac): rpos[i] as bns_fetch_seq counts
      * (doubled-strand coordinate; ~x = read downwards from x, the reversed slices of left extensions) */
     void getScoresRef(SeqPair *pairArray, const bsw_ref_t *ref, const int64_t *rpos, uint8_t *seqBufQer, int32_t numPairs, int32_t w)

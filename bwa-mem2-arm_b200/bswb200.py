@@ -31,7 +31,7 @@ EXPORTS = (
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
-    "bsw_arena_begin", "bsw_arena_end", "bsw_ref_upload", "bsw_ref_free", "bsw_getScoresRef",
+    "bsw_arena_begin", "bsw_arena_end", "bsw_arena_defer", "bsw_ref_upload", "bsw_ref_free", "bsw_getScoresRef",
     "bsw_set_direct_min", "kswv_set_direct_min", "bsw_set_wide_max", "bsw_set_wide_policy", "bsw_engine_get_stats", "bsw_engine_reset_stats",
 )
 
@@ -106,6 +106,8 @@ def lib():
     L.bsw_arena_begin.restype = None
     L.bsw_arena_begin.argtypes = [vp, vp, C.c_size_t, vp, C.c_size_t]
     L.bsw_arena_end.argtypes = [vp]
+    L.bsw_arena_defer.restype = None
+    L.bsw_arena_defer.argtypes = [vp, C.c_int]
     L.bsw_ref_upload.restype = vp
     L.bsw_ref_upload.argtypes = [vp, C.c_int64]
     L.bsw_ref_free.argtypes = [vp]
@@ -196,6 +198,10 @@ class BandedPairWiseSW:
 
     def arena_end(self):
         self._L.bsw_arena_end(self._h)
+
+    def arena_defer(self, on=True):
+        """Large calls inside an arena bracket complete at arena_end (see bsw_arena_defer)."""
+        self._L.bsw_arena_defer(self._h, 1 if on else 0)
 
     def getScoresRef(self, pairArray, ref, rpos, seqBufQer, numPairs=None, w=100):
         """Targets from the resident reference `ref` (a Reference object) at doubled-strand positions `rpos` (int64)."""

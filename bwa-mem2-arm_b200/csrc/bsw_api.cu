@@ -217,6 +217,7 @@ struct Core {
     size_t arena_ref_n = 0, arena_qer_n = 0;
     size_t arena_ref_piece = 0, arena_qer_piece = 0;     /* bytes per upload piece */
     bool arena_on = false;
+    bool arena_defer = false;                     /* bsw_arena_defer: large calls of a bracket complete at bsw_arena_end */
 
     DevRt &rt(int i) { return devrt(devs[i]); }
     DevCtx &cx(int i)
@@ -715,8 +716,9 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
         if (trace) { t_a += t2 - t1; t_b += now_ns() - t2; }
     }
     long long t3 = trace ? now_ns() : 0;
-    for (size_t i = 0; i < k.ctx.size(); ++i)
-        if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
+    if (!(k.arena_on && k.arena_defer))            /* deferred: bsw_arena_end (or the next user of a slot) waits for them */
+        for (size_t i = 0; i < k.ctx.size(); ++i)
+            if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
     if (trace)
         fprintf(stderr, "[bsw-b200] direct call: %d pairs, %d chunks, total %.3f ms: stage A (retire slot + enqueue uploads, prep, sort) %.3f, "
                         "stage B (wait histogram + launch DP + enqueue download) %.3f, final drain %.3f\n",
@@ -1032,10 +1034,16 @@ void bsw_arena_end(bsw_t *h)
     Core &k = h->k;
     if (!k.arena_on) return;
     for (size_t i = 0; i < k.ctx.size(); ++i)
-        if (k.ctx[i]) { CK(cudaSetDevice(k.ctx[i]->dev)); CK(cudaStreamSynchronize(k.ctx[i]->arena_stream)); }
+        if (k.ctx[i]) {
+            CK(cudaSetDevice(k.ctx[i]->dev));
+            for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);      /* deferred calls land here */
+            CK(cudaStreamSynchronize(k.ctx[i]->arena_stream));
+        }
     k.arena_on = false;
     k.arena_ref_h = k.arena_qer_h = nullptr; k.arena_ref_n = k.arena_qer_n = 0;
 }
+
+void bsw_arena_defer(bsw_t *h, int on) { h->k.arena_defer = on != 0; }
 
 /* ---- resident reference --------------------------------------------------- */
 bsw_ref_t *bsw_ref_upload(const uint8_t *pac, int64_t l_pac)

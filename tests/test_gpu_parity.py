@@ -716,6 +716,37 @@ def test_arena_upload_once(ora, bsw):
     assert res[True][1] < 0.75 * res[False][1]
 
 
+def test_arena_deferred_completion(ora, bsw):
+    """bsw_arena_defer: inside an arena bracket the tier-8 call may return before its last chunks are home; everything has
+    landed when bsw_arena_end returns.  Small chunks so that several are in flight across the two calls."""
+    import os
+    (L, lr, lq), _ = common.bsw_c1(40000, seed=0x6B)
+    o, _ = _oracle_bsw(ora, L, lr, lq)
+    tiers = ora.classify(L)
+    os.environ["BSW_CUDA_CHUNK_PAIRS"] = "4096"
+    try:
+        h = bsw.BandedPairWiseSW(6, 1, 6, 1, 100, 5, None, 1, 4, 1)
+    finally:
+        os.environ.pop("BSW_CUDA_CHUNK_PAIRS")
+    h.set_direct_min(0)
+    h.arena_defer(True)
+    for rep in range(2):
+        parts = []
+        h.arena_begin(lr, lq)
+        for tier, fn in ((0, h.getScores8), (1, h.getScores16)):
+            sel = np.nonzero(tiers == tier)[0]
+            part = np.ascontiguousarray(L[sel])
+            fn(part, lr, lq, len(part), 1, 100)
+            parts.append((sel, part))
+        h.arena_end()
+        g = L.copy()
+        for sel, part in parts:
+            g[sel] = part
+        _assert_same(o, g)
+    h.arena_defer(False)
+    h.close()
+
+
 def _ref_workload(ora, n, seed, l_pac=200000):
     """Pairs whose targets are slices of a reference: both strands, both read directions."""
     rng = np.random.default_rng(seed)
