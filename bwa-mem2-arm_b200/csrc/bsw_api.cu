@@ -204,6 +204,7 @@ struct Core {
     int count_cells = 0;
     int trace = 0;                   /* BSW_CUDA_TRACE: host-side timing of every direct call on stderr */
     int chunk_pairs = 1 << 19;
+    bool chunk_ramp = true;                       /* direct calls: chunk sizes ramp up / down at the ends (chunk_starts) */
     bool kswv_lanes4 = false;                     /* kswv_sys.cuh: four lanes per group for bins of up to 160 columns */
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
@@ -262,6 +263,7 @@ void core_init(Core &k, int mode)
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.kswv_lanes4 = env_int("BSW_CUDA_KSWV_LANES4", 0) != 0;
+    k.chunk_ramp = env_int("BSW_CUDA_CHUNK_RAMP", 1) != 0;
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.trace = env_int("BSW_CUDA_TRACE", 0);
     k.direct_min = env_int("BSW_CUDA_DIRECT_MIN", 1 << 17);
@@ -578,6 +580,30 @@ void arena_pieces_upto(Core &k, DevCtx &x, int piece)
     }
 }
 
+/* Chunk boundaries of a direct call.  A call cannot start computing before its first chunk is up, sorted and planned, and
+ * cannot return before its last chunk is computed and home: with equal chunks that is ~2 x (one chunk's upload + DP) of
+ * unoverlapped time per call.  So the chunks ramp up from chunk / 8 (at least 16 k pairs) by doubling and ramp down the
+ * same way at the end, each size once per device (BSW_CUDA_CHUNK_RAMP=0: equal chunks).  Used by the kswv calls, whose
+ * kernel is quick on small batches: C4 e2e step 40.5 -> 37.6 ms. */
+std::vector<int> chunk_starts(int n, int chunk, int nd, bool ramp)
+{
+    std::vector<int> st;
+    if (!ramp || n <= chunk) { for (int f = 0; f < n; f += chunk) st.push_back(f); st.push_back(n); return st; }
+    const int lo = std::max(16384, chunk >> 3);
+    std::vector<int> head, tail;
+    long long used = 0;
+    for (int sz = lo; sz < chunk; sz <<= 1)
+        for (int d = 0; d < nd; ++d) { head.push_back(sz); tail.push_back(sz); used += 2ll * sz; }
+    if (used >= n) { for (int f = 0; f < n; f += chunk) st.push_back(f); st.push_back(n); return st; }
+    int f = 0;
+    for (int sz : head) { st.push_back(f); f += sz; }
+    long long tail_sum = used / 2;
+    while (n - f - tail_sum > 0) { st.push_back(f); f += (int)std::min<long long>(chunk, n - f - tail_sum); }
+    for (size_t i = tail.size(); i-- > 0;) { st.push_back(f); f += tail[i]; }
+    st.push_back(n);
+    return st;
+}
+
 /* ---- direct BSW call: chunked, pipelined, sharded ---------------------------------------------
  * The pair array is cut into chunks of BSW_CUDA_CHUNK_PAIRS pairs, dealt round-robin to the handle's
  * devices.  Each chunk uploads its 56-byte records and only the byte ranges of the sequence buffers its pairs
@@ -591,7 +617,10 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
 {
     const int nd = (int)k.devs.size();
     const int chunk = std::max(1024, k.chunk_pairs);
-    const int nchunks = (n + chunk - 1) / chunk;
+    /* equal chunks: a warp of the thread-owns-two-pairs kernel lives 0.4-0.9 ms whatever the chunk holds, so small ramp chunks only
+     * add sorts and tails (measured on c2: 53.1 ms ramped vs 49.6 ms) */
+    const std::vector<int> cstart = chunk_starts(n, chunk, nd, k.chunk_ramp && env_int("BSW_CUDA_CHUNK_RAMP_BSW", 0));
+    const int nchunks = (int)cstart.size() - 1;
     struct Job { int first, cnt, di; long long rlo, qlo; const uint8_t *d_ref, *d_qer; DevCtx *x; Slot *sl; };
     const bool in_arena_r = k.arena_on && !rref && ref >= k.arena_ref_h && ref < k.arena_ref_h + k.arena_ref_n;
     const bool in_arena_q = k.arena_on && qer >= k.arena_qer_h && qer < k.arena_qer_h + k.arena_qer_n;
@@ -668,7 +697,7 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
     auto stage_a = [&](int ci) {
         Job &j = jobs[ci];
-        j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
+        j.first = cstart[ci]; j.cnt = cstart[ci + 1] - cstart[ci];
         j.di = ci % nd;
         j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
         slot_retire(*j.x, *j.sl);              /* its previous chunk must have landed */
@@ -733,7 +762,8 @@ void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const u
 {
     const int nd = (int)k.devs.size();
     const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
-    const int nchunks = (n + chunk - 1) / chunk;
+    const std::vector<int> cstart = chunk_starts(n, chunk, nd, k.chunk_ramp);
+    const int nchunks = (int)cstart.size() - 1;
     struct Job { int first, cnt, di; long long rlo, qlo; DevCtx *x; Slot *sl; bsw_kswr_t *h_res; bool landed; };
     std::vector<Job> jobs(nchunks);
     auto finish = [&](Job &j) {              /* chunk landed: phase 1 applies the refinement rule on the host */
@@ -765,7 +795,7 @@ void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const u
     /* stage A: the slot's previous chunk lands, then uploads + prep + sort + histogram read-back are enqueued */
     auto stage_a = [&](int ci) {
         Job &j = jobs[ci];
-        j.first = ci * chunk; j.cnt = std::min(chunk, n - j.first);
+        j.first = cstart[ci]; j.cnt = cstart[ci + 1] - cstart[ci];
         j.di = ci % nd; j.landed = false;
         j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
         if (ci >= nd * BSW_NSLOT) finish(jobs[ci - nd * BSW_NSLOT]);
