@@ -64,7 +64,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
     const PairIn *in[2] = { &A, &B };
     uint32_t *bl[2] = { blA, blB };
     const int shift = c.b > -c.ambig ? c.b : -c.ambig;       /* |min(mat)| */
-    int qlen[2], tlen[2], pad[2], lim[2], minsc[2], endsc[2], gmax[2], te[2], qk[2], bsc[2], brow[2], bn[2];
+    int qlen[2], tlen[2], pad[2], lim[2], minsc[2], endsc[2], gmax[2], te[2], qk[2], bn[2];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const PairIn &x = *in[p];
@@ -74,7 +74,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
         lim[p] = tlen[p] > 0 ? tlen[p] : 0;                  /* rows the bookkeeping still wants */
         minsc[p] = (x.h0 & KSW_XSUBO_) ? (x.h0 & 0xffff) : 0x10000;
         endsc[p] = (x.h0 & KSW_XSTOP_) ? (x.h0 & 0xffff) : 0x10000;
-        gmax[p] = 0; te[p] = -1; qk[p] = 0; bsc[p] = 0; brow[p] = -2; bn[p] = 0;
+        gmax[p] = 0; te[p] = -1; qk[p] = 0; bn[p] = 0;
     }
 
     /* ---- query selectors of this lane's columns; state = 0 ---- */
@@ -118,6 +118,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
 
     /* bookkeeping state of the last lane, both pairs packed: rows left, best (max << 8 | 255 - column) key and its max, te */
     uint32_t R = pack2(lim[0], lim[1]), GM = 0u, BK = 0u, TE = 0xffffffffu;
+    uint32_t BS = 0u, BR = 0xfffefffeu;                   /* open `b`-list entry: score, row (0xfffe: none yet) */
     const uint32_t ONE2 = 0x00010001u, NEG1 = 0xffffffffu;
     uint32_t NTH, NMS;
     {
@@ -197,18 +198,22 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
                 if (stopb & 0x00008000u) { lim[0] = row + 1; R &= 0xffff0000u; }
                 if (stopb & 0x80000000u) { lim[1] = row + 1; R &= 0x0000ffffu; }
             }
-            const uint32_t qb = ~p_add(IM, NMS) & LM & 0x80008000u;  /* imax >= minsc: ksw_u8's `b` list */
-            if (qb) {
+            /* ksw_u8's `b` list, both pairs at once.  A row with imax >= minsc either extends the open entry (its row is
+             * brow + 1: the entry keeps the larger score and, on a strictly larger one, takes this row) or opens a new one;
+             * the entry it replaces goes to the list (rare: once per run of rows). */
+            const uint32_t ROW2 = (uint32_t)row * ONE2;
+            const uint32_t QM = LM & ~p_perm(p_add(IM, NMS), 0u, 0xBB99u);        /* 0xffff where imax >= minsc */
+            const uint32_t Z = (BR + ONE2) ^ ROW2;                                 /* non-zero half: not adjacent */
+            const uint32_t NEWM = p_minu(Z, ONE2) * 0xffffu & QM;
+            if (NEWM) {
 #pragma unroll
                 for (int p = 0; p < 2; ++p)
-                    if (qb & (p ? 0x80000000u : 0x00008000u)) {
-                        const int imax = half_u(IM, p);
-                        if (brow[p] + 1 != row) {            /* new entry (brow = -2: none yet) */
-                            if (brow[p] >= 0) bl[p][bn[p]++] = ((uint32_t)bsc[p] << 16) | (uint32_t)brow[p];
-                            bsc[p] = imax; brow[p] = row;
-                        } else if (bsc[p] < imax) { bsc[p] = imax; brow[p] = row; }
-                    }
+                    if (half_u(NEWM, p) && half_u(BR, p) != 0xfffeu)
+                        bl[p][bn[p]++] = ((uint32_t)half_u(BS, p) << 16) | (uint32_t)half_u(BR, p);
             }
+            const uint32_t UM = p_minu((p_maxu(BS, IM) ^ BS) | Z, ONE2) * 0xffffu & QM;   /* new entry, or a strictly larger score */
+            BS = (BS & ~UM) | (IM & UM);
+            BR = (BR & ~UM) | (ROW2 & UM);
             R = p_addmax_relu(R, NEG1, 0u);
         }
         ++s;
@@ -228,7 +233,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
             o.qe = qlen[p] > 0 ? (gmax[p] > 0 ? 255 - qk[p] - pad[p] : 0) : -1;
             if (minsc[p] < 0x10000) {
                 const int d = (o.score + c.maxsc - 1) / c.maxsc, low = te[p] - d, high = te[p] + d;
-                if (brow[p] >= 0) bl[p][bn[p]++] = ((uint32_t)bsc[p] << 16) | (uint32_t)brow[p];
+                if (half_u(BR, p) != 0xfffeu) bl[p][bn[p]++] = ((uint32_t)half_u(BS, p) << 16) | (uint32_t)half_u(BR, p);
                 for (int k = 0; k < bn[p]; ++k) {
                     const int e = (int)(bl[p][k] & 0xffffu), sc2 = (int)(bl[p][k] >> 16);
                     if ((e < low || e > high) && sc2 > o.score2) { o.score2 = sc2; o.te2 = e; }
