@@ -485,7 +485,7 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
             cudaStream_t bs = rt.bin_stream[qb];
             if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
             used |= 1u << qb;
-            launch_kswv_sys(qb, sym, pass == 0, k.kswv_lanes4, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
+            launch_kswv_sys(std::min(qb * 16, std::max(1, pl->max_len2_bin[qb])), sym, pass == 0, k.kswv_lanes4, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
                             k.c, is8, phase, (unsigned long long *)x.cells.p, bs);
             CK(cudaGetLastError());
             k.st.kernel_launches++;

@@ -47,6 +47,7 @@ struct Plan {
     int max_len2_general;
     int bad_pairs;                 /* contract violations seen by prep    */
     int oob_pairs;                 /* pairs whose bases fall outside the uploaded byte ranges */
+    int max_len2_bin[BSW_NBINS + 2]; /* kswv: longest query of each bin (N and plain classes together): columns per lane of its launch */
 };
 
 enum { MODE_BSW = 0, MODE_KSWV = 1 };
@@ -78,9 +79,11 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
     __shared__ int s_hist[2 * (BSW_NBINS + 2)];
     __shared__ int s_misc[5];
     __shared__ int s_wide[BSW_WIDE_NCFG];
+    __shared__ int s_ml2[BSW_NBINS + 2];
     if (threadIdx.x < 2 * (BSW_NBINS + 2)) s_hist[threadIdx.x] = 0;
     if (threadIdx.x < 5) s_misc[threadIdx.x] = 0;
     if (threadIdx.x < BSW_WIDE_NCFG) s_wide[threadIdx.x] = 0;
+    if (threadIdx.x < BSW_NBINS + 2) s_ml2[threadIdx.x] = 0;
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -105,6 +108,7 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
             if (qn) key |= 1u << 25;
             atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
             atomicMax(&s_misc[4], len1);
+            if (mode == MODE_KSWV) atomicMax(&s_ml2[qb], len2);
         } else if (mode == MODE_BSW && allow_wide && wide_eligible(c, len1, len2, h0)) {
             /* too long or too high-scoring for the byte-packed rows: the 16-bit lanes-per-pair kernel takes it */
             const int cfg = wide_cfg_for(len2);
@@ -129,6 +133,7 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
     if (threadIdx.x < 2 * (BSW_NBINS + 2) && s_hist[threadIdx.x])      /* hist and hist_n are adjacent in Plan */
         atomicAdd(&plan->hist[threadIdx.x], s_hist[threadIdx.x]);
     if (threadIdx.x < BSW_WIDE_NCFG && s_wide[threadIdx.x]) atomicAdd(&plan->hist_w[threadIdx.x], s_wide[threadIdx.x]);
+    if (threadIdx.x < BSW_NBINS + 2 && s_ml2[threadIdx.x]) atomicMax(&plan->max_len2_bin[threadIdx.x], s_ml2[threadIdx.x]);
     if (threadIdx.x == 0) {
         if (s_misc[0]) atomicAdd(&plan->n_general, s_misc[0]);
         atomicMax(&plan->max_len1, s_misc[1]);
@@ -428,11 +433,12 @@ kswv_sys_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__res
     if (lane == 0 && my_cells) atomicAdd(cells, my_cells);
 }
 
-/* columns per lane the launch of bin qb (queries of up to qb * 16 bases) uses with G lanes per group.  The common variant
- * (symmetric gap sums, no N in the query) has one instantiation per bin; the three others share four shapes. */
-static inline int kswv_sys_cols(int qb, int G, bool sym, bool qn)
+/* Columns per lane of a launch with 8 lanes per group that holds queries of up to max_len2 bases.  The common variant
+ * (symmetric gap sums, no N in the query) has one instantiation per column count 1..32; the three others share four shapes. */
+static inline int kswv_sys_cols(int max_len2, bool sym, bool qn)
 {
-    const int c = 16 * qb / G;
+    int c = (max_len2 + 7) >> 3;
+    c = c < 1 ? 1 : c > 32 ? 32 : c;
     return (sym && !qn) ? c : (c + 7) & ~7;
 }
 
@@ -448,22 +454,24 @@ static inline void launch_kswv_sys_shape(int first, int count, int max_rows, Pai
     kswv_sys_kernel<G, C, SYM, QN><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells);
 }
 
-/* lanes4: four lanes per group for the bins of up to 160 columns (twice the cells per step and lane: the per-step
- * shuffles and bookkeeping weigh half as much; 40 columns per lane is what the register file takes) */
-static inline void launch_kswv_sys(int qb, bool sym, bool qn, bool lanes4, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
+/* one launch over the sorted slots [first, first + count), all of whose queries have at most max_len2 bases.
+ * lanes4 (experiment, BSW_CUDA_KSWV_LANES4): four lanes per group for up to 160 columns -- twice the cells per step and
+ * lane, but 197 registers: measured slower (3184 vs 3409 GCUPS on config 4). */
+static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, bool lanes4, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
                                    const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
                                    unsigned long long *cells, cudaStream_t s)
 {
 #define KSWV_SYS_LAUNCH(G, CC, SYM, QN) \
     launch_kswv_sys_shape<G, CC, SYM, QN>(first, count, max_rows, io, ref, qer, aln, sorted, c, is8, phase, cells, s)
 #define KSWV_SYS_COARSE(SYM, QN) \
-    switch (kswv_sys_cols(qb, 8, SYM, QN)) { \
+    switch (kswv_sys_cols(max_len2, SYM, QN)) { \
     case 8: KSWV_SYS_LAUNCH(8, 8, SYM, QN); break; case 16: KSWV_SYS_LAUNCH(8, 16, SYM, QN); break; \
     case 24: KSWV_SYS_LAUNCH(8, 24, SYM, QN); break; default: KSWV_SYS_LAUNCH(8, 32, SYM, QN); break; }
+#define KSWV_SYS_CASE(CC) case CC: KSWV_SYS_LAUNCH(8, CC, true, false); break;
     if (sym && !qn) {
-        if (lanes4 && qb <= 10) {
-            switch (qb) {
-            case 1: KSWV_SYS_LAUNCH(4, 4, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, 8, true, false); break;
+        if (lanes4 && max_len2 <= 160) {
+            switch ((max_len2 + 15) >> 4) {
+            case 0: case 1: KSWV_SYS_LAUNCH(4, 4, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, 8, true, false); break;
             case 3: KSWV_SYS_LAUNCH(4, 12, true, false); break;  case 4: KSWV_SYS_LAUNCH(4, 16, true, false); break;
             case 5: KSWV_SYS_LAUNCH(4, 20, true, false); break;  case 6: KSWV_SYS_LAUNCH(4, 24, true, false); break;
             case 7: KSWV_SYS_LAUNCH(4, 28, true, false); break;  case 8: KSWV_SYS_LAUNCH(4, 32, true, false); break;
@@ -471,19 +479,17 @@ static inline void launch_kswv_sys(int qb, bool sym, bool qn, bool lanes4, int f
             }
             return;
         }
-        switch (qb) {
-        case 1: KSWV_SYS_LAUNCH(8, 2, true, false); break;   case 2: KSWV_SYS_LAUNCH(8, 4, true, false); break;
-        case 3: KSWV_SYS_LAUNCH(8, 6, true, false); break;   case 4: KSWV_SYS_LAUNCH(8, 8, true, false); break;
-        case 5: KSWV_SYS_LAUNCH(8, 10, true, false); break;  case 6: KSWV_SYS_LAUNCH(8, 12, true, false); break;
-        case 7: KSWV_SYS_LAUNCH(8, 14, true, false); break;  case 8: KSWV_SYS_LAUNCH(8, 16, true, false); break;
-        case 9: KSWV_SYS_LAUNCH(8, 18, true, false); break;  case 10: KSWV_SYS_LAUNCH(8, 20, true, false); break;
-        case 11: KSWV_SYS_LAUNCH(8, 22, true, false); break; case 12: KSWV_SYS_LAUNCH(8, 24, true, false); break;
-        case 13: KSWV_SYS_LAUNCH(8, 26, true, false); break; case 14: KSWV_SYS_LAUNCH(8, 28, true, false); break;
-        case 15: KSWV_SYS_LAUNCH(8, 30, true, false); break; default: KSWV_SYS_LAUNCH(8, 32, true, false); break;
+        switch (kswv_sys_cols(max_len2, true, false)) {
+        KSWV_SYS_CASE(1) KSWV_SYS_CASE(2) KSWV_SYS_CASE(3) KSWV_SYS_CASE(4) KSWV_SYS_CASE(5) KSWV_SYS_CASE(6) KSWV_SYS_CASE(7) KSWV_SYS_CASE(8)
+        KSWV_SYS_CASE(9) KSWV_SYS_CASE(10) KSWV_SYS_CASE(11) KSWV_SYS_CASE(12) KSWV_SYS_CASE(13) KSWV_SYS_CASE(14) KSWV_SYS_CASE(15) KSWV_SYS_CASE(16)
+        KSWV_SYS_CASE(17) KSWV_SYS_CASE(18) KSWV_SYS_CASE(19) KSWV_SYS_CASE(20) KSWV_SYS_CASE(21) KSWV_SYS_CASE(22) KSWV_SYS_CASE(23) KSWV_SYS_CASE(24)
+        KSWV_SYS_CASE(25) KSWV_SYS_CASE(26) KSWV_SYS_CASE(27) KSWV_SYS_CASE(28) KSWV_SYS_CASE(29) KSWV_SYS_CASE(30) KSWV_SYS_CASE(31)
+        default: KSWV_SYS_LAUNCH(8, 32, true, false); break;
         }
     } else if (sym) { KSWV_SYS_COARSE(true, true) }
     else if (qn) { KSWV_SYS_COARSE(false, true) }
     else { KSWV_SYS_COARSE(false, false) }
+#undef KSWV_SYS_CASE
 #undef KSWV_SYS_COARSE
 #undef KSWV_SYS_LAUNCH
 }

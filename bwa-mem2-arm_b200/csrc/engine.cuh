@@ -461,7 +461,7 @@ inline void Engine::submit(StagedSlot &s)
             for (int pass = 0; pass < 2; ++pass) {
                 const BinTable &t = tb[pass];
                 for (int b = 0; b < t.nbins; ++b) {
-                    launch_kswv_sys(t.ne[b] / 16, sym, pass == 0, false, t.first_pair[b], t.first_pair[b + 1] - t.first_pair[b],
+                    launch_kswv_sys(t.ne[b], sym, pass == 0, false, t.first_pair[b], t.first_pair[b + 1] - t.first_pair[b],
                                     std::max(1, s.max_len1_packed), io, seq, seq, d_aln, s.d_sorted, key.c, key.is8, 0, d_cells, q);
                     ++launches;
                 }
