@@ -205,7 +205,7 @@ struct Core {
     int trace = 0;                   /* BSW_CUDA_TRACE: host-side timing of every direct call on stderr */
     int chunk_pairs = 1 << 19;
     bool chunk_ramp = true;                       /* direct calls: chunk sizes ramp up / down at the ends (chunk_starts) */
-    bool kswv_lanes4 = false;                     /* kswv_sys.cuh: four lanes per group for bins of up to 160 columns */
+    int kswv_lanes = 0;                           /* kswv_sys.cuh: lanes per group (8 / 16 / 32); 0 = by batch size */
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
     long long direct_bytes = 8ll << 20;  /* ... unless they carry at least this many bases (call_is_heavy) */
@@ -262,7 +262,7 @@ void core_init(Core &k, int mode)
     for (size_t i = 0; i < k.devs.size(); ++i) (void)devrt(k.devs[i]);       /* first handle on a device builds its runtime */
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
-    k.kswv_lanes4 = env_int("BSW_CUDA_KSWV_LANES4", 0) != 0;
+    k.kswv_lanes = env_int("BSW_CUDA_KSWV_LANES", 0);
     k.chunk_ramp = env_int("BSW_CUDA_CHUNK_RAMP", 1) != 0;
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.trace = env_int("BSW_CUDA_TRACE", 0);
@@ -476,26 +476,44 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
     if (k.timing) CK(cudaEventRecord(x.ev0, s));
     int n_packed = 0;
     const bool sym = k.c.oe_del == k.c.oe_ins;
-    unsigned used = 0;
-    CK(cudaEventRecord(x.fork_ev, s));
-    for (int pass = 0; pass < 2; ++pass)
-        for (int qb = BSW_NBINS; qb >= 1; --qb) {
-            const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
-            if (cnt <= 0) continue;
-            cudaStream_t bs = rt.bin_stream[qb];
-            if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
-            used |= 1u << qb;
-            launch_kswv_sys(std::min(qb * 16, std::max(1, pl->max_len2_bin[qb])), sym, pass == 0, k.kswv_lanes4, n_packed, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
-                            k.c, is8, phase, (unsigned long long *)x.cells.p, bs);
+    int lanes = k.kswv_lanes ? k.kswv_lanes : kswv_sys_lanes_for(n);
+    if (!sym) lanes = 8;
+    if (lanes > 8) {
+        /* a small call: ONE launch over all packed pairs on the shape with more lanes per group (see engine.cuh) */
+        int any_n = 0, ml2 = 1;
+        for (int qb = 1; qb <= BSW_NBINS; ++qb) {
+            n_packed += pl->hist_n[qb] + pl->hist[qb]; any_n += pl->hist_n[qb];
+            if (pl->hist_n[qb] + pl->hist[qb] > 0) ml2 = std::max(ml2, std::min(qb * 16, std::max(1, pl->max_len2_bin[qb])));
+        }
+        if (n_packed > 0) {
+            launch_kswv_sys(ml2, sym, any_n > 0, lanes, 0, n_packed, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
+                            k.c, is8, phase, (unsigned long long *)x.cells.p, s);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
-            n_packed += cnt;
         }
-    for (int qb = BSW_NBINS; qb >= 1; --qb)
-        if (used & (1u << qb)) {
-            CK(cudaEventRecord(x.bin_ev[qb], rt.bin_stream[qb]));
-            CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
-        }
+    } else {
+        unsigned used = 0;
+        CK(cudaEventRecord(x.fork_ev, s));
+        for (int pass = 0; pass < 2; ++pass)
+            for (int qb = BSW_NBINS; qb >= 1; --qb) {
+                const int cnt = pass == 0 ? pl->hist_n[qb] : pl->hist[qb];
+                if (cnt <= 0) continue;
+                cudaStream_t bs = rt.bin_stream[qb];
+                if (!(used & (1u << qb))) CK(cudaStreamWaitEvent(bs, x.fork_ev, 0));
+                used |= 1u << qb;
+                launch_kswv_sys(std::min(qb * 16, std::max(1, pl->max_len2_bin[qb])), sym, pass == 0, 8, n_packed, cnt,
+                                std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted,
+                                k.c, is8, phase, (unsigned long long *)x.cells.p, bs);
+                CK(cudaGetLastError());
+                k.st.kernel_launches++;
+                n_packed += cnt;
+            }
+        for (int qb = BSW_NBINS; qb >= 1; --qb)
+            if (used & (1u << qb)) {
+                CK(cudaEventRecord(x.bin_ev[qb], rt.bin_stream[qb]));
+                CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
+            }
+    }
     if (pl->n_general > 0) {
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
         int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));

@@ -455,9 +455,17 @@ static inline void launch_kswv_sys_shape(int first, int count, int max_rows, Pai
 }
 
 /* one launch over the sorted slots [first, first + count), all of whose queries have at most max_len2 bases.
- * lanes4 (experiment, BSW_CUDA_KSWV_LANES4): four lanes per group for up to 160 columns -- twice the cells per step and
- * lane, but 197 registers: measured slower (3184 vs 3409 GCUPS on config 4). */
-static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, bool lanes4, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
+ * lanes = lanes per group: 8 is the throughput shape; 16 and 32 put the same columns on more lanes (a row step is half /
+ * a quarter as long, 2 / 4 times the warps per pair) for batches too small to fill the device anyway -- the staged
+ * small-call route picks them by batch size (kswv_sys_lanes_for) and runs the whole batch -- all query lengths, with and
+ * without N -- in ONE such launch (qn: the general score table for everybody).  Symmetric gap sums only. */
+static inline int kswv_sys_lanes_for(int pairs)
+{
+    /* the device holds ~2400 warps of this kernel: more lanes per group while the batch stays within one wave */
+    return pairs <= 4096 ? 32 : pairs <= 8192 ? 16 : 8;
+}
+
+static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, int lanes, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
                                    const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
                                    unsigned long long *cells, cudaStream_t s)
 {
@@ -467,29 +475,41 @@ static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, bool lanes4,
     switch (kswv_sys_cols(max_len2, SYM, QN)) { \
     case 8: KSWV_SYS_LAUNCH(8, 8, SYM, QN); break; case 16: KSWV_SYS_LAUNCH(8, 16, SYM, QN); break; \
     case 24: KSWV_SYS_LAUNCH(8, 24, SYM, QN); break; default: KSWV_SYS_LAUNCH(8, 32, SYM, QN); break; }
-#define KSWV_SYS_CASE(CC) case CC: KSWV_SYS_LAUNCH(8, CC, true, false); break;
-    if (sym && !qn) {
-        if (lanes4 && max_len2 <= 160) {
-            switch ((max_len2 + 15) >> 4) {
-            case 0: case 1: KSWV_SYS_LAUNCH(4, 4, true, false); break;   case 2: KSWV_SYS_LAUNCH(4, 8, true, false); break;
-            case 3: KSWV_SYS_LAUNCH(4, 12, true, false); break;  case 4: KSWV_SYS_LAUNCH(4, 16, true, false); break;
-            case 5: KSWV_SYS_LAUNCH(4, 20, true, false); break;  case 6: KSWV_SYS_LAUNCH(4, 24, true, false); break;
-            case 7: KSWV_SYS_LAUNCH(4, 28, true, false); break;  case 8: KSWV_SYS_LAUNCH(4, 32, true, false); break;
-            case 9: KSWV_SYS_LAUNCH(4, 36, true, false); break;  default: KSWV_SYS_LAUNCH(4, 40, true, false); break;
-            }
-            return;
+#define KSWV_SYS_CASE(G, CC) case CC: KSWV_SYS_LAUNCH(G, CC, true, false); break;
+#define KSWV_SYS_CASEQ(G, CC) case CC: KSWV_SYS_LAUNCH(G, CC, true, true); break;
+    if (sym && lanes >= 32) {
+        if (qn) switch ((std::max(max_len2, 1) + 31) >> 5) {
+            KSWV_SYS_CASEQ(32, 1) KSWV_SYS_CASEQ(32, 2) KSWV_SYS_CASEQ(32, 3) KSWV_SYS_CASEQ(32, 4) KSWV_SYS_CASEQ(32, 5) KSWV_SYS_CASEQ(32, 6) KSWV_SYS_CASEQ(32, 7)
+            default: KSWV_SYS_LAUNCH(32, 8, true, true); break;
+        } else switch ((std::max(max_len2, 1) + 31) >> 5) {
+            KSWV_SYS_CASE(32, 1) KSWV_SYS_CASE(32, 2) KSWV_SYS_CASE(32, 3) KSWV_SYS_CASE(32, 4) KSWV_SYS_CASE(32, 5) KSWV_SYS_CASE(32, 6) KSWV_SYS_CASE(32, 7)
+            default: KSWV_SYS_LAUNCH(32, 8, true, false); break;
         }
+        return;
+    }
+    if (sym && lanes >= 16) {
+        if (qn) switch (((std::max(max_len2, 1) + 31) >> 5) * 2) {       /* even column counts: 32-column steps */
+            KSWV_SYS_CASEQ(16, 2) KSWV_SYS_CASEQ(16, 4) KSWV_SYS_CASEQ(16, 6) KSWV_SYS_CASEQ(16, 8) KSWV_SYS_CASEQ(16, 10) KSWV_SYS_CASEQ(16, 12) KSWV_SYS_CASEQ(16, 14)
+            default: KSWV_SYS_LAUNCH(16, 16, true, true); break;
+        } else switch (((std::max(max_len2, 1) + 31) >> 5) * 2) {
+            KSWV_SYS_CASE(16, 2) KSWV_SYS_CASE(16, 4) KSWV_SYS_CASE(16, 6) KSWV_SYS_CASE(16, 8) KSWV_SYS_CASE(16, 10) KSWV_SYS_CASE(16, 12) KSWV_SYS_CASE(16, 14)
+            default: KSWV_SYS_LAUNCH(16, 16, true, false); break;
+        }
+        return;
+    }
+    if (sym && !qn) {
         switch (kswv_sys_cols(max_len2, true, false)) {
-        KSWV_SYS_CASE(1) KSWV_SYS_CASE(2) KSWV_SYS_CASE(3) KSWV_SYS_CASE(4) KSWV_SYS_CASE(5) KSWV_SYS_CASE(6) KSWV_SYS_CASE(7) KSWV_SYS_CASE(8)
-        KSWV_SYS_CASE(9) KSWV_SYS_CASE(10) KSWV_SYS_CASE(11) KSWV_SYS_CASE(12) KSWV_SYS_CASE(13) KSWV_SYS_CASE(14) KSWV_SYS_CASE(15) KSWV_SYS_CASE(16)
-        KSWV_SYS_CASE(17) KSWV_SYS_CASE(18) KSWV_SYS_CASE(19) KSWV_SYS_CASE(20) KSWV_SYS_CASE(21) KSWV_SYS_CASE(22) KSWV_SYS_CASE(23) KSWV_SYS_CASE(24)
-        KSWV_SYS_CASE(25) KSWV_SYS_CASE(26) KSWV_SYS_CASE(27) KSWV_SYS_CASE(28) KSWV_SYS_CASE(29) KSWV_SYS_CASE(30) KSWV_SYS_CASE(31)
+        KSWV_SYS_CASE(8, 1) KSWV_SYS_CASE(8, 2) KSWV_SYS_CASE(8, 3) KSWV_SYS_CASE(8, 4) KSWV_SYS_CASE(8, 5) KSWV_SYS_CASE(8, 6) KSWV_SYS_CASE(8, 7) KSWV_SYS_CASE(8, 8)
+        KSWV_SYS_CASE(8, 9) KSWV_SYS_CASE(8, 10) KSWV_SYS_CASE(8, 11) KSWV_SYS_CASE(8, 12) KSWV_SYS_CASE(8, 13) KSWV_SYS_CASE(8, 14) KSWV_SYS_CASE(8, 15) KSWV_SYS_CASE(8, 16)
+        KSWV_SYS_CASE(8, 17) KSWV_SYS_CASE(8, 18) KSWV_SYS_CASE(8, 19) KSWV_SYS_CASE(8, 20) KSWV_SYS_CASE(8, 21) KSWV_SYS_CASE(8, 22) KSWV_SYS_CASE(8, 23) KSWV_SYS_CASE(8, 24)
+        KSWV_SYS_CASE(8, 25) KSWV_SYS_CASE(8, 26) KSWV_SYS_CASE(8, 27) KSWV_SYS_CASE(8, 28) KSWV_SYS_CASE(8, 29) KSWV_SYS_CASE(8, 30) KSWV_SYS_CASE(8, 31)
         default: KSWV_SYS_LAUNCH(8, 32, true, false); break;
         }
     } else if (sym) { KSWV_SYS_COARSE(true, true) }
     else if (qn) { KSWV_SYS_COARSE(false, true) }
     else { KSWV_SYS_COARSE(false, false) }
 #undef KSWV_SYS_CASE
+#undef KSWV_SYS_CASEQ
 #undef KSWV_SYS_COARSE
 #undef KSWV_SYS_LAUNCH
 }

@@ -456,16 +456,25 @@ inline void Engine::submit(StagedSlot &s)
     } else {
         bsw_kswr_t *d_aln = (bsw_kswr_t *)s.d_res;
         if (n_packed > 0) {
-            /* one registers-and-shuffles launch per non-empty bin (kswv_sys.cuh): queries with an N first, longest bin first */
+            /* kswv_sys.cuh.  A small batch (more lanes per group, symmetric gap sums) is ONE launch over all its packed
+             * pairs -- every query length, with or without N (then the general score table for everybody): two or three
+             * bin launches one after another would add their latencies.  Otherwise one launch per non-empty bin: queries
+             * with an N first, longest bin first. */
             const bool sym = key.c.oe_del == key.c.oe_ins;
-            for (int pass = 0; pass < 2; ++pass) {
-                const BinTable &t = tb[pass];
-                for (int b = 0; b < t.nbins; ++b) {
-                    launch_kswv_sys(t.ne[b], sym, pass == 0, false, t.first_pair[b], t.first_pair[b + 1] - t.first_pair[b],
-                                    std::max(1, s.max_len1_packed), io, seq, seq, d_aln, s.d_sorted, key.c, key.is8, 0, d_cells, q);
-                    ++launches;
+            const int lanes = sym ? kswv_sys_lanes_for(n_packed) : 8;
+            if (lanes > 8) {
+                launch_kswv_sys(std::max(maxne[0], maxne[1]), sym, tb[0].nbins > 0, lanes, 0, n_packed, std::max(1, s.max_len1_packed), io, seq, seq,
+                                d_aln, s.d_sorted, key.c, key.is8, 0, d_cells, q);
+                ++launches;
+            } else
+                for (int pass = 0; pass < 2; ++pass) {
+                    const BinTable &t = tb[pass];
+                    for (int b = 0; b < t.nbins; ++b) {
+                        launch_kswv_sys(t.ne[b], sym, pass == 0, 8, t.first_pair[b], t.first_pair[b + 1] - t.first_pair[b],
+                                        std::max(1, s.max_len1_packed), io, seq, seq, d_aln, s.d_sorted, key.c, key.is8, 0, d_cells, q);
+                        ++launches;
+                    }
                 }
-            }
         }
         if (n_general > 0) {
             const size_t he_b = (size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2);

@@ -199,10 +199,11 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         // the library's routing: the registers-and-shuffles kernel (kswv_sys.cuh) for every pair it admits, the general kernel
         // for the rest (force_general = 1: the general kernel for all).  Bits 8..15:
         // minimum columns per lane (a larger shape than the query needs: more pad columns, same results); bit 16: run
-        // every group through the QN variant.  Pairs are taken in input order, two per group, like the sorted order
+        // every group through the QN variant; bits 17..18: lanes per group.  Pairs are taken in input order, two per group, like the sorted order
         // of the library only that neighbouring lengths differ more.
         const int min_c = (force_general >> 8) & 0xff;
         const bool all_qn = (force_general >> 16) & 1;
+        const int lanes = 8 << ((force_general >> 17) & 3);      // bits 17..18: 8 / 16 / 32 lanes per group (the small-batch shapes)
         std::vector<int> by[2][17];
         for (int i = 0; i < n; ++i) {
             if (!kswv_sys_eligible(c, pairs[i].len1, pairs[i].len2)) { ge.push_back(i); continue; }
@@ -216,9 +217,23 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         for (int qn = 0; qn < 2; ++qn)
             for (int qb = 1; qb <= 16; ++qb) {
                 const std::vector<int> &v = by[qn][qb];
-                for (size_t f = 0; f < v.size(); f += 8) {
-                    const int cnt = (int)std::min<size_t>(8, v.size() - f);
+                const int per = 2 * (32 / lanes);
+                for (size_t f = 0; f < v.size(); f += per) {
+                    const int cnt = (int)std::min<size_t>(per, v.size() - f);
                     KswOut res[8];
+                    if (lanes == 32) {
+                        switch ((qb + 1) / 2) {      // 32-column steps
+#define SYS_CASE(CC) case CC: sys_warp_v<32, CC>(c, is8, qn != 0, pairs, v.data() + f, cnt, ref, qer, res); break;
+                        SYS_CASE(1) SYS_CASE(2) SYS_CASE(3) SYS_CASE(4) SYS_CASE(5) SYS_CASE(6) SYS_CASE(7) SYS_CASE(8)
+#undef SYS_CASE
+                        }
+                    } else if (lanes == 16) {
+                        switch ((qb + 1) / 2) {
+#define SYS_CASE(CC) case CC: sys_warp_v<16, 2 * CC>(c, is8, qn != 0, pairs, v.data() + f, cnt, ref, qer, res); break;
+                        SYS_CASE(1) SYS_CASE(2) SYS_CASE(3) SYS_CASE(4) SYS_CASE(5) SYS_CASE(6) SYS_CASE(7) SYS_CASE(8)
+#undef SYS_CASE
+                        }
+                    } else
                     switch (qb) {
 #define SYS_CASE(QB) case QB: sys_warp_v<8, 2 * QB>(c, is8, qn != 0, pairs, v.data() + f, cnt, ref, qer, res); break;
                     SYS_CASE(1) SYS_CASE(2) SYS_CASE(3) SYS_CASE(4) SYS_CASE(5) SYS_CASE(6) SYS_CASE(7) SYS_CASE(8)

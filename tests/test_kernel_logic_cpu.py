@@ -97,6 +97,8 @@ def test_kswv_sys_kernel(ora):
     assert _check_kswv_sys(ora, P, r, q, 1) == len(P)
     _check_kswv_sys(ora, P, r, q, 1, mode=1 << 16)          # every group through the general score table (QN)
     _check_kswv_sys(ora, P, r, q, 1, mode=26 << 8)          # a larger shape than needed: more pad columns
+    _check_kswv_sys(ora, P, r, q, 1, mode=1 << 17)          # 16 lanes per group (small-batch shape)
+    _check_kswv_sys(ora, P, r, q, 1, mode=2 << 17)          # 32 lanes per group
     P, r, q = ora.gen_kswv(100, qlen=250, tmin=400, tmax=700, seed=5)
     _check_kswv_sys(ora, P, r, q, 0)
     # ragged lengths (neighbouring pairs of one group differ), empty sequences, N in queries and targets, early stops
@@ -107,6 +109,8 @@ def test_kswv_sys_kernel(ora):
     P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | 9
     _check_kswv_sys(ora, P, r, q, 0)
     _check_kswv_sys(ora, P, r, q, 1)
+    _check_kswv_sys(ora, P, r, q, 0, mode=2 << 17)
+    _check_kswv_sys(ora, P, r, q, 1, mode=1 << 17)
     # 8-bit overflow rule, tandem repeats (second-best list), scoring variants (asymmetric gap sums: the non-SYM variants)
     P, r, q = ora.gen_kswv(80, qlen=255, tmin=300, tmax=400, seed=9, div=0.0,
                            xtra=ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 19)
