@@ -502,8 +502,8 @@ def run_bsw(args):
         if wl == "c2":
             sw.reset_stats(); ms = time_host(c, args, lambda: step_e2e(True, True)); s2 = sw.stats()
             variants["arena_deferred"] = {"ms_per_step": ms / args.steps, "h2d_bytes_per_step": s2["h2d_bytes"] // (args.steps + 2),
-                                          "api": "arenas declared + bsw_arena_defer: a tier call may return before its last chunks are home, "
-                                                 "bsw_arena_end completes the bracket (measured: no gain, the step is bound by PCIe bytes)"}
+                                          "api": "arenas declared + bsw_arena_defer: the large tier calls of a side are recorded and run as ONE "
+                                                 "interleaved chunk pipeline at bsw_arena_end (upstream reads no result between the tier calls)"}
             sw.reset_stats(); ms = time_host(c, args, lambda: step_e2e(False)); s2 = sw.stats()
             variants["strict"] = {"ms_per_step": ms / args.steps, "h2d_bytes_per_step": s2["h2d_bytes"] // (args.steps + 2),
                                   "api": "bsw_getScores8/16 only: each tier call uploads the byte range of the shared arenas it touches"}

@@ -195,6 +195,9 @@ void ctx_release(DevRt &rt, DevCtx *x)
     rt.free_ctx.push_back(x);
 }
 
+/* one host-pointer BSW call on the direct route (direct_call_bsw_multi) */
+struct DirectSeg { bsw_seqpair_t *pairs; const uint8_t *ref, *qer; int n, w, tier8_check; };
+
 struct Core {
     Const c;
     std::vector<int> devs;
@@ -219,6 +222,7 @@ struct Core {
     size_t arena_ref_piece = 0, arena_qer_piece = 0;     /* bytes per upload piece */
     bool arena_on = false;
     bool arena_defer = false;                     /* bsw_arena_defer: large calls of a bracket complete at bsw_arena_end */
+    std::vector<DirectSeg> pending;               /* ... and these are the ones waiting for it */
 
     DevRt &rt(int i) { return devrt(devs[i]); }
     DevCtx &cx(int i)
@@ -630,19 +634,41 @@ std::vector<int> chunk_starts(int n, int chunk, int nd, bool ramp)
  * chunk c-1 overlap the kernels of chunk c.  Results land directly in the caller's SeqPair array (whole-record
  * DMA: a 24-of-56-byte strided copy reaches 1.5 GB/s up and 15 GB/s down against 55 GB/s for the contiguous
  * records, profiles/r02_pcie_probe_1gpu.json).  Synchronous on return. */
-void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check,
-                     const bsw_ref *rref = nullptr, const int64_t *rpos = nullptr)
+/* One or more direct calls in ONE chunk pipeline.  Several segments = the deferred calls of an arena bracket
+ * (bsw_arena_defer): their chunks are interleaved in proportion, so that a call that mostly waits for PCIe (the first
+ * tier call of a side: it brings the arenas up) and one that mostly waits for the GPU (the second: only records go up)
+ * fill each other's gaps. */
+void direct_call_bsw_multi(Core &k, const std::vector<DirectSeg> &segs, const bsw_ref *rref = nullptr, const int64_t *rpos = nullptr)
 {
     const int nd = (int)k.devs.size();
     const int chunk = std::max(1024, k.chunk_pairs);
     /* equal chunks: a warp of the thread-owns-two-pairs kernel lives 0.4-0.9 ms whatever the chunk holds, so small ramp chunks only
      * add sorts and tails (measured on c2: 53.1 ms ramped vs 49.6 ms) */
-    const std::vector<int> cstart = chunk_starts(n, chunk, nd, k.chunk_ramp && env_int("BSW_CUDA_CHUNK_RAMP_BSW", 0));
-    const int nchunks = (int)cstart.size() - 1;
-    struct Job { int first, cnt, di; long long rlo, qlo; const uint8_t *d_ref, *d_qer; DevCtx *x; Slot *sl; };
-    const bool in_arena_r = k.arena_on && !rref && ref >= k.arena_ref_h && ref < k.arena_ref_h + k.arena_ref_n;
-    const bool in_arena_q = k.arena_on && qer >= k.arena_qer_h && qer < k.arena_qer_h + k.arena_qer_n;
+    struct Job { int seg, first, cnt, di; long long rlo, qlo; const uint8_t *d_ref, *d_qer; DevCtx *x; Slot *sl; };
+    std::vector<Job> jobs;
+    {
+        /* chunks of every segment, merged by their relative position inside their segment */
+        std::vector<std::pair<double, Job>> all;
+        for (size_t sg = 0; sg < segs.size(); ++sg) {
+            const std::vector<int> cs = chunk_starts(segs[sg].n, chunk, nd, k.chunk_ramp && env_int("BSW_CUDA_CHUNK_RAMP_BSW", 0));
+            const int nc = (int)cs.size() - 1;
+            for (int ci = 0; ci < nc; ++ci) {
+                Job j{}; j.seg = (int)sg; j.first = cs[ci]; j.cnt = cs[ci + 1] - cs[ci];
+                all.push_back({ (ci + 0.5) / nc, j });
+            }
+        }
+        std::stable_sort(all.begin(), all.end(), [](const std::pair<double, Job> &a, const std::pair<double, Job> &b) { return a.first < b.first; });
+        for (auto &e : all) jobs.push_back(e.second);
+    }
+    const int nchunks = (int)jobs.size();
+    long long n = 0;
+    for (const DirectSeg &sg : segs) n += sg.n;
     auto upload = [&](Job &j, bool exact) {
+        bsw_seqpair_t *pairs = segs[j.seg].pairs;
+        const uint8_t *ref = segs[j.seg].ref, *qer = segs[j.seg].qer;
+        const int tier8_check = segs[j.seg].tier8_check;
+        const bool in_arena_r = k.arena_on && !rref && ref >= k.arena_ref_h && ref < k.arena_ref_h + k.arena_ref_n;
+        const bool in_arena_q = k.arena_on && qer >= k.arena_qer_h && qer < k.arena_qer_h + k.arena_qer_n;
         long long rlo, rhi, qlo, qhi, l1s = 0;
         if (exact) { extents(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi); for (int i = j.first; i < j.first + j.cnt; ++i) l1s += std::max(pairs[i].len1, 0) + 4; }
         else extents_sampled(pairs, j.first, j.cnt, rlo, rhi, qlo, qhi, &l1s);
@@ -711,11 +737,10 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
         }
         plan_enqueue(k, sl, d_pairs, j.d_qer, j.cnt, sl.stream, tier8_check, rlo, rhi, qlo, qhi, !rref);
     };
-    std::vector<Job> jobs(nchunks);
     /* stage A: extents, uploads, prep + sort + histogram read-back -- all asynchronous */
     auto stage_a = [&](int ci) {
         Job &j = jobs[ci];
-        j.first = cstart[ci]; j.cnt = cstart[ci + 1] - cstart[ci];
+        bsw_seqpair_t *pairs = segs[j.seg].pairs;
         j.di = ci % nd;
         j.x = &k.cx(j.di); j.sl = &j.x->slot[(ci / nd) % BSW_NSLOT];
         slot_retire(*j.x, *j.sl);              /* its previous chunk must have landed */
@@ -731,6 +756,8 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
     auto stage_b = [&](int ci) {
         Job &j = jobs[ci];
         Slot &sl = *j.sl;
+        bsw_seqpair_t *pairs = segs[j.seg].pairs;
+        const int w = segs[j.seg].w;
         CK(cudaSetDevice(j.x->dev));
         const Plan *pl = plan_wait(sl, sl.stream);
         if (pl->oob_pairs) {                      /* the sampled ranges missed a pair: redo with the exact scan */
@@ -763,13 +790,18 @@ void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const ui
         if (trace) { t_a += t2 - t1; t_b += now_ns() - t2; }
     }
     long long t3 = trace ? now_ns() : 0;
-    if (!(k.arena_on && k.arena_defer))            /* deferred: bsw_arena_end (or the next user of a slot) waits for them */
-        for (size_t i = 0; i < k.ctx.size(); ++i)
-            if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
+    for (size_t i = 0; i < k.ctx.size(); ++i)
+        if (k.ctx[i]) for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);
     if (trace)
         fprintf(stderr, "[bsw-b200] direct call: %d pairs, %d chunks, total %.3f ms: stage A (retire slot + enqueue uploads, prep, sort) %.3f, "
                         "stage B (wait histogram + launch DP + enqueue download) %.3f, final drain %.3f\n",
-                n, nchunks, (now_ns() - t0) * 1e-6, t_a * 1e-6, t_b * 1e-6, (now_ns() - t3) * 1e-6);
+                (int)n, nchunks, (now_ns() - t0) * 1e-6, t_a * 1e-6, t_b * 1e-6, (now_ns() - t3) * 1e-6);
+}
+
+void direct_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, int n, int w, int tier8_check,
+                     const bsw_ref *rref = nullptr, const int64_t *rpos = nullptr)
+{
+    direct_call_bsw_multi(k, std::vector<DirectSeg>{ DirectSeg{ pairs, ref, qer, n, w, tier8_check } }, rref, rpos);
 }
 
 /* ---- direct kswv call: chunks of BSW_CUDA_KSWV_CHUNK pairs, pipelined over the slots like BSW -----
@@ -989,7 +1021,13 @@ void host_call_bsw(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint
     k.st.calls++;
     if (n <= 0) return;
     if (!pairs || !ref || !qer) die("null buffer passed to getScores");
-    if (n >= k.direct_min || k.count_cells || k.timing || call_is_heavy(k, pairs, n)) direct_call_bsw(k, pairs, ref, qer, n, w, tier8_check);
+    if (n >= k.direct_min || k.count_cells || k.timing || call_is_heavy(k, pairs, n)) {
+        if (k.arena_on && k.arena_defer && !k.count_cells && !k.timing) {      /* runs with the other calls of the bracket, at bsw_arena_end */
+            k.pending.push_back(DirectSeg{ pairs, ref, qer, n, w, tier8_check });
+            return;
+        }
+        direct_call_bsw(k, pairs, ref, qer, n, w, tier8_check);
+    }
     else staged_call(k, pairs, ref, qer, nullptr, n, w, tier8_check, 0, 0);
 }
 
@@ -1081,17 +1119,27 @@ void bsw_arena_end(bsw_t *h)
 {
     Core &k = h->k;
     if (!k.arena_on) return;
+    if (!k.pending.empty()) {                      /* the deferred calls of the bracket: one interleaved chunk pipeline */
+        const std::vector<DirectSeg> segs = std::move(k.pending);
+        k.pending.clear();
+        direct_call_bsw_multi(k, segs);
+    }
     for (size_t i = 0; i < k.ctx.size(); ++i)
-        if (k.ctx[i]) {
-            CK(cudaSetDevice(k.ctx[i]->dev));
-            for (Slot &sl : k.ctx[i]->slot) slot_retire(*k.ctx[i], sl);      /* deferred calls land here */
-            CK(cudaStreamSynchronize(k.ctx[i]->arena_stream));
-        }
+        if (k.ctx[i]) { CK(cudaSetDevice(k.ctx[i]->dev)); CK(cudaStreamSynchronize(k.ctx[i]->arena_stream)); }
     k.arena_on = false;
     k.arena_ref_h = k.arena_qer_h = nullptr; k.arena_ref_n = k.arena_qer_n = 0;
 }
 
-void bsw_arena_defer(bsw_t *h, int on) { h->k.arena_defer = on != 0; }
+void bsw_arena_defer(bsw_t *h, int on)
+{
+    Core &k = h->k;
+    k.arena_defer = on != 0;
+    if (!on && !k.pending.empty()) {               /* switched off inside a bracket: what is pending runs now */
+        const std::vector<DirectSeg> segs = std::move(k.pending);
+        k.pending.clear();
+        direct_call_bsw_multi(k, segs);
+    }
+}
 
 /* ---- resident reference --------------------------------------------------- */
 bsw_ref_t *bsw_ref_upload(const uint8_t *pac, int64_t l_pac)

@@ -121,12 +121,14 @@ void bsw_scalarBandedSWAWrapper(bsw_t *h, bsw_seqpair_t *pairArray, const uint8_
  * (staged) calls ignore the declaration. */
 void bsw_arena_begin(bsw_t *h, const uint8_t *seqBufRef, size_t refBytes, const uint8_t *seqBufQer, size_t qerBytes);
 void bsw_arena_end(bsw_t *h);
-/* Deferred completion inside an arena bracket (opt-in, off by default).  mem_chain2aln_across_reads_V2 reads no result
- * between the getScores8 and the getScores16 call of a side (bwamem.cpp; it only reads them once both tiers are back, to
- * chain h0 and to pick the band-retry pairs).  With on != 0 a large call between bsw_arena_begin and bsw_arena_end may
- * return while its last chunks are still computing / on their way home: the next call's uploads overlap them, and
- * bsw_arena_end returns only when every result of the bracket has landed in its SeqPair array.  The arrays must stay
- * valid and untouched until then.  Results are identical. */
+/* Deferred execution inside an arena bracket (opt-in, off by default).  mem_chain2aln_across_reads_V2 reads no result
+ * between the getScores8 and the getScores16 call of a side (bwamem.cpp; it reads them once both tiers are back, to chain
+ * h0 and to pick the band-retry pairs).  With on != 0 a LARGE call (direct route) between bsw_arena_begin and
+ * bsw_arena_end only records its arguments and returns; bsw_arena_end runs all recorded calls of the bracket as ONE
+ * interleaved chunk pipeline -- the call that mostly waits for PCIe (it brings the arenas up) and the one that mostly
+ * waits for the GPU fill each other's gaps -- and returns when every result has landed in its SeqPair array.  The
+ * arrays and buffers must stay valid and untouched until then.  Small (staged) calls are not deferred.  Results are
+ * identical. */
 void bsw_arena_defer(bsw_t *h, int on);
 
 /* ---- resident reference (no reference counterpart) -----------

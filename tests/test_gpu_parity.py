@@ -717,8 +717,8 @@ def test_arena_upload_once(ora, bsw):
 
 
 def test_arena_deferred_completion(ora, bsw):
-    """bsw_arena_defer: inside an arena bracket the tier-8 call may return before its last chunks are home; everything has
-    landed when bsw_arena_end returns.  Small chunks so that several are in flight across the two calls."""
+    """bsw_arena_defer: the large calls of an arena bracket are recorded and run as one interleaved chunk pipeline by
+    bsw_arena_end; every result has landed when it returns.  Small chunks so that the two calls really interleave."""
     import os
     (L, lr, lq), _ = common.bsw_c1(40000, seed=0x6B)
     o, _ = _oracle_bsw(ora, L, lr, lq)
