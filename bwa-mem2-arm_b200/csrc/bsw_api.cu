@@ -208,6 +208,7 @@ struct Core {
     int trace = 0;                   /* BSW_CUDA_TRACE: host-side timing of every direct call on stderr */
     int chunk_pairs = 1 << 19;
     bool chunk_ramp = true;                       /* direct calls: chunk sizes ramp up / down at the ends (chunk_starts) */
+    int kswv_no_w = 0;                            /* BSW_CUDA_KSWV_NO_W=1: resident kswv calls keep the 16-bit shapes off (probe) */
     int kswv_lanes = 0;                           /* kswv_sys.cuh: lanes per group (8 / 16 / 32); 0 = by batch size */
     int ahead = 2;
     int direct_min = 1 << 17;        /* host-pointer calls with fewer pairs go through the staged engine */
@@ -267,6 +268,7 @@ void core_init(Core &k, int mode)
     k.count_cells = env_int("BSW_CUDA_COUNT_CELLS", 0);
     k.chunk_pairs = env_int("BSW_CUDA_CHUNK_PAIRS", 1 << 19);
     k.kswv_lanes = env_int("BSW_CUDA_KSWV_LANES", 0);
+    k.kswv_no_w = env_int("BSW_CUDA_KSWV_NO_W", 0) ? 1 : 0;
     k.chunk_ramp = env_int("BSW_CUDA_CHUNK_RAMP", 1) != 0;
     k.ahead = env_int("BSW_CUDA_AHEAD", 2);
     k.trace = env_int("BSW_CUDA_TRACE", 0);
@@ -518,6 +520,17 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
                 CK(cudaStreamWaitEvent(s, x.bin_ev[qb], 0));
             }
     }
+    /* the 16-bit tier: sorted after the byte-key pairs, largest configuration first */
+    int n_w = 0;
+    for (int cfg = KSWV_SYSW_NCFG - 1; cfg >= 0; --cfg) {
+        const int cnt = pl->hist_w[cfg];
+        if (cnt <= 0) continue;
+        launch_kswv_sysw(cfg, sym, n_packed + n_w, cnt, std::max(1, pl->max_len1_packed), io, d_ref, d_qer, d_aln, sorted, k.c, is8, phase,
+                         (unsigned long long *)x.cells.p, s);
+        CK(cudaGetLastError());
+        k.st.kernel_launches++;
+        n_w += cnt;
+    }
     if (pl->n_general > 0) {
         const size_t per_pair = ((size_t)pl->max_len2_general + 2) * sizeof(int2) + ((size_t)pl->max_len1 + 2) * sizeof(int);
         int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)pl->n_general, ((size_t)1 << 30) / per_pair));
@@ -526,7 +539,7 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
         int *rm = (int *)((char *)sl.scratch.p + (size_t)chunk * ((size_t)pl->max_len2_general + 2) * sizeof(int2));
         for (int first = 0; first < pl->n_general; first += chunk) {
             int cnt = std::min(chunk, pl->n_general - first);
-            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, d_aln, sorted, n_packed + first, cnt,
+            kswv_general_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(io, d_ref, d_qer, d_aln, sorted, n_packed + n_w + first, cnt,
                                                                k.c, is8, phase, he, rm, (unsigned long long *)x.cells.p);
             CK(cudaGetLastError());
             k.st.kernel_launches++;
@@ -536,14 +549,14 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
         CK(cudaEventRecord(x.ev1, s)); CK(cudaEventSynchronize(x.ev1));
         float ms = 0; CK(cudaEventElapsedTime(&ms, x.ev0, x.ev1)); k.st.kernel_ms += ms;
     }
-    k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_general += pl->n_general;
+    k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_wide += n_w; k.st.pairs_general += pl->n_general;
 }
 
 void launch_kswv(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
                  bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
 {
     if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, 0);
+    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, is8 | k.kswv_no_w);      /* kswv: the plan's tier flag = is8 (admission of the 16-bit shapes) */
     launch_kswv_dp(k, rt, x, sl, pl, d_pairs, d_ref, d_qer, d_aln, n, is8, phase, s);
 }
 
@@ -840,7 +853,7 @@ void direct_call_kswv(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const u
         if (qhi > qlo) CK(cudaMemcpyAsync(sl.qer.p, qer + qlo, (size_t)(qhi - qlo), cudaMemcpyHostToDevice, sl.stream));
         k.st.h2d_bytes += (int64_t)j.cnt * sizeof(bsw_seqpair_t) + (rhi - rlo) + (qhi - qlo);
         j.rlo = rlo; j.qlo = qlo;
-        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - qlo, j.cnt, sl.stream, 0, rlo, rhi, qlo, qhi);
+        plan_enqueue(k, sl, (const bsw_seqpair_t *)sl.pairs.p, (const uint8_t *)sl.qer.p - qlo, j.cnt, sl.stream, is8, rlo, rhi, qlo, qhi);
     };
     /* stage A: the slot's previous chunk lands, then uploads + prep + sort + histogram read-back are enqueued */
     auto stage_a = [&](int ci) {
@@ -904,13 +917,14 @@ inline bool bytes_have_n(const uint8_t *p, int len)
 }
 
 /* class of one pair: the same rules prep_kernel applies on the device (bsw_kernels.cuh) */
-inline int classify(const Core &k, const bsw_seqpair_t &p, const uint8_t *qer)
+inline int classify(const Core &k, const bsw_seqpair_t &p, const uint8_t *qer, int is8)
 {
     const bool ok = k.mode == MODE_BSW ? packed_eligible(k.c, p.len1, p.len2, p.h0) : kswv_sys_eligible(k.c, p.len1, p.len2);
     int qb = (p.len2 + (k.mode == MODE_BSW ? BSW_SWEEP_SLACK : 0) + 15) >> 4;
     qb = qb < 1 ? 1 : qb;
     if (!ok || qb > BSW_NBINS) {
         if (k.mode == MODE_BSW && wide_eligible(k.c, p.len1, p.len2, p.h0)) return CLS_WIDE0 + wide_cfg_for(p.len2);
+        if (k.mode == MODE_KSWV && kswv_sysw_eligible(k.c, is8, p.len1, p.len2)) return CLS_WIDE0 + kswv_sysw_cfg_for(p.len2);
         return CLS_GENERAL;
     }
     if (p.len2 > 0 && bytes_have_n(qer + p.idq, p.len2)) return BSW_NBINS + qb;
@@ -941,10 +955,10 @@ void staged_call(Core &k, bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_
                 break;
             }
             bytes += b;
-            const int c = classify(k, p, qer);
+            const int c = classify(k, p, qer, is8);
             cls.push_back((uint8_t)c); cnt[c]++;
             if (c == CLS_GENERAL) { ml2g = std::max(ml2g, p.len2); ml1g = std::max(ml1g, p.len1); }
-            else if (c < CLS_GENERAL) ml1p = std::max(ml1p, p.len1);
+            else if (c < CLS_GENERAL || k.mode == MODE_KSWV) ml1p = std::max(ml1p, p.len1);     /* kswv: the 16-bit classes size the `b` lists too */
         }
         if (bad) die_contract(bad);
         const long long t1 = now_ns();

@@ -109,6 +109,12 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
             atomicAdd(&s_hist[qb + (qn ? BSW_NBINS + 2 : 0)], 1);
             atomicMax(&s_misc[4], len1);
             if (mode == MODE_KSWV) atomicMax(&s_ml2[qb], len2);
+        } else if (mode == MODE_KSWV && kswv_sysw_eligible(c, tier8_check, len1, len2)) {
+            /* scores or columns beyond the byte key: the 16-bit shapes of the registers kernel (kswv_sys.cuh, W) */
+            const int cfg = kswv_sysw_cfg_for(len2);
+            key = ((uint32_t)(cfg + 1) << 12) | ((uint32_t)len1 < 4095u ? (uint32_t)len1 : 4095u);
+            atomicAdd(&s_wide[cfg], 1);
+            atomicMax(&s_misc[4], len1);
         } else if (mode == MODE_BSW && allow_wide && wide_eligible(c, len1, len2, h0)) {
             /* too long or too high-scoring for the byte-packed rows: the 16-bit lanes-per-pair kernel takes it */
             const int cfg = wide_cfg_for(len2);
@@ -121,7 +127,7 @@ __global__ void prep_kernel(const bsw_seqpair_t *__restrict__ pairs, const uint8
         }
         atomicMax(&s_misc[1], len1);
         bool bad = len1 < 0 || len2 < 0 || (mode == MODE_BSW && h0 <= 0);
-        if (tier8_check && (len1 >= BSW_MAX_SEQ_LEN8 || len2 >= BSW_MAX_SEQ_LEN8)) bad = true;
+        if (mode == MODE_BSW && tier8_check && (len1 >= BSW_MAX_SEQ_LEN8 || len2 >= BSW_MAX_SEQ_LEN8)) bad = true;   /* kswv: tier8_check = is8 */
         if (bad) atomicAdd(&s_misc[3], 1);
         /* the host estimates the byte ranges to upload from a sample of the pairs; verify them all here */
         const long long ir = pairs[i].idr, iq = pairs[i].idq;
@@ -408,7 +414,7 @@ __device__ __forceinline__ void kswv_store(bsw_kswr_t *__restrict__ aln, const P
 /* ------------------------------------------------------------------ 4b. kswv in registers (kswv_sys.cuh)
  * One warp per block = 32 / G groups of two pairs; group g of block b serves the sorted slots first + (b * 32 / G + g) * 2
  * and + 1.  Dynamic shared memory: the `b` lists, cap words per pair. */
-template <int G, int C, bool SYM, bool QN>
+template <int G, int C, bool SYM, bool QN, bool W = false>
 __global__ void __launch_bounds__(32)
 kswv_sys_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, bsw_kswr_t *__restrict__ aln,
                 const uint32_t *__restrict__ sorted_idx, int first, int count, Const c, int is8, int phase, int cap,
@@ -423,7 +429,7 @@ kswv_sys_kernel(PairIO io, const uint8_t *__restrict__ ref, const uint8_t *__res
     const int pb = rel + 1 < count ? (int)sorted_idx[first + rel + 1] : -1;
     const PairIn A = load_pair(io, pa), B = load_pair(io, pb);
     KswOut oa, ob;
-    kswv_sys_lane<G, C, SYM, QN>(c, is8, A, B, ref, qer, gl, bl + (size_t)(g * 2) * cap, bl + (size_t)(g * 2 + 1) * cap, oa, ob);
+    kswv_sys_lane<G, C, SYM, QN, W>(c, is8, A, B, ref, qer, gl, bl + (size_t)(g * 2) * cap, bl + (size_t)(g * 2 + 1) * cap, oa, ob);
     unsigned long long my_cells = 0;
     if (gl == G - 1) {
         if (pa >= 0) { kswv_store(aln, io, pa, oa, phase); my_cells += (unsigned long long)oa.cells; }
@@ -442,7 +448,7 @@ static inline int kswv_sys_cols(int max_len2, bool sym, bool qn)
     return (sym && !qn) ? c : (c + 7) & ~7;
 }
 
-template <int G, int C, bool SYM, bool QN>
+template <int G, int C, bool SYM, bool QN, bool W = false>
 static inline void launch_kswv_sys_shape(int first, int count, int max_rows, PairIO io, const uint8_t *ref, const uint8_t *qer,
                                          bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
                                          unsigned long long *cells, cudaStream_t s)
@@ -451,7 +457,7 @@ static inline void launch_kswv_sys_shape(int first, int count, int max_rows, Pai
     const int cap = kswv_sys_list_cap(max_rows);
     const int grid = (count + 2 * NG - 1) / (2 * NG);
     const size_t smem = (size_t)NG * 2 * cap * sizeof(uint32_t);
-    kswv_sys_kernel<G, C, SYM, QN><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells);
+    kswv_sys_kernel<G, C, SYM, QN, W><<<grid, 32, smem, s>>>(io, ref, qer, aln, sorted, first, count, c, is8, phase, cap, cells);
 }
 
 /* one launch over the sorted slots [first, first + count), all of whose queries have at most max_len2 bases.
@@ -512,6 +518,24 @@ static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, int lanes, i
 #undef KSWV_SYS_CASEQ
 #undef KSWV_SYS_COARSE
 #undef KSWV_SYS_LAUNCH
+}
+
+/* the 16-bit tier: configuration cfg of kswv_sys.cuh (kswv_sysw_cols) over the sorted slots [first, first + count); always
+ * the general score table (queries with and without N together) */
+static inline void launch_kswv_sysw(int cfg, bool sym, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
+                                    const uint8_t *qer, bsw_kswr_t *aln, const uint32_t *sorted, const Const &c, int is8, int phase,
+                                    unsigned long long *cells, cudaStream_t s)
+{
+#define KSWV_SYSW_LAUNCH(G, CC) \
+    if (sym) launch_kswv_sys_shape<G, CC, true, true, true>(first, count, max_rows, io, ref, qer, aln, sorted, c, is8, phase, cells, s); \
+    else launch_kswv_sys_shape<G, CC, false, true, true>(first, count, max_rows, io, ref, qer, aln, sorted, c, is8, phase, cells, s)
+    switch (cfg) {
+    case 0: KSWV_SYSW_LAUNCH(8, 8); break;   case 1: KSWV_SYSW_LAUNCH(8, 16); break;
+    case 2: KSWV_SYSW_LAUNCH(8, 24); break;  case 3: KSWV_SYSW_LAUNCH(8, 32); break;
+    case 4: KSWV_SYSW_LAUNCH(16, 20); break; case 5: KSWV_SYSW_LAUNCH(16, 24); break;
+    case 6: KSWV_SYSW_LAUNCH(16, 28); break; default: KSWV_SYSW_LAUNCH(16, 32); break;
+    }
+#undef KSWV_SYSW_LAUNCH
 }
 
 /* ------------------------------------------------------------------ 5b. kswv general */

@@ -476,6 +476,11 @@ inline void Engine::submit(StagedSlot &s)
                     }
                 }
         }
+        for (const WideSeg &sg : segs) {               /* the 16-bit classes (kswv_sys.cuh, W), largest configuration first */
+            launch_kswv_sysw(sg.cfg, key.c.oe_del == key.c.oe_ins, sg.first, sg.count, std::max(1, s.max_len1_packed), io, seq, seq, d_aln,
+                             s.d_sorted, key.c, key.is8, 0, d_cells, q);
+            ++launches;
+        }
         if (n_general > 0) {
             const size_t he_b = (size_t)n_general * ((size_t)s.max_len2_general + 2) * sizeof(int2);
             s.scratch.reserve(he_b + (size_t)n_general * ((size_t)s.max_len1_general + 2) * sizeof(int));

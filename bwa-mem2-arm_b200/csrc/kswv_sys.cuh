@@ -47,6 +47,23 @@ BSW_HD bool kswv_sys_eligible(const Const &c, int len1, int len2)
 {
     return kswv_packed_eligible(c, len1, len2) && len1 <= KSWV_SYS_MAX_ROWS && c.a <= 120 && c.b <= 120 && c.ambig <= 0;
 }
+/* The 16-bit tier (template flag W): scores < 2048, queries of up to 512 bases -- what kswv::getScores16 is for (reads
+ * longer than 255 bp, match scores > 1).  Eight shapes by query length: 8 lanes x 8 / 16 / 24 / 32 columns, then
+ * 16 lanes x 20 / 24 / 28 / 32 columns.  The 8-bit entry point keeps ksw_u8's saturation rule and is not admitted. */
+#define KSWV_SYSW_NCFG 8
+#define KSWV_SYSW_MAX_SCORE 2047
+BSW_HD int kswv_sysw_cols(int cfg) { return cfg < 4 ? 64 * (cfg + 1) : 320 + 64 * (cfg - 4); }
+BSW_HD int kswv_sysw_cfg_for(int len2)
+{
+    for (int k = 0; k < KSWV_SYSW_NCFG; ++k) if (len2 <= kswv_sysw_cols(k)) return k;
+    return -1;
+}
+BSW_HD bool kswv_sysw_eligible(const Const &c, int is8, int len1, int len2)
+{
+    if (is8 || len1 < 0 || len2 < 0 || len2 > kswv_sysw_cols(KSWV_SYSW_NCFG - 1) || len1 > KSWV_SYS_MAX_ROWS) return false;
+    if (c.a > 120 || c.b > 120 || c.ambig > 0) return false;
+    return (long long)mn(len1, len2) * c.a <= KSWV_SYSW_MAX_SCORE;
+}
 /* `b`-list entries a pair of `rows` target bases can produce, plus the open one */
 BSW_HD int kswv_sys_list_cap(int rows) { return (rows >> 1) + 2; }
 
@@ -55,12 +72,14 @@ BSW_HD int kswv_sys_list_cap(int rows) { return (rows >> 1) + 2; }
  * group's `b`-list storage for pair A / B (kswv_sys_list_cap(max rows) words each; only the last lane touches it).
  * Results are valid in lane G - 1 only.
  */
-template <int G, int C, bool SYM, bool QN>
+template <int G, int C, bool SYM, bool QN, bool W = false>
 BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn &B,
                           const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer, int gl,
                           uint32_t *blA, uint32_t *blB, KswOut &oa, KswOut &ob)
 {
-    static_assert(G * C <= KSWV_SYS_MAX_COLS, "column index must fit the key's byte");
+    /* key of a cell: max << 8 | 255 - global column (scores and columns < 256), or -- W, the 16-bit tier -- max << 5 |
+     * 31 - column within the lane (scores < 2048, any number of columns), the lane travelling beside it */
+    static_assert(W ? C <= 32 : G * C <= KSWV_SYS_MAX_COLS, "column index must fit the key");
     const PairIn *in[2] = { &A, &B };
     uint32_t *bl[2] = { blA, blB };
     const int shift = c.b > -c.ambig ? c.b : -c.ambig;       /* |min(mat)| */
@@ -107,7 +126,8 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
     const uint32_t KOFF = (uint32_t)(gl * C) * 0x00010001u;
     /* h * 256 + column as an IMAD (the FMA pipe idles, the ALU pipe is the bound): the multiplier must be a value ptxas
      * cannot fold, or it emits an ALU-pipe LEA */
-    const uint32_t K256 = 256u + ((uint32_t)is8 & 2u);
+    const uint32_t K256 = (W ? 32u : 256u) + ((uint32_t)is8 & 2u);
+    const uint32_t KCOL = W ? 0x001f001fu : 0x00ff00ffu;
 
     /* target bases, G rows at a time: in the steps with s % G == 0 lane l of the group turns the bases of row s + l (fetched
      * one batch ahead) into that row's score tables; lane 0 picks row s's up with one indexed shuffle per table.  Rows
@@ -133,7 +153,7 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
 
     /* row tables of the step (QN: LA = target selector T, LB unused).  A lane without a row yet: all-zero tables / the N code */
     uint32_t LA = QN ? 0x4444u : 0u, LB = 0u;
-    uint32_t hout = 0u, fout = 0u, kout = 0u, dprev = 0u;
+    uint32_t hout = 0u, fout = 0u, kout = 0u, dprev = 0u, lout = 0u, BL = 0u;    /* W: lane of the running key / of the best key */
     int s = 0;
     while (w_any(gl == G - 1 && R != 0u)) {
         if ((s & (G - 1)) == 0) {
@@ -148,7 +168,9 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
         uint32_t nLA = w_shfl_up(LA, 1, G), nLB = 0u, fB = 0u;
         if (!QN) { fB = w_shfl(TB, s & (G - 1), G); nLB = w_shfl_up(LB, 1, G); }
         uint32_t hin = w_shfl_up(hout, 1, G), f = w_shfl_up(fout, 1, G), kin = w_shfl_up(kout, 1, G);
-        if (gl == 0) { nLA = fA; nLB = fB; hin = 0u; f = 0u; kin = 0u; }
+        uint32_t lin = 0u;
+        if (W) lin = w_shfl_up(lout, 1, G);
+        if (gl == 0) { nLA = fA; nLB = fB; hin = 0u; f = 0u; kin = 0u; lin = 0u; }
         LA = nLA; LB = nLB;
 
         /* ---- this lane's C cells of row s - gl (A.2) ----
@@ -174,25 +196,32 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
                 f = p_addmax_relu(h, NOI, p_add(f, NEI));
             }
             Hc[k] = h;
-            const uint32_t kc = h * K256 + (0x00ff00ffu - (uint32_t)k * 0x00010001u);     /* IMAD: the FMA pipe idles here */
+            const uint32_t kc = h * K256 + (KCOL - (uint32_t)k * 0x00010001u);           /* IMAD: the FMA pipe idles here */
             if (k & 1) key = p_max3u(key, kprev, kc); else kprev = kc;
             t = tn;
         }
         if (C & 1) key = p_maxu(key, kprev);
         hout = Hc[C - 1]; fout = f;
-        kout = p_maxu(kin, key - KOFF);              /* column byte 255 - (gl*C + k): ties keep the smaller column */
+        if (!W) kout = p_maxu(kin, key - KOFF);      /* column byte 255 - (gl*C + k): ties keep the smaller column */
+        else {                                       /* mine only on a strictly larger maximum: ties keep the earlier lane */
+            const uint32_t KI = kin | 0x001f001fu;
+            const uint32_t WM = p_minu(p_maxu(KI, key) ^ KI, ONE2) * 0xffffu;
+            kout = (kin & ~WM) | (key & WM);
+            lout = (lin & ~WM) | (((uint32_t)gl * ONE2) & WM);
+        }
 
         /* ---- bookkeeping of row s - (G-1), in the last lane (A.2), both pairs at once ---- */
         if (gl == G - 1 && s >= G - 1) {
             const int row = s - (G - 1);
             const uint32_t LM = p_minu(R, ONE2) * 0xffffu;           /* 0xffff per pair that still wants this row */
-            const uint32_t IM = st_e(kout) & LM;                     /* row maxima */
+            const uint32_t IM = (W ? (kout >> 5) & 0x07ff07ffu : st_e(kout)) & LM;     /* row maxima */
             const uint32_t nGM = p_maxu(GM, IM);
             const uint32_t chg = nGM ^ GM;
             if (chg) {                                               /* imax > gmax: new (gmax, te, qe); stop conditions */
                 const uint32_t CM = p_minu(chg, ONE2) * 0xffffu;
                 TE = (TE & ~CM) | (((uint32_t)row * ONE2) & CM);
                 BK = (BK & ~CM) | (kout & CM);
+                if (W) BL = (BL & ~CM) | (lout & CM);
                 GM = nGM;
                 const uint32_t stopb = ~p_add(nGM, NTH) & CM & 0x80008000u;
                 if (stopb & 0x00008000u) { lim[0] = row + 1; R &= 0xffff0000u; }
@@ -219,7 +248,11 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
         ++s;
     }
 #pragma unroll
-    for (int p = 0; p < 2; ++p) { gmax[p] = half_u(GM, p); te[p] = half_s(TE, p); qk[p] = half_u(BK, p) & 0xff; }
+    for (int p = 0; p < 2; ++p) {
+        gmax[p] = half_u(GM, p); te[p] = half_s(TE, p);
+        /* 255 - global column of the best key */
+        qk[p] = W ? 255 - (half_u(BL, p) * C + 31 - (half_u(BK, p) & 31)) : half_u(BK, p) & 0xff;
+    }
 
     KswOut *out[2] = { &oa, &ob };
 #pragma unroll

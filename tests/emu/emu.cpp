@@ -155,7 +155,7 @@ static void kput(bsw_kswr_t *aln, const bsw_seqpair_t &sp, int i, const KswOut &
 }   // extern "C"
 
 // registers-and-shuffles kernel (kswv_sys.cuh): one emulated warp per 32 / G groups of two pairs
-template <int G, int C, bool SYM, bool QN>
+template <int G, int C, bool SYM, bool QN, bool W = false>
 static void sys_warp(const Const &c, int is8, const bsw_seqpair_t *pairs, const int *ids, int cnt, const uint8_t *ref,
                      const uint8_t *qer, KswOut *res)
 {
@@ -173,7 +173,7 @@ static void sys_warp(const Const &c, int is8, const bsw_seqpair_t *pairs, const 
             else P[u] = { 0, 0, 0, 0, 0, 0 };
         }
         KswOut oa, ob;
-        kswv_sys_lane<G, C, SYM, QN>(c, is8, P[0], P[1], ref, qer, gl, bl.data() + (size_t)(g * 2) * cap, bl.data() + (size_t)(g * 2 + 1) * cap, oa, ob);
+        kswv_sys_lane<G, C, SYM, QN, W>(c, is8, P[0], P[1], ref, qer, gl, bl.data() + (size_t)(g * 2) * cap, bl.data() + (size_t)(g * 2 + 1) * cap, oa, ob);
         if (gl == G - 1) { if (g * 2 < cnt) res[g * 2] = oa; if (g * 2 + 1 < cnt) res[g * 2 + 1] = ob; }
     });
 }
@@ -188,6 +188,20 @@ static void sys_warp_v(const Const &c, int is8, bool qn, const bsw_seqpair_t *pa
 }
 
 extern "C" {
+
+// the 16-bit tier (kswv_sys.cuh, W): configuration cfg, general score table
+static void sysw_warp(int cfg, const Const &c, int is8, const bsw_seqpair_t *pairs, const int *ids, int cnt, const uint8_t *ref,
+                      const uint8_t *qer, KswOut *res)
+{
+    const bool sym = c.oe_del == c.oe_ins;
+#define SYSW(G, CC) if (sym) sys_warp<G, CC, true, true, true>(c, is8, pairs, ids, cnt, ref, qer, res); \
+                    else sys_warp<G, CC, false, true, true>(c, is8, pairs, ids, cnt, ref, qer, res)
+    switch (cfg) {
+    case 0: SYSW(8, 8); break;   case 1: SYSW(8, 16); break;  case 2: SYSW(8, 24); break;  case 3: SYSW(8, 32); break;
+    case 4: SYSW(16, 20); break; case 5: SYSW(16, 24); break; case 6: SYSW(16, 28); break; default: SYSW(16, 32); break;
+    }
+#undef SYSW
+}
 
 int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer, bsw_kswr_t *aln, int n,
              int o_del, int e_del, int o_ins, int e_ins, int a, int b, int ambig,
@@ -205,8 +219,14 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
         const bool all_qn = (force_general >> 16) & 1;
         const int lanes = 8 << ((force_general >> 17) & 3);      // bits 17..18: 8 / 16 / 32 lanes per group (the small-batch shapes)
         std::vector<int> by[2][17];
+        std::vector<int> byw[KSWV_SYSW_NCFG];
+        const bool force_w = (force_general >> 19) & 1;      // bit 19: every admissible pair through the 16-bit shapes
         for (int i = 0; i < n; ++i) {
-            if (!kswv_sys_eligible(c, pairs[i].len1, pairs[i].len2)) { ge.push_back(i); continue; }
+            if (force_w || !kswv_sys_eligible(c, pairs[i].len1, pairs[i].len2)) {
+                if (kswv_sysw_eligible(c, is8, pairs[i].len1, pairs[i].len2)) byw[kswv_sysw_cfg_for(pairs[i].len2)].push_back(i);
+                else ge.push_back(i);
+                continue;
+            }
             bool qn = all_qn;
             for (int j = 0; j < pairs[i].len2; ++j) qn |= qer[pairs[i].idq + j] > 3;
             int qb = (pairs[i].len2 + 15) >> 4; qb = qb < 1 ? 1 : qb;
@@ -247,6 +267,20 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
                     tot += cnt;
                 }
             }
+        for (int cfg = 0; cfg < KSWV_SYSW_NCFG; ++cfg) {
+            const std::vector<int> &v = byw[cfg];
+            const int per = cfg < 4 ? 8 : 4;
+            for (size_t f = 0; f < v.size(); f += per) {
+                const int cnt = (int)std::min<size_t>(per, v.size() - f);
+                KswOut res[8];
+                sysw_warp(cfg, c, is8, pairs, v.data() + f, cnt, ref, qer, res);
+                for (int k = 0; k < cnt; ++k) {
+                    const int i = v[f + k];
+                    kput(aln, pairs[i], i, res[k], phase); if (cells_out) cells_out[i] = res[k].cells;
+                }
+                tot += cnt;
+            }
+        }
         for (int i : ge) {
             PairIn P = { pairs[i].idr, pairs[i].idq, pairs[i].len1, pairs[i].len2, pairs[i].h0, 1 };
             KswOut o;

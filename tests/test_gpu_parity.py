@@ -388,12 +388,43 @@ def test_kswv_edge(ora, ks, bsw):
     ora.kswv_batch(P, r, q, ao, prm, 1, 0, 8)
     ks.getScores8(P, r, q, ag, len(P), 1, 0)
     assert (ao == ag).all() and (ao["score"] == 255).any()
-    P, r, q = ora.gen_kswv(200, qlen=400, tmin=600, tmax=900, seed=10, xtra=ora.KSW_XSUBO | ora.KSW_XSTART | 19)
+    P, r, q = ora.gen_kswv(200, qlen=600, tmin=700, tmax=900, seed=10, xtra=ora.KSW_XSUBO | ora.KSW_XSTART | 19)
     ao = np.zeros(len(P), ora.KSWR); ag = np.zeros(len(P), bsw.KSWR)
     ora.kswv_batch(P, r, q, ao, prm, 0, 0, 8)
     ks.getScores16(P, r, q, ag, len(P), 1, 0)
     assert (ao == ag).all()
     assert ks.stats()["pairs_general"] > 0
+
+
+def test_kswv_16bit_tier(ora, ks, bsw):
+    """kswv::getScores16 proper: scores above 255 and queries above 255 bases stay on the registers kernel (its 16-bit
+    shapes, kswv_sys.cuh W) -- nothing below 2048 / 512 bases may reach the 32-bit kernel.  2 x 300 bp and 2 x 500 bp mates,
+    phase 0 and 1, with N; match score 2 on 150 bp mates; asymmetric gap sums."""
+    prm = ora.make_params()
+    for n, ql, t0, t1 in ((6000, 300, 400, 700), (1500, 500, 600, 900)):
+        P, r, q = ora.gen_kswv(n, qlen=ql, tmin=t0, tmax=t1, seed=0xD0 + ql, p_n=0.001)
+        ao = np.zeros(len(P), ora.KSWR); ag = np.zeros(len(P), bsw.KSWR)
+        ora.kswv_batch(P, r, q, ao, prm, 0, 0, 8)
+        ks.reset_stats()
+        ks.getScores16(P, r, q, ag, len(P), 1, 0)
+        assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
+        assert (ao["score"] > 255).any()
+        p1, r1, q1 = ora.kswv_phase1_inputs(P, r, q, ao)
+        ora.kswv_batch(p1, r1, q1, ao, prm, 0, 1, 8)
+        ks.getScores16(p1, r1, q1, ag, len(p1), 1, 1)
+        assert (ao == ag).all()
+        assert ks.stats()["pairs_general"] == 0
+    for sc in (dict(o_del=6, e_del=1, o_ins=6, e_ins=1, a=2, b=4), dict(o_del=4, e_del=2, o_ins=7, e_ins=1, a=3, b=3)):
+        h = bsw.kswv(sc["o_del"], sc["e_del"], sc["o_ins"], sc["e_ins"], sc["a"], sc["b"], 1, 2048, 256)
+        if ks.route == "direct":
+            h.set_direct_min(0)
+        P, r, q = ora.gen_kswv(5000, seed=0xD5, a=sc["a"])
+        ao = np.zeros(len(P), ora.KSWR); ag = np.zeros(len(P), bsw.KSWR)
+        ora.kswv_batch(P, r, q, ao, ora.make_params(**sc), 0, 0, 8)
+        h.getScores16(P, r, q, ag, len(P), 1, 0)
+        assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
+        assert h.stats()["pairs_general"] == 0 and (ao["score"] > 255).any()
+        h.close()
 
 
 def test_device_resident_api(ora, sw, bsw):

@@ -128,6 +128,24 @@ def test_kswv_sys_kernel(ora):
         _check_kswv_sys(ora, P, r, q, 0, **sc)
 
 
+def test_kswv_sys_16bit_tier(ora):
+    """The 16-bit shapes of kswv_sys.cuh (W: key = max << 5 | column within the lane, the lane beside it): scores up to 2047,
+    queries up to 512 bases, 8 and 16 lanes per group; and every byte-key pair forced through them."""
+    P, r, q = ora.gen_kswv(120, qlen=300, tmin=400, tmax=700, seed=21)                   # 2 x 300 bp: 16 lanes x 20 columns
+    assert _check_kswv_sys(ora, P, r, q, 0) == len(P)
+    P, r, q = ora.gen_kswv(60, qlen=500, tmin=600, tmax=900, seed=22, p_n=0.002)          # 16 x 32
+    assert _check_kswv_sys(ora, P, r, q, 0) == len(P)
+    P, r, q = ora.gen_kswv(160, qlen=150, tmin=300, tmax=500, seed=23, p_n=0.002)         # a = 2: scores to 300 on 150 columns
+    assert _check_kswv_sys(ora, P, r, q, 0, o_del=6, e_del=1, o_ins=6, e_ins=1, a=2, b=4) == len(P)
+    _check_kswv_sys(ora, P, r, q, 0, o_del=4, e_del=2, o_ins=7, e_ins=1, a=3, b=3)        # asymmetric gap sums (non-SYM)
+    P, r, q = ora.gen_random(500, 0, 330, 0, 500, sim=0.85, p_n=0.004, seed=24)           # ragged, empty, every configuration
+    P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | 9
+    _check_kswv_sys(ora, P, r, q, 0, mode=1 << 19)
+    # the 8-bit entry point keeps ksw_u8's saturation rule: nothing of it may reach the 16-bit shapes
+    P, r, q = ora.gen_kswv(60, qlen=300, tmin=400, tmax=500, seed=25, div=0.0, xtra=ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 19)
+    assert _check_kswv_sys(ora, P, r, q, 1) == 0
+
+
 def test_kswv_c4_shape(ora):
     P, r, q = ora.gen_kswv(1200)
     _check_kswv(ora, P, r, q, 1)
