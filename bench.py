@@ -675,6 +675,17 @@ def run_kswv(args):
         step_e2e_timed()
     e2e_ms = 1e3 * t_calls[0]; est = ks.stats()
     check("e2e 8-bit phase 0+1", a1, ha); check("e2e 16-bit phase 0+1", b1, hb)
+    # the same step through kswv_align2: ONE call per tier, hand-off and both passes on the device, bases cross PCIe once
+    ha[...] = 0; hb[...] = 0
+
+    def step_align2():
+        ks.align2(hK, hkr, hkq, ha, n, 1); ks.align2(hK16, hkr16, hkq16, hb, n16, 0)
+    ks.reset_stats(); a2_ms = time_host(c, args, step_align2); a2st = ks.stats()
+    check("e2e kswv_align2 8-bit", a1, ha); check("e2e kswv_align2 16-bit", b1, hb)
+    variants = {"align2": {"ms_per_step": a2_ms / args.steps, "value": cells_step / (a2_ms / args.steps * 1e-3) / 1e9, "unit": "GCUPS (this rank)",
+                           "h2d_bytes_per_step": a2st["h2d_bytes"] // (args.steps + 2), "d2h_bytes_per_step": a2st["d2h_bytes"] // (args.steps + 2),
+                           "api": "kswv_align2 on pinned host buffers: one call per tier instead of getScores(phase 0) + the caller's reversed-prefix "
+                                  "loop + getScores(phase 1); the hand-off runs on the device (SURVEY.md 8(f).3)"}}
     sampler.stop()
     npairs = n + len(p1) + n16 + len(p16)
 
@@ -694,6 +705,7 @@ def run_kswv(args):
             "e2e": {"value": cells_all / (e2e_step * 1e-3) / 1e9, "unit": "GCUPS", "ms_per_step": e2e_step, "pairs_per_s": pairs_all / (e2e_step * 1e-3),
                     "h2d_bytes_per_step": est["h2d_bytes"] // args.steps, "d2h_bytes_per_step": est["d2h_bytes"] // args.steps,
                     "api": "kswv_getScores8/16 phase 0 then phase 1 on pinned host buffers (the caller's reversed-prefix hand-off between them is host work and not in the time)"},
+            "e2e_variants": variants,
             "gpu_launches": int(launches),
             "roofline": roofline(bswb200, c, 7, cells_step, kms, ms_step, "kswv_sys_kernel", "kswv_sys_kernel"),
             "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "setup_s": time.perf_counter() - t_setup, "oracle_full_config_s": oracle_s,

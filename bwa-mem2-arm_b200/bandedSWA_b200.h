@@ -98,6 +98,10 @@ public:
                      uint16_t numThreads, int phase)
     { kswv_getScores16(h_, pairArray, seqBufRef, seqBufQer, reinterpret_cast<bsw_kswr_t *>(aln), numPairs, numThreads, phase); }
 
+    /* host buffers: ksw_align2 in ONE call -- replaces getScores(phase 0) + the host hand-off loop + getScores(phase 1) */
+    void align2(const SeqPair *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, kswr_t *aln, int32_t numPairs, int is8)
+    { kswv_align2(h_, pairArray, seqBufRef, seqBufQer, reinterpret_cast<bsw_kswr_t *>(aln), numPairs, is8); }
+
     /* device-resident pairs: ksw_align2 (forward pass, hand-off, reverse pass) in one submission; see kswv_dev_align2 */
     void align2Resident(const SeqPair *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer, kswr_t *d_aln,
                         int32_t numPairs, int is8, void *stream)

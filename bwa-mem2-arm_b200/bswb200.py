@@ -27,7 +27,7 @@ KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "kswv_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -92,6 +92,8 @@ def lib():
     L.bsw_global2.argtypes = [vp, vp, i32, vp, vp, vp, C.c_int64]
     L.bsw_dev_global2.restype = C.c_int64
     L.bsw_dev_global2.argtypes = [vp, vp, i32, vp, vp, vp, C.c_int64, i32, vp]
+    L.kswv_align2.restype = None
+    L.kswv_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int]
     L.kswv_dev_align2.restype = None
     L.kswv_dev_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, vp]
     L.bsw_host_alloc.restype = vp
@@ -279,6 +281,11 @@ class kswv:
     def dev_getScores(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, phase=0, stream=0):
         self._L.kswv_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), _ptr(d_aln), numPairs,
                                    int(is8), int(phase), C.c_void_p(stream))
+
+    def align2(self, pairArray, seqBufRef, seqBufQer, aln, numPairs=None, is8=1):
+        """ksw_align2 on host buffers in one call: both passes and the hand-off on the device (kswv_align2)."""
+        n = len(pairArray) if numPairs is None else numPairs
+        self._L.kswv_align2(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), _ptr(aln), n, int(is8))
 
     def dev_align2(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, stream=0):
         """Forward pass, device-side hand-off and reverse pass of ksw_align2 in one submission (resident buffers)."""

@@ -19,6 +19,7 @@
  * No CPU fallback: any CUDA failure is fatal, as in the reference (fprintf + exit).
  */
 #include <vector>
+#include <thread>
 #include <string>
 #include <algorithm>
 #include <mutex>
@@ -552,12 +553,19 @@ void launch_kswv_dp(Core &k, DevRt &rt, DevCtx &x, Slot &sl, const Plan *pl, bsw
     k.st.pairs += n; k.st.pairs_packed += n_packed; k.st.pairs_wide += n_w; k.st.pairs_general += pl->n_general;
 }
 
-void launch_kswv(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
-                 bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s)
+/* returns false (nothing launched) when a pair names bases outside [rlo, rhi) / [qlo, qhi): the caller uploaded ranges
+ * estimated from a sample of the pairs and has to redo them exactly */
+bool launch_kswv(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_ref, const uint8_t *d_qer,
+                 bsw_kswr_t *d_aln, int n, int is8, int phase, cudaStream_t s,
+                 long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62)
 {
-    if (n <= 0) return;
-    const Plan *pl = run_plan(k, sl, d_pairs, d_qer, n, s, is8 | k.kswv_no_w);      /* kswv: the plan's tier flag = is8 (admission of the 16-bit shapes) */
+    if (n <= 0) return true;
+    /* kswv: the plan's tier flag = is8 (admission of the 16-bit shapes) */
+    plan_enqueue(k, sl, d_pairs, d_qer, n, s, is8 | k.kswv_no_w, rlo, rhi, qlo, qhi);
+    const Plan *pl = plan_wait(sl, s);
+    if (pl->oob_pairs) return false;
     launch_kswv_dp(k, rt, x, sl, pl, d_pairs, d_ref, d_qer, d_aln, n, is8, phase, s);
+    return true;
 }
 
 /* byte extents [lo, hi) of the sequence buffers touched by pairs[first, first+cnt) */
@@ -1316,20 +1324,13 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
  * get a second pass, their reversed prefixes, the phase-1 records), reverse pass refining d_aln in place.  The pairs and
  * the sequence buffers are not modified.  Two small read-backs (the hand-off totals, the second pass's histogram) on
  * top of the first pass's histogram. */
-void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
-                     bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream)
+/* ksw_align2 on resident buffers: forward pass, hand-off, reverse pass.  sl = scratch slot.  Returns
+ * false when the forward pass found a pair outside the given byte ranges (nothing was computed). */
+static bool dev_align2_core(Core &k, DevRt &rt, DevCtx &x, Slot &sl, bsw_seqpair_t *d_pairs, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                            bsw_kswr_t *d_aln, int n, int is8, cudaStream_t s,
+                            long long rlo = 0, long long rhi = (long long)1 << 62, long long qlo = 0, long long qhi = (long long)1 << 62)
 {
-    Core &k = h->k;
-    DevCtx &x = k.cx(0);
-    DevRt &rt = k.rt(0);
-    CK(cudaSetDevice(x.dev));
-    cudaStream_t s = (cudaStream_t)stream;
-    k.st.calls++;
-    const int n = numPairs;
-    if (n <= 0) return;
-    Slot &sl = dev_slot(x, s, false);
-    bsw_seqpair_t *d_pairs = const_cast<bsw_seqpair_t *>(d_pairArray);
-    launch_kswv(k, rt, x, sl, d_pairs, d_seqBufRef, d_seqBufQer, d_aln, n, is8, 0, s);
+    if (!launch_kswv(k, rt, x, sl, d_pairs, d_seqBufRef, d_seqBufQer, d_aln, n, is8, 0, s, rlo, rhi, qlo, qhi)) return false;
     /* hand-off: three exclusive scans (slot, target bytes, query bytes), totals, fill */
     sl.kx_off.reserve((size_t)n * 3 * sizeof(int) + 4 * sizeof(int));
     int *off_k = (int *)sl.kx_off.p, *off_r = off_k + n, *off_q = off_r + n, *totals = off_q + n;
@@ -1347,7 +1348,7 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
     CK(cudaStreamSynchronize(s));
     const int n1 = sl.h_count[0], tot_r = sl.h_count[1], tot_q = sl.h_count[2];
     k.st.kernel_launches += 7;
-    if (n1 < 0 || tot_r < 0 || tot_q < 0) die("kswv_dev_align2: hand-off sizes overflow 31 bits (split the batch)");
+    if (n1 < 0 || tot_r < 0 || tot_q < 0) die("kswv align2: hand-off sizes overflow 31 bits (split the batch)");
     if (n1 > 0) {
         sl.kx_pairs.reserve((size_t)n1 * sizeof(bsw_seqpair_t));
         sl.kx_ref.reserve((size_t)tot_r + 64); sl.kx_qer.reserve((size_t)tot_q + 64);
@@ -1358,7 +1359,116 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
         k.st.kernel_launches++;
         launch_kswv(k, rt, x, sl, (bsw_seqpair_t *)sl.kx_pairs.p, (const uint8_t *)sl.kx_ref.p, (const uint8_t *)sl.kx_qer.p, d_aln, n1, is8, 1, s);
     }
+    return true;
+}
+
+void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                     bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream)
+{
+    Core &k = h->k;
+    DevCtx &x = k.cx(0);
+    CK(cudaSetDevice(x.dev));
+    cudaStream_t s = (cudaStream_t)stream;
+    k.st.calls++;
+    if (numPairs <= 0) return;
+    Slot &sl = dev_slot(x, s, false);
+    dev_align2_core(k, k.rt(0), x, sl, const_cast<bsw_seqpair_t *>(d_pairArray), d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, s);
     CK(cudaEventRecord(sl.dev_done, s));
+}
+
+/* ksw_align2 on HOST buffers in one call: what mem_sam_pe_batch does with getScores(phase 0), a host loop that reverses the
+ * prefixes of the qualifying hits, and getScores(phase 1) -- here records and bases go up once, the hand-off and both
+ * passes stay on the device, the finished kswr_t come down.  Chunks of BSW_CUDA_KSWV_CHUNK pairs (ramped at the ends):
+ * chunk c + 1 uploads on its staging slot's stream while chunk c computes on slot 0's. */
+void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, bsw_kswr_t *aln,
+                 int32_t numPairs, int is8)
+{
+    Core &k = h->k;
+    k.st.calls++;
+    const int n = numPairs;
+    if (n <= 0) return;
+    if (!pairArray || !seqBufRef || !seqBufQer || !aln) die("null buffer passed to kswv_align2");
+    DevCtx &x = k.cx(0);
+    DevRt &rt = k.rt(0);
+    CK(cudaSetDevice(x.dev));
+    for (Slot &sl : x.slot) slot_retire(x, sl);
+    const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
+    const std::vector<int> cstart = chunk_starts(n, chunk, 1, k.chunk_ramp);
+    const int nchunks = (int)cstart.size() - 1;
+    /* A chunk's three phases each end in a small read-back the host waits for (two plans, the hand-off sizes), and the
+     * device drains meanwhile.  Two workers -- the calling thread and one helper on a second context from the pool --
+     * take alternate chunks, so one chunk's kernels fill the other's gaps (BSW_CUDA_ALIGN2_WORKERS=1: one). */
+    const int nworkers = nchunks >= 4 ? std::max(1, std::min(std::min(4, nchunks / 2), env_int("BSW_CUDA_ALIGN2_WORKERS", 2))) : 1;
+    auto run = [&](Core &kk, DevCtx &xx, int worker) {
+        CK(cudaSetDevice(xx.dev));
+        Slot &cs = xx.slot[0];                     /* scratch (plan, sort, hand-off) and the compute stream */
+        struct Up { long long rlo, rhi, qlo, qhi; } up[2];
+        std::vector<int> mine;
+        for (int ci = worker; ci < nchunks; ci += nworkers) mine.push_back(ci);
+        auto upload = [&](int m, bool exact) {
+            Slot &st = xx.slot[1 + (m & 1)];
+            slot_retire(xx, st);                   /* the chunk that used this staging slot two chunks ago is home */
+            const int first = cstart[mine[m]], cnt = cstart[mine[m] + 1] - first;
+            Up &u = up[m & 1];
+            if (exact) extents(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi);
+            else extents_sampled(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi);
+            st.pairs.reserve((size_t)cnt * sizeof(bsw_seqpair_t));
+            st.ref.reserve((size_t)(u.rhi - u.rlo) + 64); st.qer.reserve((size_t)(u.qhi - u.qlo) + 64);
+            st.aln.reserve((size_t)cnt * sizeof(bsw_kswr_t));
+            CK(cudaMemcpyAsync(st.pairs.p, pairArray + first, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, st.stream));
+            if (u.rhi > u.rlo) CK(cudaMemcpyAsync(st.ref.p, seqBufRef + u.rlo, (size_t)(u.rhi - u.rlo), cudaMemcpyHostToDevice, st.stream));
+            if (u.qhi > u.qlo) CK(cudaMemcpyAsync(st.qer.p, seqBufQer + u.qlo, (size_t)(u.qhi - u.qlo), cudaMemcpyHostToDevice, st.stream));
+            CK(cudaEventRecord(st.dev_done, st.stream));          /* "uploaded" */
+            kk.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (u.rhi - u.rlo) + (u.qhi - u.qlo);
+        };
+        if (!mine.empty()) upload(0, false);
+        for (int m = 0; m < (int)mine.size(); ++m) {
+            if (m + 1 < (int)mine.size()) upload(m + 1, false);
+            Slot &st = xx.slot[1 + (m & 1)];
+            const int first = cstart[mine[m]], cnt = cstart[mine[m] + 1] - first;
+            for (int attempt = 0; ; ++attempt) {
+                const Up &u = up[m & 1];
+                CK(cudaStreamWaitEvent(cs.stream, st.dev_done, 0));
+                if (dev_align2_core(kk, rt, xx, cs, (bsw_seqpair_t *)st.pairs.p, (const uint8_t *)st.ref.p - u.rlo, (const uint8_t *)st.qer.p - u.qlo,
+                                    (bsw_kswr_t *)st.aln.p, cnt, is8, cs.stream, u.rlo, u.rhi, u.qlo, u.qhi)) break;
+                if (attempt) die("a pair names bases outside its sequence buffer");
+                CK(cudaStreamSynchronize(cs.stream));
+                upload(m, true);                   /* the sampled ranges missed a pair: exact scan */
+            }
+            CK(cudaMemcpyAsync(aln + first, st.aln.p, (size_t)cnt * sizeof(bsw_kswr_t), cudaMemcpyDeviceToHost, cs.stream));
+            CK(cudaEventRecord(st.done, cs.stream));
+            st.busy = true;
+            kk.st.d2h_bytes += (int64_t)cnt * sizeof(bsw_kswr_t);
+        }
+        for (Slot &sl : xx.slot) slot_retire(xx, sl);
+        CK(cudaStreamSynchronize(cs.stream));
+    };
+    if (nworkers == 1) { run(k, x, 0); return; }
+    /* every helper gets its own view of the handle: own context, own counters */
+    std::vector<Core> kb((size_t)nworkers - 1, k);
+    std::vector<DevCtx *> xb((size_t)nworkers - 1, nullptr);
+    std::vector<std::thread> helpers;
+    for (int w = 1; w < nworkers; ++w) {
+        xb[w - 1] = ctx_acquire(rt);
+        kb[w - 1].ctx[0] = xb[w - 1];
+        memset(&kb[w - 1].st, 0, sizeof(bsw_stats_t));
+    }
+    for (int w = 1; w < nworkers; ++w) helpers.emplace_back([&, w] { run(kb[w - 1], *xb[w - 1], w); });
+    run(k, x, 0);
+    for (std::thread &t : helpers) t.join();
+    CK(cudaSetDevice(x.dev));
+    unsigned long long ca = 0;
+    CK(cudaMemcpy(&ca, x.cells.p, sizeof ca, cudaMemcpyDeviceToHost));
+    for (int w = 1; w < nworkers; ++w) {
+        const bsw_stats_t &b = kb[w - 1].st;
+        k.st.pairs += b.pairs; k.st.pairs_packed += b.pairs_packed; k.st.pairs_general += b.pairs_general; k.st.pairs_wide += b.pairs_wide;
+        k.st.kernel_launches += b.kernel_launches; k.st.h2d_bytes += b.h2d_bytes; k.st.d2h_bytes += b.d2h_bytes; k.st.kernel_ms += b.kernel_ms;
+        unsigned long long cb = 0;                 /* the helper context's cell counter joins the handle's */
+        CK(cudaMemcpy(&cb, xb[w - 1]->cells.p, sizeof cb, cudaMemcpyDeviceToHost));
+        ca += cb;
+        ctx_release(rt, xb[w - 1]);
+    }
+    CK(cudaMemcpy(x.cells.p, &ca, sizeof ca, cudaMemcpyHostToDevice));
 }
 
 /* ---- CIGAR generation ------------------------------------------------------ */

@@ -211,6 +211,14 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
 void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                      const uint8_t *d_seqBufQer, bsw_kswr_t *d_aln, int32_t numPairs, int is8, void *stream);
 
+/* The same on HOST buffers, synchronous: one call instead of mem_sam_pe_batch's getScores8/16(phase 0), the host loop
+ * that builds the reversed prefixes, and getScores8/16(phase 1) (bwa-mem2 src/bwamem_pair.cpp).
+ * aln[i] receives the complete kswr_t of pairArray[i] (score, te, qe, score2, te2, tb, qb; tb = qb = -1 where ksw_align2
+ * runs no second pass).  Records and bases cross PCIe once, no reversed copy is built on the host.  is8: the
+ * getScores8 (1) or getScores16 (0) arithmetic.  Uses the handle's first device. */
+void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
+                 bsw_kswr_t *aln, int32_t numPairs, int is8);
+
 /* ---- CIGAR generation ------------------------------------------------------------
  * Batched bwa ksw.c ksw_global2 (bwa-mem2 src/ksw.cpp), the banded global alignment with backtrack that mem_reg2aln
  * reaches through bwa_gen_cigar2 once per reported alignment: one job per alignment, scoring from the handle

@@ -372,6 +372,36 @@ def test_guard_bands_untouched(ora, bsw):
     h.close()
 
 
+def test_kswv_align2_host(ora, bsw):
+    """kswv_align2: ksw_align2 on host buffers in one call (records and bases up once, hand-off and both passes on the device)
+    equals the CPU restatement per pair -- several chunks (ramped), 8- and 16-bit, N, hits below minsc, 16-bit shapes, the
+    32-bit kernel, a batch with no second pass, an empty batch; inputs untouched."""
+    import os
+    prm = ora.make_params()
+    os.environ["BSW_CUDA_KSWV_CHUNK"] = "8192"
+    try:
+        ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+        cases = []
+        P, r, q = ora.gen_kswv(60000); cases.append((P, r, q, 1))
+        P, r, q = ora.gen_kswv(3000, qlen=250, tmin=400, tmax=700, seed=0xC5); cases.append((P, r, q, 0))
+        P, r, q = ora.gen_random(3000, 0, 120, 0, 250, sim=0.75, p_n=0.03, seed=31)
+        P["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | ora.KSW_XBYTE | 30; cases.append((P, r, q, 1))
+        P, r, q = ora.gen_kswv(2000, qlen=300, tmin=400, tmax=700, seed=12, p_n=0.001); cases.append((P, r, q, 0))
+        P, r, q = ora.gen_kswv(200, qlen=600, tmin=700, tmax=900, seed=10, xtra=ora.KSW_XSUBO | ora.KSW_XSTART | 19); cases.append((P, r, q, 0))
+        P, r, q = ora.gen_kswv(500, seed=77, xtra=ora.KSW_XSUBO | ora.KSW_XBYTE | 19); cases.append((P, r, q, 1))       # no KSW_XSTART
+        for P, r, q, is8 in cases:
+            P0 = P.copy()
+            ao, _ = ora.kswv_align2_batch(P, r, q, prm, 8)
+            ag = np.zeros(len(P), bsw.KSWR)
+            ks.align2(P, r, q, ag, len(P), is8)
+            assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
+            assert (P == P0).all()
+        ks.align2(P, r, q, ag, 0, 1)
+        ks.close()
+    finally:
+        os.environ.pop("BSW_CUDA_KSWV_CHUNK")
+
+
 def test_kswv_edge(ora, ks, bsw):
     prm = ora.make_params()
     P, r, q = ora.gen_random(2000, 0, 60, 0, 150, sim=0.7, p_n=0.05, seed=3)
