@@ -613,11 +613,17 @@ def run_kswv(args):
     dK16, dkr16, dkq16, dp16, dr16, dq16 = dv(K16), dv(kr16), dv(kq16), dv(p16), dv(r16), dv(q16)
     da = torch.zeros(n * 28, dtype=torch.uint8, device="cuda"); db = torch.zeros(n16 * 28, dtype=torch.uint8, device="cuda")
 
+    s16 = c.side[0].cuda_stream if len(c.side) > 1 else c.stream      # the 16-bit slice on its own caller stream: the tiers are independent
+
     def step_resident():
         ks.dev_getScores(dK, dkr, dkq, da, n, 1, 0, c.stream)
+        ks.dev_getScores(dK16, dkr16, dkq16, db, n16, 0, 0, s16)
         ks.dev_getScores(dp1, dr1, dq1, da, len(p1), 1, 1, c.stream)
-        ks.dev_getScores(dK16, dkr16, dkq16, db, n16, 0, 0, c.stream)
-        ks.dev_getScores(dp16, dr16, dq16, db, len(p16), 0, 1, c.stream)
+        ks.dev_getScores(dp16, dr16, dq16, db, len(p16), 0, 1, s16)
+
+    def join_side():
+        if len(c.side) > 1:
+            torch.cuda.current_stream().wait_stream(c.side[0])
 
     ks.reset_stats(); step_resident(); torch.cuda.synchronize()
     if ks.stats()["cells"] != cells_step:
@@ -634,7 +640,7 @@ def run_kswv(args):
                                   f"(scalar C, exact arithmetic, pthreads x{c.cores}); `--impl reference --workload kswv_c4` runs the whole config"}
     sampler = ClockSampler(c.local_rank); sampler.start()
     ks.reset_stats()
-    ms_total = time_resident(c, args, step_resident)
+    ms_total = time_resident(c, args, step_resident, join_side)
     launches = ks.stats()["kernel_launches"]
     ks.set_timing(True)
     kms = []

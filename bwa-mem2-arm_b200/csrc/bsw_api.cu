@@ -1205,7 +1205,7 @@ void bsw_getScoresRef(bsw_t *h, bsw_seqpair_t *pairArray, const bsw_ref_t *ref, 
  * Calls on one stream stay ordered by that stream.  A slot is reused only after the call that last used it has finished (stream-side wait). */
 static Slot &dev_slot(DevCtx &x, cudaStream_t s, bool rotate)
 {
-    /* kswv keeps to one slot: its row-maxima scratch is large, and a slot's buffers grow on first use */
+    /* rotate = false pins a caller to slot 0 (kswv_dev_align2: its hand-off scratch grows on first use) */
     Slot &sl = x.slot[rotate ? x.dev_rr : 0];
     if (rotate) x.dev_rr = (x.dev_rr + 1) % BSW_NSLOT;
     if (sl.dev_used) CK(cudaStreamWaitEvent(s, sl.dev_done, 0));
@@ -1314,7 +1314,7 @@ void kswv_dev_getScores(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8
     DevCtx &x = h->k.cx(0);
     CK(cudaSetDevice(x.dev));
     h->k.st.calls++;
-    Slot &sl = dev_slot(x, (cudaStream_t)stream, false);
+    Slot &sl = dev_slot(x, (cudaStream_t)stream, true);
     launch_kswv(h->k, h->k.rt(0), x, sl, const_cast<bsw_seqpair_t *>(d_pairArray), d_seqBufRef, d_seqBufQer, d_aln, numPairs, is8, phase,
                 (cudaStream_t)stream);
     CK(cudaEventRecord(sl.dev_done, (cudaStream_t)stream));
