@@ -89,6 +89,8 @@ def lib():
         L.ora_kswv_batch.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int, C.c_int, C.c_int, vp]
         L.ora_ksw_align2.restype = None
         L.ora_ksw_align2.argtypes = [C.c_int, vp, C.c_int, vp, C.POINTER(Params), C.c_int, vp, vp]
+        L.ora_kswv_batch_avx2.restype = C.c_int64
+        L.ora_kswv_batch_avx2.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int, C.c_int, C.c_int, vp]
         L.ora_kswv_batch_striped.restype = None
         L.ora_kswv_batch_striped.argtypes = [vp, vp, vp, vp, C.c_int32, C.POINTER(Params), C.c_int]
         L.ora_ksw_global2.restype = C.c_int
@@ -133,6 +135,15 @@ def kswv_batch(pairs, ref, qer, aln, params, is8, phase, nthreads=1, want_cells=
     cells = np.zeros(len(pairs), dtype=np.int64) if want_cells else None
     tot = lib().ora_kswv_batch(_p(pairs), _p(ref), _p(qer), _p(aln), len(pairs), C.byref(params),
                                int(is8), int(phase), nthreads, _p(cells))
+    return (tot, cells) if want_cells else tot
+
+
+def kswv_batch_avx2(pairs, ref, qer, aln, params, is8, phase, nthreads=1, want_cells=False):
+    """The inter-sequence AVX2 port (oracle/kswv_avx2.c): same contract and results as kswv_batch."""
+    assert pairs.dtype == SEQPAIR and aln.dtype == KSWR
+    cells = np.zeros(len(pairs), dtype=np.int64) if want_cells else None
+    tot = lib().ora_kswv_batch_avx2(_p(pairs), _p(ref), _p(qer), _p(aln), len(pairs), C.byref(params),
+                                    int(is8), int(phase), nthreads, _p(cells))
     return (tot, cells) if want_cells else tot
 
 
@@ -309,8 +320,10 @@ def protocol_side(pairs, ref, qer, params, w=100, tries=2, nthreads=8, runner=No
     return out, submitted, cells
 
 
-def kswv_align2_batch(pairs, ref, qer, params, nthreads=8):
-    """mem_sam_pe_batch's sequence on the oracle: phase 0 by precision, hand-off, phase 1.  Returns (aln, cells)."""
+def kswv_align2_batch(pairs, ref, qer, params, nthreads=8, simd=False):
+    """mem_sam_pe_batch's sequence on the oracle: phase 0 by precision, hand-off, phase 1.  Returns (aln, cells).
+    simd: the passes on the inter-sequence AVX2 port (identical results)."""
+    kswv_batch = kswv_batch_avx2 if simd else globals()["kswv_batch"]
     aln = np.zeros(len(pairs), KSWR)
     is8 = (pairs["h0"] & KSW_XBYTE) != 0
     cells = 0

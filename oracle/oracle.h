@@ -86,6 +86,12 @@ int64_t ora_kswv_batch(const ora_seqpair_t *pairs, const uint8_t *ref, const uin
                        ora_kswr_t *aln, int32_t n, const ora_bsw_params_t *p, int is8,
                        int phase, int nthreads, int64_t *cells_out);
 
+/* inter-sequence AVX2 port of the same (oracle/kswv_avx2.c: 16 pairs in the 16-bit lanes of a register, pairs sorted
+ * by length).  Identical results and cell counts; the CPU baseline of the kswv bench. */
+int64_t ora_kswv_batch_avx2(const ora_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
+                            ora_kswr_t *aln, int32_t n, const ora_bsw_params_t *p, int is8,
+                            int phase, int nthreads, int64_t *cells_out);
+
 /* whole ksw_align2 for one pair (forward, hand-off rule, reverse), used by
  * tests to replay the caller protocol. */
 void ora_ksw_align2(int qlen, const uint8_t *query, int tlen, const uint8_t *target,
