@@ -1388,18 +1388,19 @@ void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBu
     const int n = numPairs;
     if (n <= 0) return;
     if (!pairArray || !seqBufRef || !seqBufQer || !aln) die("null buffer passed to kswv_align2");
-    DevCtx &x = k.cx(0);
-    DevRt &rt = k.rt(0);
-    CK(cudaSetDevice(x.dev));
-    for (Slot &sl : x.slot) slot_retire(x, sl);
+    const int nd = (int)k.devs.size();
+    for (int i = 0; i < nd; ++i) { DevCtx &xi = k.cx(i); CK(cudaSetDevice(xi.dev)); for (Slot &sl : xi.slot) slot_retire(xi, sl); }
     const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
-    const std::vector<int> cstart = chunk_starts(n, chunk, 1, k.chunk_ramp);
+    const std::vector<int> cstart = chunk_starts(n, chunk, nd, k.chunk_ramp);
     const int nchunks = (int)cstart.size() - 1;
     /* A chunk's three phases each end in a small read-back the host waits for (two plans, the hand-off sizes), and the
-     * device drains meanwhile.  Two workers -- the calling thread and one helper on a second context from the pool --
-     * take alternate chunks, so one chunk's kernels fill the other's gaps (BSW_CUDA_ALIGN2_WORKERS=1: one). */
-    const int nworkers = nchunks >= 4 ? std::max(1, std::min(std::min(4, nchunks / 2), env_int("BSW_CUDA_ALIGN2_WORKERS", 2))) : 1;
+     * device drains meanwhile.  Two workers per device -- the calling thread and helpers, each on a context of its own --
+     * take the chunks in turn, so one chunk's kernels fill the other's gaps; worker w serves device w mod (number of
+     * devices of the handle) (BSW_CUDA_ALIGN2_WORKERS = workers per device, default 2). */
+    const int per_dev = std::max(1, std::min(4, env_int("BSW_CUDA_ALIGN2_WORKERS", 2)));
+    const int nworkers = std::max(1, std::min(nd * per_dev, nchunks >= 4 ? nchunks / 2 : 1));
     auto run = [&](Core &kk, DevCtx &xx, int worker) {
+        DevRt &rt = k.rt(worker % nd);
         CK(cudaSetDevice(xx.dev));
         Slot &cs = xx.slot[0];                     /* scratch (plan, sort, hand-off) and the compute stream */
         struct Up { long long rlo, rhi, qlo, qhi; } up[2];
@@ -1443,32 +1444,40 @@ void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBu
         for (Slot &sl : xx.slot) slot_retire(xx, sl);
         CK(cudaStreamSynchronize(cs.stream));
     };
-    if (nworkers == 1) { run(k, x, 0); return; }
-    /* every helper gets its own view of the handle: own context, own counters */
+    DevCtx &x0 = k.cx(0);
+    if (nworkers == 1) { run(k, x0, 0); return; }
+    /* every helper gets its own view of the handle (own counters) and its own context: the handle's context of its device
+     * for the first worker of a device, one from the pool for the others */
     std::vector<Core> kb((size_t)nworkers - 1, k);
     std::vector<DevCtx *> xb((size_t)nworkers - 1, nullptr);
+    std::vector<char> pooled((size_t)nworkers - 1, 0);
     std::vector<std::thread> helpers;
     for (int w = 1; w < nworkers; ++w) {
-        xb[w - 1] = ctx_acquire(rt);
+        const int di = w % nd;
+        if (w < nd) xb[w - 1] = &k.cx(di);
+        else { xb[w - 1] = ctx_acquire(k.rt(di)); pooled[w - 1] = 1; }
         kb[w - 1].ctx[0] = xb[w - 1];
         memset(&kb[w - 1].st, 0, sizeof(bsw_stats_t));
     }
     for (int w = 1; w < nworkers; ++w) helpers.emplace_back([&, w] { run(kb[w - 1], *xb[w - 1], w); });
-    run(k, x, 0);
+    run(k, x0, 0);
     for (std::thread &t : helpers) t.join();
-    CK(cudaSetDevice(x.dev));
-    unsigned long long ca = 0;
-    CK(cudaMemcpy(&ca, x.cells.p, sizeof ca, cudaMemcpyDeviceToHost));
     for (int w = 1; w < nworkers; ++w) {
         const bsw_stats_t &b = kb[w - 1].st;
         k.st.pairs += b.pairs; k.st.pairs_packed += b.pairs_packed; k.st.pairs_general += b.pairs_general; k.st.pairs_wide += b.pairs_wide;
         k.st.kernel_launches += b.kernel_launches; k.st.h2d_bytes += b.h2d_bytes; k.st.d2h_bytes += b.d2h_bytes; k.st.kernel_ms += b.kernel_ms;
-        unsigned long long cb = 0;                 /* the helper context's cell counter joins the handle's */
+        if (!pooled[w - 1]) continue;
+        /* a pooled context's cell counter joins the handle's context on the same device */
+        DevCtx &home = k.cx(w % nd);
+        CK(cudaSetDevice(home.dev));
+        unsigned long long ca = 0, cb = 0;
+        CK(cudaMemcpy(&ca, home.cells.p, sizeof ca, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(&cb, xb[w - 1]->cells.p, sizeof cb, cudaMemcpyDeviceToHost));
         ca += cb;
-        ctx_release(rt, xb[w - 1]);
+        CK(cudaMemcpy(home.cells.p, &ca, sizeof ca, cudaMemcpyHostToDevice));
+        ctx_release(k.rt(w % nd), xb[w - 1]);
     }
-    CK(cudaMemcpy(x.cells.p, &ca, sizeof ca, cudaMemcpyHostToDevice));
+    CK(cudaSetDevice(x0.dev));
 }
 
 /* ---- CIGAR generation ------------------------------------------------------ */

@@ -215,7 +215,7 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
  * that builds the reversed prefixes, and getScores8/16(phase 1) (bwa-mem2 src/bwamem_pair.cpp).
  * aln[i] receives the complete kswr_t of pairArray[i] (score, te, qe, score2, te2, tb, qb; tb = qb = -1 where ksw_align2
  * runs no second pass).  Records and bases cross PCIe once, no reversed copy is built on the host.  is8: the
- * getScores8 (1) or getScores16 (0) arithmetic.  Uses the handle's first device. */
+ * getScores8 (1) or getScores16 (0) arithmetic.  Chunks go round-robin to the handle's devices. */
 void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
                  bsw_kswr_t *aln, int32_t numPairs, int is8);
 

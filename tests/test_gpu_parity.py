@@ -927,3 +927,18 @@ def test_multi_device_handle(ora, bsw, monkeypatch):
         _assert_same(o[k::8], out[k])
     used = sum(1 for dv in range(nd) if bsw.engine_stats(dv)["batches"] > 0)
     assert used >= 2
+    # kswv on every device of the handle: the two boundary calls and the one-call ksw_align2
+    monkeypatch.setenv("BSW_CUDA_KSWV_CHUNK", "4096")
+    prm = ora.make_params()
+    P, r, q = ora.gen_kswv(40000, seed=0x2E)
+    ao, _ = ora.kswv_align2_batch(P, r, q, prm, 8)
+    ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    ks.set_direct_min(0)
+    ag = np.zeros(len(P), bsw.KSWR)
+    ks.align2(P, r, q, ag, len(P), 1)
+    assert (ao == ag).all()
+    a0 = np.zeros(len(P), ora.KSWR); ora.kswv_batch(P, r, q, a0, prm, 1, 0, 8)
+    ag[...] = 0
+    ks.getScores8(P, r, q, ag, len(P), 1, 0)
+    assert (a0 == ag).all()
+    ks.close()
