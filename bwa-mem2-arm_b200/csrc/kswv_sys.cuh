@@ -121,8 +121,9 @@ BSW_HD void kswv_sys_lane(const Const &c, int is8, const PairIn &A, const PairIn
 
     const uint32_t MISW = ((uint32_t)(-c.b) & 0xffu) * 0x01010101u, AMBW = lut_hi(c), XW = ((uint32_t)c.a ^ (uint32_t)(-c.b)) & 0xffu;
     const uint32_t LUTLO = launder(lut_lo(c)), LUTHI = launder(AMBW);
-    const uint32_t NOD = pack2(-c.oe_del, -c.oe_del), NOI = pack2(-c.oe_ins, -c.oe_ins);
-    const uint32_t NED = pack2(-c.e_del, -c.e_del), NEI = pack2(-c.e_ins, -c.e_ins);
+    /* kept in registers: left to itself ptxas rebuilds these four from the kernel arguments in every step (nine instructions) */
+    const uint32_t NOD = launder(pack2(-c.oe_del, -c.oe_del)), NOI = launder(pack2(-c.oe_ins, -c.oe_ins));
+    const uint32_t NED = launder(pack2(-c.e_del, -c.e_del)), NEI = launder(pack2(-c.e_ins, -c.e_ins));
     const uint32_t KOFF = (uint32_t)(gl * C) * 0x00010001u;
     /* h * 256 + column as an IMAD (the FMA pipe idles, the ALU pipe is the bound): the multiplier must be a value ptxas
      * cannot fold, or it emits an ALU-pipe LEA */
