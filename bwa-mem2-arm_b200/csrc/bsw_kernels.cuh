@@ -531,9 +531,9 @@ static inline void launch_kswv_sysw(int cfg, bool sym, int first, int count, int
     else launch_kswv_sys_shape<G, CC, false, true, true>(first, count, max_rows, io, ref, qer, aln, sorted, c, is8, phase, cells, s)
     switch (cfg) {
     case 0: KSWV_SYSW_LAUNCH(8, 8); break;   case 1: KSWV_SYSW_LAUNCH(8, 16); break;
-    case 2: KSWV_SYSW_LAUNCH(8, 24); break;  case 3: KSWV_SYSW_LAUNCH(8, 32); break;
-    case 4: KSWV_SYSW_LAUNCH(16, 20); break; case 5: KSWV_SYSW_LAUNCH(16, 24); break;
-    case 6: KSWV_SYSW_LAUNCH(16, 28); break; default: KSWV_SYSW_LAUNCH(16, 32); break;
+    case 2: KSWV_SYSW_LAUNCH(8, 20); break;  case 3: KSWV_SYSW_LAUNCH(8, 24); break;
+    case 4: KSWV_SYSW_LAUNCH(8, 32); break;  case 5: KSWV_SYSW_LAUNCH(16, 20); break;
+    case 6: KSWV_SYSW_LAUNCH(16, 26); break; default: KSWV_SYSW_LAUNCH(16, 32); break;
     }
 #undef KSWV_SYSW_LAUNCH
 }

@@ -48,11 +48,14 @@ BSW_HD bool kswv_sys_eligible(const Const &c, int len1, int len2)
     return kswv_packed_eligible(c, len1, len2) && len1 <= KSWV_SYS_MAX_ROWS && c.a <= 120 && c.b <= 120 && c.ambig <= 0;
 }
 /* The 16-bit tier (template flag W): scores < 2048, queries of up to 512 bases -- what kswv::getScores16 is for (reads
- * longer than 255 bp, match scores > 1).  Eight shapes by query length: 8 lanes x 8 / 16 / 24 / 32 columns, then
- * 16 lanes x 20 / 24 / 28 / 32 columns.  The 8-bit entry point keeps ksw_u8's saturation rule and is not admitted. */
+ * longer than 255 bp, match scores > 1).  Eight shapes by query length: 8 lanes x 8 / 16 / 20 / 24 / 32 columns, then
+ * 16 lanes x 20 / 26 / 32 columns.  The 8-bit entry point keeps ksw_u8's saturation rule and is not admitted. */
 #define KSWV_SYSW_NCFG 8
 #define KSWV_SYSW_MAX_SCORE 2047
-BSW_HD int kswv_sysw_cols(int cfg) { return cfg < 4 ? 64 * (cfg + 1) : 320 + 64 * (cfg - 4); }
+BSW_HD int kswv_sysw_cols(int cfg)
+{   /* spaced for the usual read lengths: 150 -> 160, 250 -> 256, 300 -> 320 */
+    return cfg == 0 ? 64 : cfg == 1 ? 128 : cfg == 2 ? 160 : cfg == 3 ? 192 : cfg == 4 ? 256 : cfg == 5 ? 320 : cfg == 6 ? 416 : 512;
+}
 BSW_HD int kswv_sysw_cfg_for(int len2)
 {
     for (int k = 0; k < KSWV_SYSW_NCFG; ++k) if (len2 <= kswv_sysw_cols(k)) return k;

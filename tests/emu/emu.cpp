@@ -197,8 +197,8 @@ static void sysw_warp(int cfg, const Const &c, int is8, const bsw_seqpair_t *pai
 #define SYSW(G, CC) if (sym) sys_warp<G, CC, true, true, true>(c, is8, pairs, ids, cnt, ref, qer, res); \
                     else sys_warp<G, CC, false, true, true>(c, is8, pairs, ids, cnt, ref, qer, res)
     switch (cfg) {
-    case 0: SYSW(8, 8); break;   case 1: SYSW(8, 16); break;  case 2: SYSW(8, 24); break;  case 3: SYSW(8, 32); break;
-    case 4: SYSW(16, 20); break; case 5: SYSW(16, 24); break; case 6: SYSW(16, 28); break; default: SYSW(16, 32); break;
+    case 0: SYSW(8, 8); break;   case 1: SYSW(8, 16); break;  case 2: SYSW(8, 20); break;  case 3: SYSW(8, 24); break;
+    case 4: SYSW(8, 32); break;  case 5: SYSW(16, 20); break; case 6: SYSW(16, 26); break; default: SYSW(16, 32); break;
     }
 #undef SYSW
 }
@@ -269,7 +269,7 @@ int emu_kswv(const bsw_seqpair_t *pairs, const uint8_t *ref, const uint8_t *qer,
             }
         for (int cfg = 0; cfg < KSWV_SYSW_NCFG; ++cfg) {
             const std::vector<int> &v = byw[cfg];
-            const int per = cfg < 4 ? 8 : 4;
+            const int per = cfg < 5 ? 8 : 4;
             for (size_t f = 0; f < v.size(); f += per) {
                 const int cnt = (int)std::min<size_t>(per, v.size() - f);
                 KswOut res[8];

@@ -13,14 +13,14 @@ for tag, n, kw, a in (("2x300bp", 200000, dict(qlen=300, tmin=400, tmax=700), 1)
     ks = bswb200.kswv(6, 1, 6, 1, a, 4, 1, 2048, 256)
     dk = torch.from_numpy(K.view(np.uint8).copy()).cuda(); dr = torch.from_numpy(kr).cuda(); dq = torch.from_numpy(kq).cuda()
     da = torch.zeros(n * 28, dtype=torch.uint8, device="cuda")
-    for _ in range(2): ks.dev_getScores(dk, dr, dq, da, n, 0, 0, st)
+    for _ in range(6): ks.dev_getScores(dk, dr, dq, da, n, 0, 0, st)       # every slot of the context has grown its buffers
     torch.cuda.synchronize(); ks.reset_stats()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(3): ks.dev_getScores(dk, dr, dq, da, n, 0, 0, st)
+    for _ in range(6): ks.dev_getScores(dk, dr, dq, da, n, 0, 0, st)
     e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 3; s = ks.stats()
+    ms = e0.elapsed_time(e1) / 6; s = ks.stats()
     ok = int((da.cpu().numpy().view(bswb200.KSWR) != ao).sum())
     print(json.dumps({"workload": tag, "pairs": n, "ms": ms, "gcups": cells / ms / 1e6, "frac_of_dpx_peak": cells / ms / 1e6 / peak, "mismatches": ok,
-                      "max_score": int(ao["score"].max()), "pairs_packed": s["pairs_packed"] // 3, "pairs_wide": s["pairs_wide"] // 3, "pairs_general": s["pairs_general"] // 3}), flush=True)
+                      "max_score": int(ao["score"].max()), "pairs_packed": s["pairs_packed"] // 6, "pairs_wide": s["pairs_wide"] // 6, "pairs_general": s["pairs_general"] // 6}), flush=True)
     ks.close()
