@@ -1,7 +1,8 @@
 #!/bin/bash
 # AddressSanitizer over the kernels' per-thread code: builds tests/emu (the __host__ __device__ cores compiled for the host)
 # with -fsanitize=address and runs the CPU kernel-logic suite on it.  compute-sanitizer is closed on the GPU pool; this
-# covers the row arrays, the register-array indexing and the scratch layouts of every core.  ~10 minutes.
+# covers the row arrays, the register-array indexing and the scratch layouts of every core.  ~40 minutes (the emulated warps
+# switch contexts at every shuffle).
 set -e
 cd "$(dirname "$0")/.."
 ASAN=$(g++ -print-file-name=libasan.so)
