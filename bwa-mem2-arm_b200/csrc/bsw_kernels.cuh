@@ -51,6 +51,7 @@ struct Plan {
 };
 
 enum { MODE_BSW = 0, MODE_KSWV = 1 };
+static_assert(KSWV_SYSW_NCFG <= BSW_WIDE_NCFG, "the 16-bit kswv shapes share Plan::hist_w and the CLS_WIDE0 classes with the BSW lanes-per-pair configurations");
 
 /* ------------------------------------------------------------------ 1. prep */
 /* does the query hold a base > 3?  Aligned word reads; stays inside the words that hold the query's bytes */
