@@ -21,6 +21,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <string.h>
+#include <stdlib.h>
 #include "../../include/bsw_cuda.h"
 #include "bsw_core.cuh"
 #include "bsw_core2.cuh"
@@ -468,8 +469,13 @@ static inline void launch_kswv_sys_shape(int first, int count, int max_rows, Pai
  * without N -- in ONE such launch (qn: the general score table for everybody).  Symmetric gap sums only. */
 static inline int kswv_sys_lanes_for(int pairs)
 {
-    /* the device holds ~2400 warps of this kernel: more lanes per group while the batch stays within one wave */
-    return pairs <= 4096 ? 32 : pairs <= 8192 ? 16 : 8;
+    /* the device holds ~2400 warps of this kernel: more lanes per group while the batch stays within a wave or two.
+     * Measured (tools/kswv_lanes_sweep.sh, device flight of one call of 150 x 300-500 bp pairs, 8 / 16 / 32 lanes): 1000 pairs
+     * 514 / 207 / 147 us, 2452: 610 / 364 / 344, 5000: 697 / 355 / 483, 10000: 851 / 635 / 707
+     * (BSW_CUDA_KSWV_L32 / BSW_CUDA_KSWV_L16: the largest batch on 32 / 16 lanes) */
+    static const int l32 = getenv("BSW_CUDA_KSWV_L32") ? atoi(getenv("BSW_CUDA_KSWV_L32")) : 4096;
+    static const int l16 = getenv("BSW_CUDA_KSWV_L16") ? atoi(getenv("BSW_CUDA_KSWV_L16")) : 20000;
+    return pairs <= l32 ? 32 : pairs <= l16 ? 16 : 8;
 }
 
 static inline void launch_kswv_sys(int max_len2, bool sym, bool qn, int lanes, int first, int count, int max_rows, PairIO io, const uint8_t *ref,
