@@ -426,6 +426,20 @@ def test_kswv_edge(ora, ks, bsw):
     assert ks.stats()["pairs_general"] > 0
 
 
+def test_kswv_long_targets(ora, ks, bsw):
+    """Targets around and beyond the registers kernel's row limit (2046: it sizes the `b` lists in shared memory): the
+    longer ones take the 32-bit kernel, results equal either way."""
+    prm = ora.make_params()
+    P, r, q = ora.gen_kswv(600, qlen=100, tmin=2030, tmax=2070, seed=0xD9)
+    ao = np.zeros(len(P), ora.KSWR); ag = np.zeros(len(P), bsw.KSWR)
+    ora.kswv_batch(P, r, q, ao, prm, 1, 0, 8)
+    ks.reset_stats()
+    ks.getScores8(P, r, q, ag, len(P), 1, 0)
+    assert (ao == ag).all(), np.nonzero(ao != ag)[0][:5]
+    st = ks.stats()
+    assert st["pairs_general"] == int((P["len1"] > 2046).sum()) and 0 < st["pairs_general"] < len(P)
+
+
 def test_kswv_16bit_tier(ora, ks, bsw):
     """kswv::getScores16 proper: scores above 255 and queries above 255 bases stay on the registers kernel (its 16-bit
     shapes, kswv_sys.cuh W) -- nothing below 2048 / 512 bases may reach the 32-bit kernel.  2 x 300 bp and 2 x 500 bp mates,
