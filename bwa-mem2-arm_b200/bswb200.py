@@ -27,7 +27,7 @@ KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "kswv_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_getScores_static", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "kswv_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -84,6 +84,8 @@ def lib():
         f.argtypes = [vp, vp, vp, vp, vp, i32, C.c_uint16, C.c_int]
     L.bsw_dev_getScores.restype = None
     L.bsw_dev_getScores.argtypes = [vp, vp, vp, vp, i32, i32, vp]
+    L.bsw_dev_getScores_static.restype = C.c_int
+    L.bsw_dev_getScores_static.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp]
     L.bsw_dev_extendChained.restype = None
     L.bsw_dev_extendChained.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, vp]
     L.kswv_dev_getScores.restype = None
@@ -186,6 +188,12 @@ class BandedPairWiseSW:
     def dev_getScores(self, d_pairs, d_ref, d_qer, numPairs, w=100, stream=0):
         """Device-resident variant: arguments are device pointers / CUDA tensors."""
         self._L.bsw_dev_getScores(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), numPairs, w, C.c_void_p(stream))
+
+    def dev_getScores_static(self, d_pairs, d_ref, d_qer, numPairs, maxQueryLen, w=100, stream=0):
+        """bsw_dev_getScores_static: the same on the library's static device scratch, no allocation; returns the
+        C entry point's code (0 = done, -2 = beyond BSW_STATIC_MAX_ENTRIES, ...)."""
+        return int(self._L.bsw_dev_getScores_static(self._h, _ptr(d_pairs), _ptr(d_ref), _ptr(d_qer), numPairs, maxQueryLen, w,
+                                                    C.c_void_p(stream)))
 
     def dev_extendChained(self, d_left, d_lref, d_lqer, numLeft, d_right, d_rref, d_rqer, numRight, w=100, maxBandTry=2,
                           stream=0):

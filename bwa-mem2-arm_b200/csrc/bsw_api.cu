@@ -1706,3 +1706,86 @@ double bsw_measure_dpx_peak(int device, int which)
 }
 
 } /* extern "C" */
+
+/* ------------------------------------------------------------------ bsw_dev_getScores_static
+ * The allocation-free variant of bsw_dev_getScores (include/bsw_cuda.h; no reference counterpart).
+ * The general kernel's DP rows live in the file-scope array below instead of Slot::scratch.
+ * bsw_static_scratch is a HOST-side stand-in in host code, not a device address: the pointer the kernel gets comes from
+ * cudaGetSymbolAddress, once per device, with that device current. */
+static __device__ __align__(256) unsigned char bsw_static_scratch[BSW_STATIC_SCRATCH_BYTES];
+/* layout: [0, 4) status word = pairs refused by the kernel (cleared by every call); [256, ...) int2 rows, entry j of
+ * pair g at (j * numPairs + g) -- the layout of bsw_general_kernel */
+
+namespace {
+
+__global__ void __launch_bounds__(64)
+bsw_static_kernel(bsw_seqpair_t *__restrict__ pairs, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ qer,
+                  int n, int max_qlen, Const c, int w, unsigned char *scratch)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const PairIO io = { (const char *)pairs, (char *)pairs + offsetof(bsw_seqpair_t, score), (int)sizeof(bsw_seqpair_t), (int)sizeof(bsw_seqpair_t) };
+    const PairIn P = load_pair(io, g);
+    PairOut o;
+    if (P.len1 < 0 || P.len2 < 0 || P.len2 > max_qlen) {
+        o.score = o.tle = o.gtle = o.qle = o.gscore = o.max_off = -1;
+        atomicAdd(reinterpret_cast<int *>(bsw_static_scratch), 1);      /* device code names the array directly */
+    } else {
+        bsw_general_thread<long long>(c, w, P, ref, qer, reinterpret_cast<int2 *>(scratch + 256) + g, (long long)n, o);
+    }
+    store_bsw(io, g, o);
+}
+
+struct StaticScratch { std::once_flag once; unsigned char *ptr = nullptr; cudaError_t err = cudaSuccess; };
+StaticScratch g_static_scratch[64];
+
+int static_fail(int code, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (e != cudaSuccess) fprintf(stderr, "[bsw-b200] bsw_dev_getScores_static: %s: %s (%s)\n", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    else fprintf(stderr, "[bsw-b200] bsw_dev_getScores_static: %s\n", what);
+    return code;
+}
+
+} /* namespace */
+
+extern "C" int bsw_dev_getScores_static(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer,
+                                        int32_t numPairs, int32_t maxQueryLen, int32_t w, void *stream)
+{
+    if (!h || numPairs < 0 || maxQueryLen < 0) return static_fail(-1, "invalid argument (null handle, negative numPairs or maxQueryLen)");
+    if (numPairs == 0) return 0;
+    if (!d_pairArray || !d_seqBufRef || !d_seqBufQer) return static_fail(-1, "invalid argument (null device pointer)");
+    const long long entries = (long long)numPairs * ((long long)maxQueryLen + 1);
+    if (entries > (long long)BSW_STATIC_MAX_ENTRIES) {
+        fprintf(stderr, "[bsw-b200] bsw_dev_getScores_static: numPairs * (maxQueryLen + 1) = %d * %d = %lld exceeds the static scratch of "
+                        "%d entries (BSW_STATIC_MAX_ENTRIES); split the batch or use bsw_dev_getScores\n",
+                numPairs, maxQueryLen + 1, entries, (int)BSW_STATIC_MAX_ENTRIES);
+        return -2;
+    }
+    const int dev = h->k.devs[0];
+    if (dev < 0 || dev >= 64) return static_fail(-1, "device index beyond the per-device table (64)");
+    cudaError_t e = cudaSetDevice(dev);
+    if (e != cudaSuccess) return static_fail(-3, "cudaSetDevice", e);
+    StaticScratch &ss = g_static_scratch[dev];
+    std::call_once(ss.once, [&ss]() {           /* set-up: once per device, that device current */
+        void *p = nullptr;
+        ss.err = cudaGetSymbolAddress(&p, bsw_static_scratch);
+        ss.ptr = (unsigned char *)p;
+    });
+    if (ss.err != cudaSuccess || !ss.ptr) return static_fail(-3, "cudaGetSymbolAddress(bsw_static_scratch)", ss.err);
+    cudaStream_t s = (cudaStream_t)stream;
+    e = cudaMemsetAsync(ss.ptr, 0, 256, s);      /* the status word must start at zero; the rows are rewritten by the kernel */
+    if (e != cudaSuccess) return static_fail(-3, "cudaMemsetAsync", e);
+    bsw_static_kernel<<<(numPairs + 63) / 64, 64, 0, s>>>(d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, maxQueryLen, h->k.c, w, ss.ptr);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return static_fail(-3, "kernel launch", e);
+    int refused = 0;
+    e = cudaMemcpyAsync(&refused, ss.ptr, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return static_fail(-3, "status read-back", e);
+    if (refused) {
+        fprintf(stderr, "[bsw-b200] bsw_dev_getScores_static: %d pair(s) with len2 > maxQueryLen = %d or a negative length (result words set to -1)\n",
+                refused, maxQueryLen);
+        return -4;
+    }
+    return 0;
+}

@@ -181,6 +181,29 @@ void kswv_getScores16(kswv_t *h, bsw_seqpair_t *pairArray, const uint8_t *seqBuf
 void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
                        const uint8_t *d_seqBufQer, int32_t numPairs, int32_t w, void *stream);
 
+/* bsw_dev_getScores without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same computation and in-place results as bsw_dev_getScores on resident buffers of the handle's first
+ * device, by the 32-bit kernel (one thread per pair) whose DP rows -- numPairs x (maxQueryLen + 1) x 8 bytes -- live in
+ * a file-scope `static __device__` array of BSW_STATIC_SCRATCH_BYTES instead of a grow-on-demand buffer: every GPU
+ * that loads the library holds those 8 MiB (+ 256 B) until the process exits.  The call makes no cudaMalloc / cudaFree
+ * / cudaHostAlloc and uses no allocating library routine; the only set-up is one cudaGetSymbolAddress per device, made
+ * by the first call on that device.
+ *   limit:   numPairs * (maxQueryLen + 1) <= BSW_STATIC_MAX_ENTRIES (e.g. 6898 pairs of 151-base reads, 4096 of <= 255);
+ *            maxQueryLen >= every pair's len2.  Larger requests are refused: nothing is launched, -2 is returned.
+ *   returns: 0 = done; -1 = invalid argument; -2 = beyond the static scratch; -3 = a CUDA call failed;
+ *            -4 = some pair has len2 > maxQueryLen or a negative length (those pairs get all six result words = -1,
+ *            the others their results).  Every failure also prints one line to stderr.
+ *   sharing: ALL calls on a device use the one array (the rows are rewritten from scratch by each call, the status word
+ *            in its header is cleared by each call), so calls that overlap on the GPU -- different streams, different
+ *            host threads or handles -- race.  Issue them on one stream, or order them yourself.
+ *   sync:    queued on `stream`; the host blocks for the 4-byte status word (like bsw_dev_getScores for its histogram),
+ *            so the results are complete when the call returns. */
+#define BSW_STATIC_MAX_ENTRIES   (1 << 20)
+#define BSW_STATIC_SCRATCH_BYTES (256 + 8 * (size_t)BSW_STATIC_MAX_ENTRIES)
+int bsw_dev_getScores_static(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
+                             const uint8_t *d_seqBufQer, int32_t numPairs, int32_t maxQueryLen, int32_t w, void *stream);
+
 /* Caller protocol of the extension step on resident pairs, one submission
  * (replaces the host loop around bswLeft/bswRight in
  * mem_chain2aln_across_reads_V2, bwamem.cpp ~L2200-2900, anchor BUG_REPORT.md:28):
