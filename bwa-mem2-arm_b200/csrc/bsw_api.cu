@@ -1778,6 +1778,10 @@ extern "C" int bsw_dev_getScores_static(bsw_t *h, bsw_seqpair_t *d_pairArray, co
     bsw_static_kernel<<<(numPairs + 63) / 64, 64, 0, s>>>(d_pairArray, d_seqBufRef, d_seqBufQer, numPairs, maxQueryLen, h->k.c, w, ss.ptr);
     e = cudaGetLastError();
     if (e != cudaSuccess) return static_fail(-3, "kernel launch", e);
+    /* a capturing stream cannot be waited for: the launch is recorded into the caller's graph and the status word stays
+     * on the device (pairs the kernel refuses carry -1 in their result words) */
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) return 0;
     int refused = 0;
     e = cudaMemcpyAsync(&refused, ss.ptr, sizeof(int), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);

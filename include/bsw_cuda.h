@@ -198,7 +198,9 @@ void bsw_dev_getScores(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_se
  *            in its header is cleared by each call), so calls that overlap on the GPU -- different streams, different
  *            host threads or handles -- race.  Issue them on one stream, or order them yourself.
  *   sync:    queued on `stream`; the host blocks for the 4-byte status word (like bsw_dev_getScores for its histogram),
- *            so the results are complete when the call returns. */
+ *            so the results are complete when the call returns.  On a stream that is being captured into a CUDA graph the
+ *            memset + kernel are recorded, nothing is waited for and 0 is returned (make one ordinary call on the device
+ *            first: the per-device set-up must not happen under capture); refused pairs then show only as -1 results. */
 #define BSW_STATIC_MAX_ENTRIES   (1 << 20)
 #define BSW_STATIC_SCRATCH_BYTES (256 + 8 * (size_t)BSW_STATIC_MAX_ENTRIES)
 int bsw_dev_getScores_static(bsw_t *h, bsw_seqpair_t *d_pairArray, const uint8_t *d_seqBufRef,
