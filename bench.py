@@ -702,6 +702,26 @@ def run_kswv(args):
                            "h2d_bytes_per_step": a2st["h2d_bytes"] // (args.steps + 2), "d2h_bytes_per_step": a2st["d2h_bytes"] // (args.steps + 2),
                            "api": "kswv_align2 on pinned host buffers: one call per tier instead of getScores(phase 0) + the caller's reversed-prefix "
                                   "loop + getScores(phase 1); the hand-off runs on the device (SURVEY.md 8(f).3)"}}
+    # windows from a resident 2-bit reference (SURVEY.md 8(f).2 applied to mate rescue): the "genome" is the concatenation of
+    # the two window buffers (N -> a base; expected results recomputed if that changed anything)
+    fw = np.concatenate([kr, kr16]); nn = fw > 3
+    e8, e16 = a1, b1
+    if nn.any():
+        fw[nn] = (np.nonzero(nn)[0] & 3).astype(np.uint8)
+        e8 = ora.kswv_align2_batch(K, fw[:len(kr)], kq, prm, c.cores)[0]; e16 = ora.kswv_align2_batch(K16, fw[len(kr):], kq16, prm, c.cores)[0]
+    Rf = bswb200.Reference(bswb200.pack_pac(fw), len(fw))
+    rp8, rp16 = pin(K["idr"].astype(np.int64)), pin(K16["idr"].astype(np.int64) + len(kr))
+    ha[...] = 0; hb[...] = 0
+
+    def step_align2_ref():
+        ks.align2Ref(hK, Rf, rp8, hkq, ha, n, 1); ks.align2Ref(hK16, Rf, rp16, hkq16, hb, n16, 0)
+    ks.reset_stats(); a3_ms = time_host(c, args, step_align2_ref); a3st = ks.stats()
+    check("e2e kswv_align2Ref 8-bit", e8, ha); check("e2e kswv_align2Ref 16-bit", e16, hb)
+    variants["align2_ref"] = {"ms_per_step": a3_ms / args.steps, "value": cells_step / (a3_ms / args.steps * 1e-3) / 1e9, "unit": "GCUPS (this rank)",
+                              "h2d_bytes_per_step": a3st["h2d_bytes"] // (args.steps + 2), "d2h_bytes_per_step": a3st["d2h_bytes"] // (args.steps + 2),
+                              "api": "bsw_ref_upload once + kswv_align2Ref(records, rpos, mates): the windows are cut out of the resident 2-bit "
+                                     "reference on the device, no target base crosses PCIe"}
+    Rf.close()
     sampler.stop()
     npairs = n + len(p1) + n16 + len(p16)
 

@@ -102,6 +102,12 @@ public:
     void align2(const SeqPair *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, kswr_t *aln, int32_t numPairs, int is8)
     { kswv_align2(h_, pairArray, seqBufRef, seqBufQer, reinterpret_cast<bsw_kswr_t *>(aln), numPairs, is8); }
 
+    /* the same with the windows cut from the resident reference (bsw_ref_upload) at rpos[i] = mem_matesw's rb: no target
+     * bases cross PCIe; see kswv_align2Ref */
+    void align2Ref(const SeqPair *pairArray, const bsw_ref_t *ref, const int64_t *rpos, const uint8_t *seqBufQer, kswr_t *aln,
+                   int32_t numPairs, int is8)
+    { kswv_align2Ref(h_, pairArray, ref, rpos, seqBufQer, reinterpret_cast<bsw_kswr_t *>(aln), numPairs, is8); }
+
     /* device-resident pairs: ksw_align2 (forward pass, hand-off, reverse pass) in one submission; see kswv_dev_align2 */
     void align2Resident(const SeqPair *d_pairArray, const uint8_t *d_seqBufRef, const uint8_t *d_seqBufQer, kswr_t *d_aln,
                         int32_t numPairs, int is8, void *stream)

@@ -27,7 +27,7 @@ KSW_XBYTE, KSW_XSTOP, KSW_XSUBO, KSW_XSTART = 0x10000, 0x20000, 0x40000, 0x80000
 EXPORTS = (
     "bsw_create", "bsw_destroy", "bsw_getScores8", "bsw_getScores16", "bsw_scalarBandedSWAWrapper",
     "kswv_create", "kswv_destroy", "kswv_getScores8", "kswv_getScores16",
-    "bsw_dev_getScores", "bsw_dev_getScores_static", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "kswv_align2", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
+    "bsw_dev_getScores", "bsw_dev_getScores_static", "bsw_dev_extendChained", "kswv_dev_getScores", "kswv_dev_align2", "kswv_align2", "kswv_align2Ref", "bsw_global2", "bsw_dev_global2", "bsw_host_alloc", "bsw_host_free",
     "bsw_get_stats", "bsw_reset_stats", "bsw_set_timing", "bsw_set_cell_counting",
     "kswv_get_stats", "kswv_reset_stats", "kswv_set_timing",
     "bsw_measure_dpx_peak", "bsw_device_count", "bsw_version",
@@ -96,6 +96,8 @@ def lib():
     L.bsw_dev_global2.argtypes = [vp, vp, i32, vp, vp, vp, C.c_int64, i32, vp]
     L.kswv_align2.restype = None
     L.kswv_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int]
+    L.kswv_align2Ref.restype = None
+    L.kswv_align2Ref.argtypes = [vp, vp, vp, vp, vp, vp, i32, C.c_int]
     L.kswv_dev_align2.restype = None
     L.kswv_dev_align2.argtypes = [vp, vp, vp, vp, vp, i32, C.c_int, vp]
     L.bsw_host_alloc.restype = vp
@@ -294,6 +296,13 @@ class kswv:
         """ksw_align2 on host buffers in one call: both passes and the hand-off on the device (kswv_align2)."""
         n = len(pairArray) if numPairs is None else numPairs
         self._L.kswv_align2(self._h, _ptr(pairArray), _ptr(seqBufRef), _ptr(seqBufQer), _ptr(aln), n, int(is8))
+
+    def align2Ref(self, pairArray, ref, rpos, seqBufQer, aln, numPairs=None, is8=1):
+        """kswv_align2 with the windows fetched on the device from the resident reference `ref` (a Reference object) at
+        doubled-strand positions `rpos` (int64, as for getScoresRef)."""
+        n = len(pairArray) if numPairs is None else numPairs
+        assert rpos.dtype == np.int64
+        self._L.kswv_align2Ref(self._h, _ptr(pairArray), ref._r, _ptr(rpos), _ptr(seqBufQer), _ptr(aln), n, int(is8))
 
     def dev_align2(self, d_pairs, d_ref, d_qer, d_aln, numPairs, is8=1, stream=0):
         """Forward pass, device-side hand-off and reverse pass of ksw_align2 in one submission (resident buffers)."""

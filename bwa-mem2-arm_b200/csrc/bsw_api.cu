@@ -1380,14 +1380,16 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
  * prefixes of the qualifying hits, and getScores(phase 1) -- here records and bases go up once, the hand-off and both
  * passes stay on the device, the finished kswr_t come down.  Chunks of BSW_CUDA_KSWV_CHUNK pairs (ramped at the ends):
  * chunk c + 1 uploads on its staging slot's stream while chunk c computes on slot 0's. */
-void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, bsw_kswr_t *aln,
-                 int32_t numPairs, int is8)
+/* kswv_align2 / kswv_align2Ref: rref != nullptr -> the targets are expanded on the device from the resident 2-bit reference
+ * (rpos[i] as in bsw_getScoresRef) into the staging slot's scratch, the device copies of the records point into it, and no
+ * target base crosses PCIe */
+static void align2_host(Core &k, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, bsw_kswr_t *aln,
+                        int32_t numPairs, int is8, const bsw_ref *rref, const int64_t *rpos)
 {
-    Core &k = h->k;
     k.st.calls++;
     const int n = numPairs;
     if (n <= 0) return;
-    if (!pairArray || !seqBufRef || !seqBufQer || !aln) die("null buffer passed to kswv_align2");
+    if (!pairArray || (!seqBufRef && !rref) || (rref && !rpos) || !seqBufQer || !aln) die("null buffer passed to kswv_align2 / kswv_align2Ref");
     const int nd = (int)k.devs.size();
     for (int i = 0; i < nd; ++i) { DevCtx &xi = k.cx(i); CK(cudaSetDevice(xi.dev)); for (Slot &sl : xi.slot) slot_retire(xi, sl); }
     const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
@@ -1411,16 +1413,45 @@ void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBu
             slot_retire(xx, st);                   /* the chunk that used this staging slot two chunks ago is home */
             const int first = cstart[mine[m]], cnt = cstart[mine[m] + 1] - first;
             Up &u = up[m & 1];
-            if (exact) extents(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi);
-            else extents_sampled(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi);
+            long long l1s = 0;
+            if (exact) {
+                extents(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi);
+                if (rref) for (int i = first; i < first + cnt; ++i) l1s += std::max(pairArray[i].len1, 0) + 4;
+            } else extents_sampled(pairArray, first, cnt, u.rlo, u.rhi, u.qlo, u.qhi, &l1s);
             st.pairs.reserve((size_t)cnt * sizeof(bsw_seqpair_t));
-            st.ref.reserve((size_t)(u.rhi - u.rlo) + 64); st.qer.reserve((size_t)(u.qhi - u.qlo) + 64);
+            st.qer.reserve((size_t)(u.qhi - u.qlo) + 64);
             st.aln.reserve((size_t)cnt * sizeof(bsw_kswr_t));
             CK(cudaMemcpyAsync(st.pairs.p, pairArray + first, (size_t)cnt * sizeof(bsw_seqpair_t), cudaMemcpyHostToDevice, st.stream));
-            if (u.rhi > u.rlo) CK(cudaMemcpyAsync(st.ref.p, seqBufRef + u.rlo, (size_t)(u.rhi - u.rlo), cudaMemcpyHostToDevice, st.stream));
             if (u.qhi > u.qlo) CK(cudaMemcpyAsync(st.qer.p, seqBufQer + u.qlo, (size_t)(u.qhi - u.qlo), cudaMemcpyHostToDevice, st.stream));
+            kk.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (u.qhi - u.qlo);
+            if (rref) {
+                /* targets: dense scratch filled from the resident reference; its size is estimated from the sampled lengths
+                 * (x 1.25) unless `exact` -- a pair that does not fit keeps an idr beyond the scratch, which the range check of
+                 * the kernels' prep reports like a pair outside the sampled byte ranges (-> the exact retry below) */
+                const long long cap = exact ? l1s + 64 : (l1s * 32 * 5) / 4 + 65536;
+                st.reftmp.reserve((size_t)cap + 64); st.rpos.reserve((size_t)cnt * 8); st.toff.reserve((size_t)cnt * 4 + 4);
+                st.plan.reserve(sizeof(Plan));
+                CK(cudaMemsetAsync(st.plan.p, 0, sizeof(Plan), st.stream));
+                CK(cudaMemcpyAsync(st.rpos.p, rpos + first, (size_t)cnt * 8, cudaMemcpyHostToDevice, st.stream));
+                size_t tmp_bytes = 0;
+                auto it = thrust::make_transform_iterator(thrust::make_counting_iterator(0), Len1Rounded{ (const bsw_seqpair_t *)st.pairs.p });
+                CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, it, (int *)st.toff.p, cnt, st.stream));
+                st.cubtmp.reserve(tmp_bytes);
+                CK(cub::DeviceScan::ExclusiveSum(st.cubtmp.p, tmp_bytes, it, (int *)st.toff.p, cnt, st.stream));
+                const uint8_t *d_pac = rref->on(xx.dev);
+                if (!d_pac) die("the reference was not uploaded to a device this handle uses");
+                ref_expand_kernel<<<(cnt + 31) / 32, 256, 0, st.stream>>>((bsw_seqpair_t *)st.pairs.p, cnt, (const long long *)st.rpos.p, (int *)st.toff.p,
+                                                                         d_pac, rref->l_pac, (uint8_t *)st.reftmp.p, cap, (Plan *)st.plan.p);
+                CK(cudaGetLastError());
+                CK(cudaMemcpyAsync(st.h_plan, st.plan.p, sizeof(Plan), cudaMemcpyDeviceToHost, st.stream));
+                kk.st.h2d_bytes += (int64_t)cnt * 8; kk.st.d2h_bytes += sizeof(Plan); kk.st.kernel_launches += 3;
+                u.rlo = 0; u.rhi = cap;
+            } else {
+                st.ref.reserve((size_t)(u.rhi - u.rlo) + 64);
+                if (u.rhi > u.rlo) CK(cudaMemcpyAsync(st.ref.p, seqBufRef + u.rlo, (size_t)(u.rhi - u.rlo), cudaMemcpyHostToDevice, st.stream));
+                kk.st.h2d_bytes += u.rhi - u.rlo;
+            }
             CK(cudaEventRecord(st.dev_done, st.stream));          /* "uploaded" */
-            kk.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (u.rhi - u.rlo) + (u.qhi - u.qlo);
         };
         if (!mine.empty()) upload(0, false);
         for (int m = 0; m < (int)mine.size(); ++m) {
@@ -1430,8 +1461,12 @@ void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBu
             for (int attempt = 0; ; ++attempt) {
                 const Up &u = up[m & 1];
                 CK(cudaStreamWaitEvent(cs.stream, st.dev_done, 0));
-                if (dev_align2_core(kk, rt, xx, cs, (bsw_seqpair_t *)st.pairs.p, (const uint8_t *)st.ref.p - u.rlo, (const uint8_t *)st.qer.p - u.qlo,
-                                    (bsw_kswr_t *)st.aln.p, cnt, is8, cs.stream, u.rlo, u.rhi, u.qlo, u.qhi)) break;
+                const uint8_t *d_ref = rref ? (const uint8_t *)st.reftmp.p : (const uint8_t *)st.ref.p - u.rlo;
+                const bool ok = dev_align2_core(kk, rt, xx, cs, (bsw_seqpair_t *)st.pairs.p, d_ref, (const uint8_t *)st.qer.p - u.qlo,
+                                                (bsw_kswr_t *)st.aln.p, cnt, is8, cs.stream, u.rlo, u.rhi, u.qlo, u.qhi);
+                /* (the core waited for its stream, which had waited for the upload: the expansion's counters are home) */
+                if (rref && st.h_plan->bad_pairs) die("kswv_align2Ref: a pair's window (rpos, len1) leaves the reference");
+                if (ok && !(rref && st.h_plan->oob_pairs)) break;      /* oob here: the estimated target scratch was too small */
                 if (attempt) die("a pair names bases outside its sequence buffer");
                 CK(cudaStreamSynchronize(cs.stream));
                 upload(m, true);                   /* the sampled ranges missed a pair: exact scan */
@@ -1478,6 +1513,19 @@ void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBu
         ctx_release(k.rt(w % nd), xb[w - 1]);
     }
     CK(cudaSetDevice(x0.dev));
+}
+
+void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer, bsw_kswr_t *aln,
+                 int32_t numPairs, int is8)
+{
+    align2_host(h->k, pairArray, seqBufRef, seqBufQer, aln, numPairs, is8, nullptr, nullptr);
+}
+
+void kswv_align2Ref(kswv_t *h, const bsw_seqpair_t *pairArray, const bsw_ref_t *ref, const int64_t *rpos, const uint8_t *seqBufQer,
+                    bsw_kswr_t *aln, int32_t numPairs, int is8)
+{
+    if (numPairs > 0 && !ref) die("null reference passed to kswv_align2Ref");
+    align2_host(h->k, pairArray, nullptr, seqBufQer, aln, numPairs, is8, ref, rpos);
 }
 
 /* ---- CIGAR generation ------------------------------------------------------ */

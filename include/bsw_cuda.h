@@ -244,6 +244,15 @@ void kswv_dev_align2(kswv_t *h, const bsw_seqpair_t *d_pairArray, const uint8_t 
 void kswv_align2(kswv_t *h, const bsw_seqpair_t *pairArray, const uint8_t *seqBufRef, const uint8_t *seqBufQer,
                  bsw_kswr_t *aln, int32_t numPairs, int is8);
 
+/* kswv_align2 with the target windows taken from the resident reference (SURVEY.md 8(f).2 applied to mate rescue; no
+ * reference counterpart).  mem_matesw cuts every window out of the packed reference with bns_fetch_seq only to hand it to
+ * ksw_align2 (bwa-mem2 src/bwamem_pair.cpp); here the caller passes, instead of target bases, one coordinate per pair in
+ * bwa's doubled coordinate system, exactly as for bsw_getScoresRef: rpos[i] >= 0 -> target[k] = base(rpos[i] + k) (what
+ * bns_fetch_seq returns for [rb, re), either strand), rpos[i] < 0 -> target[k] = base(~rpos[i] - k).  pairArray[i].idr is
+ * ignored; everything else as kswv_align2.  Records, rpos, the mates and the results are all that crosses PCIe. */
+void kswv_align2Ref(kswv_t *h, const bsw_seqpair_t *pairArray, const bsw_ref_t *ref, const int64_t *rpos,
+                    const uint8_t *seqBufQer, bsw_kswr_t *aln, int32_t numPairs, int is8);
+
 /* ---- CIGAR generation ------------------------------------------------------------
  * Batched bwa ksw.c ksw_global2 (bwa-mem2 src/ksw.cpp), the banded global alignment with backtrack that mem_reg2aln
  * reaches through bwa_gen_cigar2 once per reported alignment: one job per alignment, scoring from the handle

@@ -869,6 +869,65 @@ def test_reference_resident_targets(ora, bsw, monkeypatch):
     h.close(); R.close()
 
 
+def _kswv_ref_workload(ora, n, seed, qlo, qhi, l_pac=300000):
+    """Mate-rescue pairs whose windows are slices of a reference, as mem_matesw cuts them (bns_fetch_seq): both strands
+    (and, beyond what bwa issues, both directions); the mate is a mutated piece of its window."""
+    rng = np.random.default_rng(seed)
+    fwd = rng.integers(0, 4, l_pac).astype(np.uint8)
+    pairs = np.zeros(n, ora.SEQPAIR); rpos = np.zeros(n, np.int64)
+    refs, qers = [], []
+    ro = qo = 0
+    for i in range(n):
+        ql = int(rng.integers(qlo, qhi + 1)); tl = ql + int(rng.integers(50, 300))
+        down = bool(rng.integers(0, 4) == 0)
+        x0 = int(rng.integers(tl, 2 * l_pac - tl))
+        if (x0 < l_pac) != ((x0 - tl if down else x0 + tl) < l_pac):
+            x0 = int(rng.integers(tl, l_pac - tl))
+        rp = ~x0 if down else x0
+        t = ora.ref_slice(fwd, rp, tl)
+        o = int(rng.integers(0, tl - ql + 1))
+        q = t[o:o + ql].copy()
+        m = rng.random(ql) < 0.05
+        q[m] = (q[m] + rng.integers(1, 4, m.sum())) % 4
+        if rng.random() < 0.05:
+            q[rng.integers(0, ql)] = 4
+        if rng.random() < 0.1:                                  # an unrelated mate: low score, no second pass
+            q = rng.integers(0, 4, ql).astype(np.uint8)
+        pairs[i]["idr"], pairs[i]["idq"], pairs[i]["id"] = ro, qo, i
+        pairs[i]["len1"], pairs[i]["len2"] = tl, ql
+        pairs[i]["h0"] = ora.KSW_XSUBO | ora.KSW_XSTART | (ora.KSW_XBYTE if ql < 250 else 0) | 19
+        rpos[i] = rp
+        refs.append(t); qers.append(q); ro += tl; qo += ql
+    ref = np.concatenate(refs + [np.zeros(64, np.uint8)]); qer = np.concatenate(qers + [np.zeros(64, np.uint8)])
+    return fwd, pairs, rpos, ref, qer
+
+
+def test_kswv_align2_reference_resident(ora, bsw, monkeypatch):
+    """kswv_align2Ref (SURVEY.md 8(f).2 applied to mate rescue): windows fetched on the device from the resident 2-bit
+    reference at rpos == kswv_align2 on the same windows sent as bytes == the CPU restatement; several ramped chunks on
+    two workers (the sampled estimate of the target scratch at work), 8- and 16-bit arithmetic; no target base goes up."""
+    monkeypatch.setenv("BSW_CUDA_KSWV_CHUNK", "2048")
+    prm = ora.make_params()
+    ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
+    for n, seed, qlo, qhi, is8 in ((12000, 5, 60, 150, 1), (3000, 6, 200, 300, 0)):
+        fwd, P, rpos, ref, qer = _kswv_ref_workload(ora, n, seed, qlo, qhi)
+        R = bsw.Reference(bsw.pack_pac(fwd), len(fwd))
+        ao, _ = ora.kswv_align2_batch(P, ref, qer, prm, 8)
+        assert (ao["tb"] >= 0).sum() > n // 2
+        a1 = np.zeros(n, bsw.KSWR)
+        ks.align2(P, ref, qer, a1, n, is8)
+        assert (ao == a1).all(), np.nonzero(ao != a1)[0][:5]
+        g = P.copy(); g["idr"] = 987654321                    # ignored by the call
+        a2 = np.full(n, -7, np.int32).repeat(7).view(bsw.KSWR)[:n].copy()
+        ks.reset_stats()
+        ks.align2Ref(g, R, rpos, qer, a2, n, is8)
+        assert (ao == a2).all(), np.nonzero(ao != a2)[0][:5]
+        assert (g["idr"] == 987654321).all()
+        assert ks.stats()["h2d_bytes"] < n * 56 + n * 8 + len(qer) + 4096
+        R.close()
+    ks.close()
+
+
 def test_shim_classes_cpp_harness(ora, bsw, tmp_path):
     """bandedSWA_b200.h compiled into tools/bin/stream_c5 (g++, links libbswcuda.so): worker threads with per-task
     BandedPairWiseSW / kswv objects replay the caller protocol of both call sites; all pairs equal the oracle."""
