@@ -1014,4 +1014,12 @@ def test_multi_device_handle(ora, bsw, monkeypatch):
     ag[...] = 0
     ks.getScores8(P, r, q, ag, len(P), 1, 0)
     assert (a0 == ag).all()
+    # ... and with the windows cut from the reference copy each device holds
+    fwd, P, rpos, ref, qer = _kswv_ref_workload(ora, 20000, 9, 60, 150)
+    Rf = bsw.Reference(bsw.pack_pac(fwd), len(fwd))
+    ao, _ = ora.kswv_align2_batch(P, ref, qer, prm, 8)
+    ag = np.zeros(len(P), bsw.KSWR)
+    ks.align2Ref(P, Rf, rpos, qer, ag, len(P), 1)
+    assert (ao == ag).all()
+    Rf.close()
     ks.close()
