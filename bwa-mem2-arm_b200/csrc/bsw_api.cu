@@ -1392,7 +1392,8 @@ static void align2_host(Core &k, const bsw_seqpair_t *pairArray, const uint8_t *
     if (!pairArray || (!seqBufRef && !rref) || (rref && !rpos) || !seqBufQer || !aln) die("null buffer passed to kswv_align2 / kswv_align2Ref");
     const int nd = (int)k.devs.size();
     for (int i = 0; i < nd; ++i) { DevCtx &xi = k.cx(i); CK(cudaSetDevice(xi.dev)); for (Slot &sl : xi.slot) slot_retire(xi, sl); }
-    const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", 1 << 18));
+    /* windows from the resident reference: little to upload, so larger chunks (each costs ~0.7 ms of device under-use) */
+    const int chunk = std::max(1024, env_int("BSW_CUDA_KSWV_CHUNK", rref ? 1 << 19 : 1 << 18));
     const std::vector<int> cstart = chunk_starts(n, chunk, nd, k.chunk_ramp);
     const int nchunks = (int)cstart.size() - 1;
     /* A chunk's three phases each end in a small read-back the host waits for (two plans, the hand-off sizes), and the
