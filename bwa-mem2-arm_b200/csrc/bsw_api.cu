@@ -1427,8 +1427,8 @@ static void align2_host(Core &k, const bsw_seqpair_t *pairArray, const uint8_t *
             kk.st.h2d_bytes += (int64_t)cnt * sizeof(bsw_seqpair_t) + (u.qhi - u.qlo);
             if (rref) {
                 /* targets: dense scratch filled from the resident reference; its size is estimated from the sampled lengths
-                 * (x 1.25) unless `exact` -- a pair that does not fit keeps an idr beyond the scratch, which the range check of
-                 * the kernels' prep reports like a pair outside the sampled byte ranges (-> the exact retry below) */
+                 * (x 1.25) unless `exact` -- the expansion counts the pairs that do not fit (Plan::oob_pairs, read back with
+                 * the upload) and the chunk is redone with the exact size, like a chunk with a pair outside the sampled ranges */
                 const long long cap = exact ? l1s + 64 : (l1s * 32 * 5) / 4 + 65536;
                 st.reftmp.reserve((size_t)cap + 64); st.rpos.reserve((size_t)cnt * 8); st.toff.reserve((size_t)cnt * 4 + 4);
                 st.plan.reserve(sizeof(Plan));

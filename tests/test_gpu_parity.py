@@ -869,7 +869,7 @@ def test_reference_resident_targets(ora, bsw, monkeypatch):
     h.close(); R.close()
 
 
-def _kswv_ref_workload(ora, n, seed, qlo, qhi, l_pac=300000):
+def _kswv_ref_workload(ora, n, seed, qlo, qhi, l_pac=300000, skew=False):
     """Mate-rescue pairs whose windows are slices of a reference, as mem_matesw cuts them (bns_fetch_seq): both strands
     (and, beyond what bwa issues, both directions); the mate is a mutated piece of its window."""
     rng = np.random.default_rng(seed)
@@ -879,6 +879,8 @@ def _kswv_ref_workload(ora, n, seed, qlo, qhi, l_pac=300000):
     ro = qo = 0
     for i in range(n):
         ql = int(rng.integers(qlo, qhi + 1)); tl = ql + int(rng.integers(50, 300))
+        if skew:                                                # every 32nd pair (the ones the size estimate samples) short, the rest long
+            tl = ql + 20 if i % 32 == 0 else ql + int(rng.integers(400, 600))
         down = bool(rng.integers(0, 4) == 0)
         x0 = int(rng.integers(tl, 2 * l_pac - tl))
         if (x0 < l_pac) != ((x0 - tl if down else x0 + tl) < l_pac):
@@ -909,8 +911,9 @@ def test_kswv_align2_reference_resident(ora, bsw, monkeypatch):
     monkeypatch.setenv("BSW_CUDA_KSWV_CHUNK", "2048")
     prm = ora.make_params()
     ks = bsw.kswv(6, 1, 6, 1, 1, 4, 1, 2048, 256)
-    for n, seed, qlo, qhi, is8 in ((12000, 5, 60, 150, 1), (3000, 6, 200, 300, 0)):
-        fwd, P, rpos, ref, qer = _kswv_ref_workload(ora, n, seed, qlo, qhi)
+    # third case: the sampled estimate of the target scratch is far too small -> the exact retry of the chunk
+    for n, seed, qlo, qhi, is8, skew in ((12000, 5, 60, 150, 1, False), (3000, 6, 200, 300, 0, False), (6000, 7, 60, 150, 1, True)):
+        fwd, P, rpos, ref, qer = _kswv_ref_workload(ora, n, seed, qlo, qhi, skew=skew)
         R = bsw.Reference(bsw.pack_pac(fwd), len(fwd))
         ao, _ = ora.kswv_align2_batch(P, ref, qer, prm, 8)
         assert (ao["tb"] >= 0).sum() > n // 2
@@ -923,7 +926,7 @@ def test_kswv_align2_reference_resident(ora, bsw, monkeypatch):
         ks.align2Ref(g, R, rpos, qer, a2, n, is8)
         assert (ao == a2).all(), np.nonzero(ao != a2)[0][:5]
         assert (g["idr"] == 987654321).all()
-        assert ks.stats()["h2d_bytes"] < n * 56 + n * 8 + len(qer) + 4096
+        assert ks.stats()["h2d_bytes"] < (2 if skew else 1) * (n * 56 + n * 8 + len(qer)) + 4096
         R.close()
     ks.close()
 
